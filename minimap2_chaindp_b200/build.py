@@ -1,0 +1,65 @@
+"""Builds the native pieces in-tree (so the .so files travel to the GPU box with the snapshot).
+
+* ``minimap2_chaindp_b200/libmm2chain_b200.so`` -- CUDA kernels + C ABI (nvcc, sm_100a only)
+* ``minimap2_chaindp_b200/libmm2workload.so``   -- synthetic anchor generator (gcc, host only)
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+LIB = os.path.join(PKG, "libmm2chain_b200.so")
+WL_LIB = os.path.join(PKG, "libmm2workload.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "--shared", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-Xlinker", "-Bsymbolic-functions",
+    "-cudart", "static",
+]
+
+
+def _nvcc() -> str:
+    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found: the CUDA extension cannot be built (there is no CPU fallback)")
+
+
+def _stale(target: str, sources) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
+    srcs = [os.path.join(CSRC, f) for f in ("chain_kernels.cu", "chain_api.cu")]
+    deps = srcs + [os.path.join(CSRC, "chain_internal.h"), os.path.join(ROOT, "include", "mm2chain_b200.h")]
+    if force or _stale(LIB, deps):
+        cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-o", LIB, *srcs, "-lpthread"]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+            print(" ".join(cmd), file=sys.stderr)
+        subprocess.run(cmd, check=True)
+    return LIB
+
+
+def build_workload(force: bool = False) -> str:
+    src = os.path.join(CSRC, "workload.c")
+    if force or _stale(WL_LIB, [src]):
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fopenmp", "-Wall", "-o", WL_LIB, src, "-lm"], check=True)
+    return WL_LIB
+
+
+def build_all(force: bool = False, verbose: bool = False) -> None:
+    build_cuda(force, verbose)
+    build_workload(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose="-v" in sys.argv)

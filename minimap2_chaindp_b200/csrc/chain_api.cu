@@ -1,0 +1,785 @@
+// chain_api.cu -- host side of libmm2chain_b200.so: contexts, the sub-batch pipeline (H2D / kernels / D2H on
+// per-slot streams), the reference entry points and their combining batcher.  C ABI in include/mm2chain_b200.h.
+//
+// There is deliberately no CPU implementation of any stage in this file: if CUDA is unavailable every compute
+// entry point fails with MM2B200_ERR_CUDA.
+#include <atomic>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "chain_internal.h"
+
+using namespace mm2b200;
+
+// kalloc of the host program (kalloc.c:72,120), if it exports it
+extern "C" void *kmalloc(void *km, size_t size) __attribute__((weak));
+extern "C" void kfree(void *km, void *ptr) __attribute__((weak));
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char *fmt, ...)
+{
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	g_err = buf;
+	return code;
+}
+
+#define CUDA_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+	return fail(MM2B200_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------------------
+// growable pinned host buffer (the context's "kalloc-style" arena for results)
+// ---------------------------------------------------------------------------------------------------------
+struct PinnedBuf {
+	void *ptr = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes, size_t keep = 0)
+	{
+		if (bytes <= cap) return MM2B200_OK;
+		size_t ncap = cap ? cap : (size_t)1 << 16;
+		while (ncap < bytes) ncap += ncap / 2 + 4096;
+		void *np = nullptr;
+		if (cudaHostAlloc(&np, ncap, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return fail(MM2B200_ERR_NOMEM, "cudaHostAlloc(%zu) failed", ncap); }
+		if (keep && ptr) memcpy(np, ptr, keep);
+		if (ptr) cudaFreeHost(ptr);
+		ptr = np; cap = ncap;
+		return MM2B200_OK;
+	}
+	void release() { if (ptr) cudaFreeHost(ptr); ptr = nullptr; cap = 0; }
+	template <class T> T *as() { return (T*)ptr; }
+};
+
+struct StageAcc { double ms = 0; int64_t launches = 0; };
+struct StageSpan { int stage; cudaEvent_t beg, end; int launches; };
+static const char *const STAGE_NAMES[] = { "prep", "fill", "compact", "tail", "gather" };
+enum { ST_PREP = 0, ST_FILL, ST_COMPACT, ST_TAIL, ST_GATHER, ST_N };
+
+// ---------------------------------------------------------------------------------------------------------
+// one in-flight sub-batch
+// ---------------------------------------------------------------------------------------------------------
+struct Slot {
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev_totals = nullptr, ev_done = nullptr;
+	Workspace w{};
+	void *d_block = nullptr;          // one allocation carved into the workspace arrays
+	void *d_rec_out = nullptr;        // lazily allocated (fill_batch only)
+	size_t cap_anchors = 0, cap_reads = 0, cap_rec_out = 0;
+	PinnedBuf h_a, h_offs, h_totals;
+	// the chunk currently occupying the slot
+	int state = 0;                    // 0 idle, 1 kernels enqueued (totals pending), 2 outputs in flight
+	int64_t read0 = 0, n_reads = 0, anchor0 = 0, n_anchors = 0;
+	int64_t ubase = 0, bbase = 0;     // position of this chunk's outputs in the packed result
+};
+
+struct mm2b200_ctx {
+	int device = 0;
+	int profile = 0;
+	int64_t slot_anchors = 0;
+	LaunchCfg lc{};
+	std::vector<Slot> slots;
+	std::mutex mu;
+	std::atomic<int64_t> launches{0};
+	// results (pinned)
+	PinnedBuf r_n_u, r_u_off, r_b_off, r_u, r_b, r_rec_off, r_rec;
+	// profiling
+	StageAcc acc[ST_N];
+	std::vector<StageSpan> spans;
+	std::vector<cudaEvent_t> ev_pool;
+};
+
+static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
+{
+	if (anchors <= s.cap_anchors && reads <= s.cap_reads && s.d_block) return MM2B200_OK;
+	size_t A = s.cap_anchors > anchors ? s.cap_anchors : anchors;
+	size_t R = s.cap_reads > reads ? s.cap_reads : reads;
+	if (A < 1024) A = 1024;
+	if (R < 64) R = 64;
+	if (A >= ((size_t)1 << 31) - 64) return fail(MM2B200_ERR_ARG, "sub-batch of %zu anchors exceeds the 2^31 index space", A);
+	CUDA_TRY(cudaStreamSynchronize(s.stream));
+	if (s.d_block) { cudaFree(s.d_block); s.d_block = nullptr; }
+	struct Item { void **pp; size_t bytes; };
+	Workspace &w = s.w;
+	void *pa = nullptr, *poffs = nullptr;
+	Item items[] = {
+		{ &pa, 16 * A }, { &poffs, 8 * (R + 1) },
+		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N },
+		{ (void**)&w.f, 4 * A }, { (void**)&w.p, 4 * A }, { (void**)&w.v, 4 * A }, { (void**)&w.t, 4 * A },
+		{ (void**)&w.newid, 4 * A }, { (void**)&w.rec, 24 * A }, { (void**)&w.recp, 4 * A }, { (void**)&w.new_i, 4 * R },
+		{ (void**)&w.succ, A }, { (void**)&w.claimed, A }, { (void**)&w.members, 4 * A },
+		{ (void**)&w.cand, 8 * A }, { (void**)&w.chain_u, 8 * A }, { (void**)&w.wy, 8 * A },
+		{ (void**)&w.voff, 4 * A }, { (void**)&w.order, 4 * A }, { (void**)&w.ooff, 4 * A }, { (void**)&w.stk, 4 * A },
+		{ (void**)&w.n_u, 4 * R }, { (void**)&w.n_v, 4 * R },
+		{ (void**)&w.u_off, 8 * (R + 1) }, { (void**)&w.b_off, 8 * (R + 1) }, { (void**)&w.rec_off, 8 * (R + 1) },
+		{ (void**)&w.totals, 8 * 4 }, { (void**)&w.u_out, 8 * A }, { (void**)&w.b_out, 16 * A },
+	};
+	size_t total = 0;
+	for (auto &it : items) total += align_up(it.bytes, 256);
+	if (cudaMalloc(&s.d_block, total) != cudaSuccess) {
+		cudaGetLastError();
+		s.cap_anchors = s.cap_reads = 0;
+		return fail(MM2B200_ERR_NOMEM, "cudaMalloc(%zu bytes) for a %zu-anchor sub-batch failed", total, A);
+	}
+	char *cur = (char*)s.d_block;
+	for (auto &it : items) { *it.pp = cur; cur += align_up(it.bytes, 256); }
+	w.a = (const ulonglong2*)pa;
+	w.offs = (const int64_t*)poffs;
+	s.cap_anchors = A; s.cap_reads = R;
+	(void)ctx;
+	return MM2B200_OK;
+}
+
+static int ensure_rec_out(Slot &s)
+{
+	if (s.cap_rec_out >= s.cap_anchors && s.d_rec_out) return MM2B200_OK;
+	if (s.d_rec_out) cudaFree(s.d_rec_out);
+	s.d_rec_out = nullptr;
+	if (cudaMalloc(&s.d_rec_out, 24 * s.cap_anchors) != cudaSuccess) { cudaGetLastError(); return fail(MM2B200_ERR_NOMEM, "cudaMalloc(rec_out) failed"); }
+	s.cap_rec_out = s.cap_anchors;
+	return MM2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// profiling helpers
+// ---------------------------------------------------------------------------------------------------------
+static cudaEvent_t get_event(mm2b200_ctx *ctx)
+{
+	cudaEvent_t e = nullptr;
+	if (!ctx->ev_pool.empty()) { e = ctx->ev_pool.back(); ctx->ev_pool.pop_back(); }
+	else cudaEventCreate(&e);
+	return e;
+}
+
+struct StageTimer {
+	mm2b200_ctx *ctx; cudaStream_t st; int stage; cudaEvent_t beg = nullptr;
+	StageTimer(mm2b200_ctx *c, cudaStream_t s, int stage_) : ctx(c), st(s), stage(stage_)
+	{
+		if (ctx->profile) { beg = get_event(ctx); cudaEventRecord(beg, st); }
+	}
+	void done(int launches)
+	{
+		ctx->launches += launches;
+		if (ctx->profile) {
+			cudaEvent_t end = get_event(ctx);
+			cudaEventRecord(end, st);
+			ctx->spans.push_back(StageSpan{stage, beg, end, launches});
+		} else ctx->acc[stage].launches += launches;
+	}
+};
+
+static void drain_spans(mm2b200_ctx *ctx)
+{
+	for (auto &sp : ctx->spans) {
+		float ms = 0;
+		cudaEventSynchronize(sp.end);
+		cudaEventElapsedTime(&ms, sp.beg, sp.end);
+		ctx->acc[sp.stage].ms += ms;
+		ctx->acc[sp.stage].launches += sp.launches;
+		ctx->ev_pool.push_back(sp.beg);
+		ctx->ev_pool.push_back(sp.end);
+	}
+	ctx->spans.clear();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// kernel sequences
+// ---------------------------------------------------------------------------------------------------------
+static int check_params(const mm2b200_params_t *p)
+{
+	if (!p) return fail(MM2B200_ERR_ARG, "params is NULL");
+	if (p->max_dist_x < 0 || p->max_dist_y < 0) return fail(MM2B200_ERR_ARG, "max_dist_x/max_dist_y must be >= 0");
+	if (p->max_iter < 0) return fail(MM2B200_ERR_ARG, "max_iter must be >= 0 (0 = unbounded)");
+	return MM2B200_OK;
+}
+
+// prep + fill + compaction (the mm_chain_dp_fpga half, chain.c:218-327)
+static int enqueue_fill(mm2b200_ctx *ctx, const Workspace &w, const mm2b200_params_t &prm, cudaStream_t st)
+{
+	{ StageTimer t(ctx, st, ST_PREP); t.done(launch_prep(w, prm, st)); }
+	{ StageTimer t(ctx, st, ST_FILL); t.done(launch_fill(w, prm, ctx->lc, prm.is_cdna != 0, st)); }
+	return MM2B200_OK;
+}
+static int enqueue_compact(mm2b200_ctx *ctx, const Workspace &w, const mm2b200_params_t &prm, cudaStream_t st)
+{
+	StageTimer t(ctx, st, ST_COMPACT); t.done(launch_compact(w, prm, st));
+	return MM2B200_OK;
+}
+// ends / backtrack / order / gather (the mm_chain_dp_bottom half, chain.c:329-431)
+static int enqueue_bottom(mm2b200_ctx *ctx, const Workspace &w, const mm2b200_params_t &prm, cudaStream_t st)
+{
+	{ StageTimer t(ctx, st, ST_TAIL); t.done(launch_tail(w, prm, st)); }
+	{ StageTimer t(ctx, st, ST_GATHER); t.done(launch_gather(w, st)); }
+	return MM2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------------------
+extern "C" const char *mm2b200_last_error(void) { return g_err.c_str(); }
+extern "C" const char *mm2b200_version(void) { return "mm2chain-b200 0.1 (sm_100a)"; }
+
+extern "C" int mm2b200_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return n;
+}
+
+extern "C" void *mm2b200_pinned_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); fail(MM2B200_ERR_NOMEM, "cudaHostAlloc(%zu) failed", bytes); return nullptr; }
+	return p;
+}
+extern "C" void mm2b200_pinned_free(void *p) { if (p) cudaFreeHost(p); }
+
+extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
+{
+	if (!out) return fail(MM2B200_ERR_ARG, "ctx out pointer is NULL");
+	*out = nullptr;
+	mm2b200_config_t c{};
+	if (cfg) c = *cfg;
+	int ndev = 0;
+	CUDA_TRY(cudaGetDeviceCount(&ndev));
+	if (c.device < 0 || c.device >= ndev) return fail(MM2B200_ERR_CUDA, "device %d not available (%d CUDA devices)", c.device, ndev);
+	CUDA_TRY(cudaSetDevice(c.device));
+	mm2b200_ctx *ctx = new mm2b200_ctx();
+	ctx->device = c.device;
+	ctx->profile = c.profile;
+	ctx->slot_anchors = c.slot_anchors > 0 ? c.slot_anchors : ((int64_t)8 << 20);
+	const int ns = c.n_slots > 0 ? c.n_slots : 3;
+	ctx->slots.resize(ns);
+	for (auto &s : ctx->slots) {
+		if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&s.ev_totals, cudaEventDisableTiming) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming) != cudaSuccess) {
+			int rc = fail(MM2B200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+			mm2b200_destroy(ctx);
+			return rc;
+		}
+	}
+	query_launch_cfg(&ctx->lc);
+	*out = ctx;
+	return MM2B200_OK;
+}
+
+extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	for (auto &s : ctx->slots) {
+		if (s.stream) cudaStreamSynchronize(s.stream);
+		if (s.d_block) cudaFree(s.d_block);
+		if (s.d_rec_out) cudaFree(s.d_rec_out);
+		s.h_a.release(); s.h_offs.release(); s.h_totals.release();
+		if (s.ev_totals) cudaEventDestroy(s.ev_totals);
+		if (s.ev_done) cudaEventDestroy(s.ev_done);
+		if (s.stream) cudaStreamDestroy(s.stream);
+	}
+	drain_spans(ctx);
+	for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+	ctx->r_n_u.release(); ctx->r_u_off.release(); ctx->r_b_off.release(); ctx->r_u.release(); ctx->r_b.release();
+	ctx->r_rec_off.release(); ctx->r_rec.release();
+	delete ctx;
+}
+
+extern "C" int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx) { return ctx ? ctx->launches.load() : 0; }
+
+extern "C" int mm2b200_stage_ms(mm2b200_ctx_t *ctx, const char *stage, double *ms, int64_t *launches)
+{
+	if (!ctx || !stage) return fail(MM2B200_ERR_ARG, "NULL argument");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	cudaSetDevice(ctx->device);
+	drain_spans(ctx);
+	for (int i = 0; i < ST_N; ++i)
+		if (!strcmp(stage, STAGE_NAMES[i])) {
+			if (ms) *ms = ctx->acc[i].ms;
+			if (launches) *launches = ctx->acc[i].launches;
+			return MM2B200_OK;
+		}
+	return fail(MM2B200_ERR_ARG, "unknown stage '%s'", stage);
+}
+
+extern "C" void mm2b200_stage_reset(mm2b200_ctx_t *ctx)
+{
+	if (!ctx) return;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	cudaSetDevice(ctx->device);
+	drain_spans(ctx);
+	for (int i = 0; i < ST_N; ++i) ctx->acc[i] = StageAcc();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// sub-batch pipeline
+// ---------------------------------------------------------------------------------------------------------
+enum Mode { MODE_CHAIN = 0, MODE_FILL = 1, MODE_BOTTOM = 2 };
+
+struct BatchJob {
+	mm2b200_ctx *ctx;
+	const mm2b200_params_t *prm;
+	Mode mode;
+	int64_t n_reads;
+	const int64_t *offs;       // host, [n_reads+1]
+	const char *src;           // host anchors (16 B) or records (24 B)
+	size_t elem;               // 16 or 24
+	bool src_pinned;
+	int32_t *dbg_f, *dbg_p, *dbg_v;   // fill mode only
+	int64_t ubase = 0, bbase = 0;     // running output positions
+	int64_t n_units = 0, n_chunks = 0;
+};
+
+static bool is_pinned(const void *p)
+{
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+	return at.type == cudaMemoryTypeHost;
+}
+
+// stage A: totals are on the host -> enqueue the output copies
+static int finish_a(BatchJob &job, Slot &s)
+{
+	mm2b200_ctx *ctx = job.ctx;
+	CUDA_TRY(cudaEventSynchronize(s.ev_totals));
+	const int64_t *tot = s.h_totals.as<int64_t>();
+	const int64_t tu = tot[0], tb = tot[1];
+	job.n_units += tot[2];
+	s.ubase = job.ubase; s.bbase = job.bbase;
+	// (result arenas were reserved to their upper bounds in run_batch, so nothing here can move a buffer that an
+	// earlier chunk's copy is still writing to; per-chunk offset copies cover n_reads entries so chunks never overlap)
+	if (job.mode == MODE_FILL) {
+		const int64_t tr = tot[3];
+		CUDA_TRY(cudaMemcpyAsync(ctx->r_rec_off.as<int64_t>() + s.read0, s.w.rec_off, (size_t)s.n_reads * 8, cudaMemcpyDeviceToHost, s.stream));
+		if (tr) CUDA_TRY(cudaMemcpyAsync(ctx->r_rec.as<char>() + (size_t)job.bbase * 24, s.w.rec_out, (size_t)tr * 24, cudaMemcpyDeviceToHost, s.stream));
+		if (job.dbg_f) CUDA_TRY(cudaMemcpyAsync(job.dbg_f + s.anchor0, s.w.f, (size_t)s.n_anchors * 4, cudaMemcpyDeviceToHost, s.stream));
+		if (job.dbg_p) CUDA_TRY(cudaMemcpyAsync(job.dbg_p + s.anchor0, s.w.p, (size_t)s.n_anchors * 4, cudaMemcpyDeviceToHost, s.stream));
+		if (job.dbg_v) CUDA_TRY(cudaMemcpyAsync(job.dbg_v + s.anchor0, s.w.v, (size_t)s.n_anchors * 4, cudaMemcpyDeviceToHost, s.stream));
+		job.bbase += tr;
+	} else {
+		CUDA_TRY(cudaMemcpyAsync(ctx->r_n_u.as<int32_t>() + s.read0, s.w.n_u, (size_t)s.n_reads * 4, cudaMemcpyDeviceToHost, s.stream));
+		CUDA_TRY(cudaMemcpyAsync(ctx->r_u_off.as<int64_t>() + s.read0, s.w.u_off, (size_t)s.n_reads * 8, cudaMemcpyDeviceToHost, s.stream));
+		CUDA_TRY(cudaMemcpyAsync(ctx->r_b_off.as<int64_t>() + s.read0, s.w.b_off, (size_t)s.n_reads * 8, cudaMemcpyDeviceToHost, s.stream));
+		if (tu) CUDA_TRY(cudaMemcpyAsync(ctx->r_u.as<uint64_t>() + job.ubase, s.w.u_out, (size_t)tu * 8, cudaMemcpyDeviceToHost, s.stream));
+		if (tb) CUDA_TRY(cudaMemcpyAsync(ctx->r_b.as<char>() + (size_t)job.bbase * 16, s.w.b_out, (size_t)tb * 16, cudaMemcpyDeviceToHost, s.stream));
+		job.ubase += tu; job.bbase += tb;
+	}
+	CUDA_TRY(cudaEventRecord(s.ev_done, s.stream));
+	s.state = 2;
+	return MM2B200_OK;
+}
+
+// stage B: outputs are on the host -> rebase the chunk-local offsets
+static int finish_b(BatchJob &job, Slot &s)
+{
+	mm2b200_ctx *ctx = job.ctx;
+	CUDA_TRY(cudaEventSynchronize(s.ev_done));
+	if (job.mode == MODE_FILL) {
+		int64_t *ro = ctx->r_rec_off.as<int64_t>() + s.read0;
+		for (int64_t r = 0; r < s.n_reads; ++r) ro[r] += s.bbase;
+	} else {
+		int64_t *uo = ctx->r_u_off.as<int64_t>() + s.read0, *bo = ctx->r_b_off.as<int64_t>() + s.read0;
+		if (s.ubase || s.bbase)
+			for (int64_t r = 0; r < s.n_reads; ++r) { uo[r] += s.ubase; bo[r] += s.bbase; }
+	}
+	s.state = 0;
+	return MM2B200_OK;
+}
+
+static int run_batch(BatchJob &job)
+{
+	mm2b200_ctx *ctx = job.ctx;
+	int rc;
+	if ((rc = check_params(job.prm))) return rc;
+	if (job.n_reads < 0 || (job.n_reads > 0 && (!job.offs || (!job.src && job.offs[job.n_reads] > job.offs[0]))))
+		return fail(MM2B200_ERR_ARG, "bad batch arguments");
+	for (int64_t r = 0; r < job.n_reads; ++r) {
+		const int64_t n = job.offs[r + 1] - job.offs[r];
+		if (n < 0) return fail(MM2B200_ERR_ARG, "offs[] is not non-decreasing at read %lld", (long long)r);
+		if (n >= ((int64_t)1 << 29)) return fail(MM2B200_ERR_ARG, "read %lld has %lld anchors; the new_seed.p encoding (chain.c:95) needs n < 2^29", (long long)r, (long long)n);
+	}
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	CUDA_TRY(cudaSetDevice(ctx->device));
+	const int64_t R = job.n_reads;
+	// reserve the pinned result arenas to their upper bounds up front (sum n_v <= N, n_u <= n / max(min_cnt,1),
+	// new_i <= n): a buffer must never move while an earlier chunk's D2H copy is still landing in it
+	const int64_t N = R > 0 ? job.offs[R] - job.offs[0] : 0;
+	if (job.mode == MODE_FILL) {
+		if ((rc = ctx->r_rec_off.reserve((size_t)(R + 2) * 8))) return rc;
+		if ((rc = ctx->r_rec.reserve((size_t)(N + 1) * 24))) return rc;
+	} else {
+		const int64_t mc = job.prm->min_cnt > 1 ? job.prm->min_cnt : 1;
+		if ((rc = ctx->r_n_u.reserve((size_t)(R + 1) * 4))) return rc;
+		if ((rc = ctx->r_u_off.reserve((size_t)(R + 2) * 8))) return rc;
+		if ((rc = ctx->r_b_off.reserve((size_t)(R + 2) * 8))) return rc;
+		if ((rc = ctx->r_u.reserve((size_t)(N / mc + R + 1) * 8))) return rc;
+		if ((rc = ctx->r_b.reserve((size_t)(N + 1) * 16))) return rc;
+	}
+	job.src_pinned = job.src ? is_pinned(job.src) : true;
+	const int S = (int)ctx->slots.size();
+	int64_t r0 = 0, chunk = 0;
+	int prev_slot = -1;
+	while (r0 < R) {
+		// greedy chunk: consecutive reads up to slot_anchors anchors (at least one read)
+		int64_t r1 = r0 + 1;
+		while (r1 < R && job.offs[r1 + 1] - job.offs[r0] <= ctx->slot_anchors && r1 - r0 < ((int64_t)1 << 24)) ++r1;
+		const int64_t na = job.offs[r1] - job.offs[r0], nr = r1 - r0;
+		Slot &s = ctx->slots[chunk % S];
+		if (s.state == 1 && (rc = finish_a(job, s))) return rc;
+		if (s.state == 2 && (rc = finish_b(job, s))) return rc;
+		if ((rc = ensure_slot(ctx, s, (size_t)na, (size_t)nr))) return rc;
+		if (job.mode == MODE_FILL && (rc = ensure_rec_out(s))) return rc;
+		if ((rc = s.h_offs.reserve((size_t)(nr + 1) * 8))) return rc;
+		if ((rc = s.h_totals.reserve(64))) return rc;
+		int64_t *ho = s.h_offs.as<int64_t>();
+		for (int64_t r = 0; r <= nr; ++r) ho[r] = job.offs[r0 + r] - job.offs[r0];
+		s.read0 = r0; s.n_reads = nr; s.anchor0 = job.offs[r0] - job.offs[0]; s.n_anchors = na;
+		Workspace &w = s.w;
+		w.n_reads = (int32_t)nr; w.n_anchors = (int32_t)na;
+		w.rec_out = (new_seed*)s.d_rec_out;
+		CUDA_TRY(cudaMemcpyAsync((void*)w.offs, ho, (size_t)(nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+		void *dst = job.mode == MODE_BOTTOM ? (void*)w.rec : (void*)w.a;
+		const char *src = job.src + (size_t)job.offs[r0] * job.elem;
+		if (na) {
+			if (job.src_pinned) CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+			else {
+				if ((rc = s.h_a.reserve((size_t)na * job.elem))) return rc;
+				memcpy(s.h_a.ptr, src, (size_t)na * job.elem);
+				CUDA_TRY(cudaMemcpyAsync(dst, s.h_a.ptr, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+			}
+		}
+		if (job.mode == MODE_BOTTOM) {
+			StageTimer t(ctx, s.stream, ST_COMPACT); t.done(launch_split_records(w, s.stream));
+			enqueue_bottom(ctx, w, *job.prm, s.stream);
+		} else {
+			enqueue_fill(ctx, w, *job.prm, s.stream);
+			enqueue_compact(ctx, w, *job.prm, s.stream);
+			if (job.mode == MODE_CHAIN) enqueue_bottom(ctx, w, *job.prm, s.stream);
+			else {
+				StageTimer t(ctx, s.stream, ST_GATHER);
+				int nl = launch_pack_records(w, s.stream);
+				if (job.dbg_p) nl += launch_localize_p(w, s.stream);
+				t.done(nl);
+			}
+		}
+		CUDA_TRY(cudaMemcpyAsync(s.h_totals.ptr, w.totals, 32, cudaMemcpyDeviceToHost, s.stream));
+		CUDA_TRY(cudaEventRecord(s.ev_totals, s.stream));
+		CUDA_TRY(cudaGetLastError());
+		s.state = 1;
+		// while this chunk runs, move the previous one along
+		if (prev_slot >= 0 && ctx->slots[prev_slot].state == 1 && (rc = finish_a(job, ctx->slots[prev_slot]))) return rc;
+		prev_slot = (int)(chunk % S);
+		++chunk;
+		r0 = r1;
+	}
+	// drain in chunk order
+	for (int64_t c = chunk > S ? chunk - S : 0; c < chunk; ++c) {
+		Slot &s = ctx->slots[c % S];
+		if (s.state == 1 && (rc = finish_a(job, s))) return rc;
+	}
+	for (int64_t c = chunk > S ? chunk - S : 0; c < chunk; ++c) {
+		Slot &s = ctx->slots[c % S];
+		if (s.state == 2 && (rc = finish_b(job, s))) return rc;
+	}
+	job.n_chunks = chunk;
+	if (job.mode == MODE_FILL) ctx->r_rec_off.as<int64_t>()[R] = job.bbase;
+	else { ctx->r_u_off.as<int64_t>()[R] = job.ubase; ctx->r_b_off.as<int64_t>()[R] = job.bbase; }
+	return MM2B200_OK;
+}
+
+static void reset_slots(mm2b200_ctx *ctx)
+{	// after an error: make sure no slot is left half-finished
+	for (auto &s : ctx->slots) { if (s.stream) cudaStreamSynchronize(s.stream); s.state = 0; }
+	cudaGetLastError();
+}
+
+extern "C" int mm2b200_chain_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, const int64_t *offs,
+                                   const mm128_t *a, mm2b200_result_t *res)
+{
+	if (!ctx || !res) return fail(MM2B200_ERR_ARG, "NULL ctx or result");
+	BatchJob job{};
+	job.ctx = ctx; job.prm = prm; job.mode = MODE_CHAIN; job.n_reads = n_reads; job.offs = offs; job.src = (const char*)a; job.elem = 16;
+	int rc = run_batch(job);
+	if (rc) { reset_slots(ctx); return rc; }
+	res->n_reads = n_reads;
+	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
+	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
+	res->n_units = job.n_units; res->n_sub_batches = job.n_chunks;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_fill_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, const int64_t *offs,
+                                  const mm128_t *a, mm2b200_records_t *out, int32_t *f, int32_t *p, int32_t *v)
+{
+	if (!ctx || !out) return fail(MM2B200_ERR_ARG, "NULL ctx or result");
+	BatchJob job{};
+	job.ctx = ctx; job.prm = prm; job.mode = MODE_FILL; job.n_reads = n_reads; job.offs = offs; job.src = (const char*)a; job.elem = 16;
+	job.dbg_f = f; job.dbg_p = p; job.dbg_v = v;
+	int rc = run_batch(job);
+	if (rc) { reset_slots(ctx); return rc; }
+	out->n_reads = n_reads;
+	out->rec_off = ctx->r_rec_off.as<int64_t>();
+	out->rec = ctx->r_rec.as<new_seed>();
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_bottom_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, const int64_t *rec_off,
+                                    const struct new_seed *rec, mm2b200_result_t *res)
+{
+	if (!ctx || !res) return fail(MM2B200_ERR_ARG, "NULL ctx or result");
+	BatchJob job{};
+	job.ctx = ctx; job.prm = prm; job.mode = MODE_BOTTOM; job.n_reads = n_reads; job.offs = rec_off; job.src = (const char*)rec; job.elem = 24;
+	int rc = run_batch(job);
+	if (rc) { reset_slots(ctx); return rc; }
+	res->n_reads = n_reads;
+	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
+	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
+	res->n_units = 0; res->n_sub_batches = job.n_chunks;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
+                                    const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_result_t *out)
+{
+	int rc;
+	if (!ctx || !out) return fail(MM2B200_ERR_ARG, "NULL ctx or result");
+	if ((rc = check_params(prm))) return rc;
+	if (n_reads < 0 || n_anchors < 0 || !d_offs || (n_anchors && !d_a)) return fail(MM2B200_ERR_ARG, "bad device batch arguments");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	CUDA_TRY(cudaSetDevice(ctx->device));
+	Slot &s = ctx->slots[0];
+	if (s.state) return fail(MM2B200_ERR_STATE, "slot 0 busy");
+	if ((rc = ensure_slot(ctx, s, (size_t)n_anchors, (size_t)n_reads))) return rc;
+	Workspace w = s.w;              // private copy pointing at the caller's inputs
+	w.a = (const ulonglong2*)d_a; w.offs = d_offs;
+	w.n_reads = (int32_t)n_reads; w.n_anchors = (int32_t)n_anchors;
+	cudaStream_t st = (cudaStream_t)stream;
+	enqueue_fill(ctx, w, *prm, st);
+	enqueue_compact(ctx, w, *prm, st);
+	enqueue_bottom(ctx, w, *prm, st);
+	CUDA_TRY(cudaGetLastError());
+	out->d_n_u = w.n_u; out->d_u_off = w.u_off; out->d_b_off = w.b_off;
+	out->d_u = w.u_out; out->d_b = (const mm128_t*)w.b_out; out->d_totals = w.totals;
+	return MM2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Section 1: reference entry points.  Concurrent mm_chain_dp callers (kt_for workers, map.c:598-604) are
+// combined by a dispatcher thread into one device batch per parameter set: while the GPU works on one batch the
+// next callers queue up, so the batch size adapts to the number of host threads without any timer.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+struct Pending {
+	mm2b200_params_t prm;
+	int64_t n;
+	const mm128_t *a;
+	// filled by the dispatcher; pointers into the context's result arena, valid until `copied` is signalled
+	int rc = 0; std::string err;
+	int32_t n_u = 0; const uint64_t *u = nullptr; const mm128_t *b = nullptr; int64_t n_b = 0;
+	bool done = false;
+};
+
+struct Batcher {
+	std::mutex mu;
+	std::condition_variable cv_work, cv_done, cv_copied;
+	std::deque<Pending*> q;
+	int outstanding_copies = 0;
+	mm2b200_ctx *ctx = nullptr;
+	int init_rc = 0; std::string init_err;
+	bool started = false;
+	std::vector<mm128_t> gather; std::vector<int64_t> offs;
+	PinnedBuf stage;
+};
+
+Batcher *g_batcher = nullptr;
+std::once_flag g_batcher_once;
+std::mutex g_default_mu;
+mm2b200_ctx *g_default_ctx = nullptr;
+std::string g_default_err;
+
+mm2b200_ctx *default_ctx()
+{
+	std::lock_guard<std::mutex> lk(g_default_mu);
+	if (!g_default_ctx && g_default_err.empty()) {
+		mm2b200_config_t cfg{};
+		const char *dev = getenv("MM2B200_DEVICE");
+		cfg.device = dev ? atoi(dev) : 0;
+		cfg.n_slots = 2;
+		cfg.slot_anchors = (int64_t)4 << 20;
+		if (mm2b200_create(&cfg, &g_default_ctx) != MM2B200_OK) g_default_err = g_err.empty() ? "mm2b200_create failed" : g_err;
+	}
+	if (!g_default_ctx) g_err = g_default_err;
+	return g_default_ctx;
+}
+
+void dispatcher_main(Batcher *B)
+{
+	for (;;) {
+		std::vector<Pending*> batch;
+		{
+			std::unique_lock<std::mutex> lk(B->mu);
+			B->cv_work.wait(lk, [&] { return !B->q.empty(); });
+			// take every queued call that shares the first one's parameters
+			const mm2b200_params_t key = B->q.front()->prm;
+			for (auto it = B->q.begin(); it != B->q.end();) {
+				if (!memcmp(&(*it)->prm, &key, sizeof(key))) { batch.push_back(*it); it = B->q.erase(it); }
+				else ++it;
+			}
+		}
+		int64_t total = 0;
+		B->offs.assign(1, 0);
+		for (auto *p : batch) { total += p->n; B->offs.push_back(total); }
+		int rc = B->stage.reserve((size_t)(total > 0 ? total : 1) * sizeof(mm128_t));
+		mm2b200_result_t res{};
+		if (!rc) {
+			mm128_t *dst = B->stage.as<mm128_t>();
+			for (size_t k = 0; k < batch.size(); ++k)
+				if (batch[k]->n > 0) memcpy(dst + B->offs[k], batch[k]->a, (size_t)batch[k]->n * sizeof(mm128_t));
+			rc = mm2b200_chain_batch(B->ctx, &batch[0]->prm, (int64_t)batch.size(), B->offs.data(), dst, &res);
+		}
+		{
+			std::unique_lock<std::mutex> lk(B->mu);
+			for (size_t k = 0; k < batch.size(); ++k) {
+				Pending *p = batch[k];
+				p->rc = rc;
+				if (rc) p->err = g_err;
+				else {
+					p->n_u = res.n_u[k];
+					p->u = res.u + res.u_off[k];
+					p->b = res.b + res.b_off[k];
+					p->n_b = res.b_off[k + 1] - res.b_off[k];
+				}
+				p->done = true;
+			}
+			B->outstanding_copies = (int)batch.size();
+			B->cv_done.notify_all();
+			// the result arena is reused by the next batch: wait until every caller has copied its slice out
+			B->cv_copied.wait(lk, [&] { return B->outstanding_copies == 0; });
+		}
+	}
+}
+
+Batcher *batcher()
+{
+	std::call_once(g_batcher_once, [] {
+		Batcher *B = new Batcher();
+		B->ctx = default_ctx();
+		if (!B->ctx) { B->init_rc = MM2B200_ERR_CUDA; B->init_err = g_err; }
+		else { std::thread(dispatcher_main, B).detach(); B->started = true; }
+		g_batcher = B;
+	});
+	return g_batcher;
+}
+
+void *host_alloc(void *km, size_t bytes)
+{
+	if (kmalloc) return kmalloc(km, bytes);
+	return malloc(bytes ? bytes : 1);
+}
+void host_free(void *km, void *p)
+{
+	if (kfree) kfree(km, p);
+	else free(p);
+}
+
+} // namespace
+
+extern "C" mm128_t *mm_chain_dp(int max_dist_x, int max_dist_y, int bw, int max_skip, int min_cnt, int min_sc, int is_cdna,
+                                int n_segs, int64_t n, mm128_t *a, int *n_u_, uint64_t **_u, void *km)
+{
+	if (_u) *_u = 0;
+	if (n_u_) *n_u_ = 0;
+	g_err.clear();
+	if (km && !kmalloc) { fail(MM2B200_ERR_ARG, "km != NULL but the host program exports no kmalloc/kfree"); return nullptr; }
+	mm128_t *ret = nullptr;
+	Batcher *B = batcher();
+	if (!B->started) { g_err = B->init_err; host_free(km, a); return nullptr; }
+	if (n > 0) {
+		Pending pd;
+		pd.prm = mm2b200_params_t{max_dist_x, max_dist_y, bw, max_skip, min_cnt, min_sc, is_cdna, n_segs, 0};
+		pd.n = n; pd.a = a;
+		{
+			std::unique_lock<std::mutex> lk(B->mu);
+			B->q.push_back(&pd);
+			B->cv_work.notify_one();
+			B->cv_done.wait(lk, [&] { return pd.done; });
+		}
+		if (pd.rc == MM2B200_OK && pd.n_u > 0) {
+			uint64_t *u = (uint64_t*)host_alloc(km, (size_t)pd.n_u * 8);
+			ret = (mm128_t*)host_alloc(km, (size_t)pd.n_b * sizeof(mm128_t));
+			memcpy(u, pd.u, (size_t)pd.n_u * 8);
+			memcpy(ret, pd.b, (size_t)pd.n_b * sizeof(mm128_t));
+			if (_u) *_u = u; else host_free(km, u);
+			if (n_u_) *n_u_ = pd.n_u;
+		} else if (pd.rc != MM2B200_OK) g_err = pd.err;
+		{
+			std::lock_guard<std::mutex> lk(B->mu);
+			if (--B->outstanding_copies == 0) B->cv_copied.notify_all();
+		}
+	}
+	host_free(km, a);   // chain.c:137,214: the input array is consumed
+	return ret;
+}
+
+extern "C" struct new_seed *mm_chain_dp_fpga(int max_dist_x, int max_dist_y, int bw, int max_skip, int min_sc, int is_cdna,
+                                             int n_segs, int64_t n, mm128_t *a, uint32_t *_new_i)
+{
+	if (_new_i) *_new_i = 0;
+	g_err.clear();
+	mm2b200_ctx *ctx = default_ctx();
+	struct new_seed *ret = nullptr;
+	if (ctx && n > 0) {
+		static std::mutex mu;   // the returned arena slice must be copied before the next call reuses it
+		std::lock_guard<std::mutex> lk(mu);
+		mm2b200_params_t prm{max_dist_x, max_dist_y, bw, max_skip, 0, min_sc, is_cdna, n_segs, 0};
+		const int64_t offs[2] = {0, n};
+		mm2b200_records_t out{};
+		if (mm2b200_fill_batch(ctx, &prm, 1, offs, a, &out, nullptr, nullptr, nullptr) == MM2B200_OK) {
+			const int64_t m = out.rec_off[1] - out.rec_off[0];
+			ret = (struct new_seed*)malloc((size_t)(m > 0 ? m : 1) * sizeof(struct new_seed));   // chain.c:233: libc malloc, n entries
+			if (m > 0) memcpy(ret, out.rec + out.rec_off[0], (size_t)m * sizeof(struct new_seed));
+			if (_new_i) *_new_i = (uint32_t)m;
+		}
+	} else if (n <= 0) ret = (struct new_seed*)malloc(sizeof(struct new_seed));
+	free(a);   // chain.c:322
+	return ret;
+}
+
+extern "C" mm128_t *mm_chain_dp_bottom(int min_cnt, int min_sc, int n_segs, int *n_u_, uint64_t **_u, void *km,
+                                       struct new_seed *fpga_a, uint32_t new_i)
+{
+	(void)km; (void)n_segs;
+	if (_u) *_u = 0;
+	if (n_u_) *n_u_ = 0;
+	g_err.clear();
+	mm2b200_ctx *ctx = default_ctx();
+	if (!ctx || new_i == 0) return nullptr;
+	static std::mutex mu;
+	std::lock_guard<std::mutex> lk(mu);
+	mm2b200_params_t prm{0, 0, 0, 0, min_cnt, min_sc, 0, n_segs, 0};
+	const int64_t offs[2] = {0, (int64_t)new_i};
+	mm2b200_result_t res{};
+	if (mm2b200_bottom_batch(ctx, &prm, 1, offs, fpga_a, &res) != MM2B200_OK || res.n_u[0] == 0) return nullptr;
+	const int32_t nu = res.n_u[0];
+	const int64_t nb = res.b_off[1] - res.b_off[0];
+	uint64_t *u = (uint64_t*)malloc((size_t)nu * 8);
+	mm128_t *b = (mm128_t*)malloc((size_t)nb * sizeof(mm128_t));
+	memcpy(u, res.u + res.u_off[0], (size_t)nu * 8);
+	memcpy(b, res.b + res.b_off[0], (size_t)nb * sizeof(mm128_t));
+	if (_u) *_u = u; else free(u);
+	if (n_u_) *n_u_ = nu;
+	return b;
+}

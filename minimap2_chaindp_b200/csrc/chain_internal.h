@@ -1,0 +1,76 @@
+// chain_internal.h -- shared between the kernels (chain_kernels.cu) and the host side (chain_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "mm2chain_b200.h"
+
+namespace mm2b200 {
+
+// One independent anchor run: consecutive x-gaps all <= max_dist_x, so the DP fill of the run
+// depends on nothing outside it except the read's avg_qspan.
+struct Unit {
+	int32_t start;   // index of the first anchor in the batch-wide arrays
+	int32_t len;     // >= 2 (singletons are finished by the prep kernel)
+	int32_t read;    // owning read (for avg_qspan)
+	int32_t pad;
+};
+
+enum Counter { CNT_UNITS = 0, CNT_QUEUE = 1, CNT_MULTISEG = 2, CNT_LONG_UNITS = 3, CNT_QUEUE_LONG = 4, CNT_N = 8 };
+
+// Device workspace of one sub-batch ("slot").  All per-anchor arrays are indexed by the batch-wide anchor index;
+// per-read scratch of the tail lives at the read's own offset offs[r] (every per-read count is <= n_r).
+struct Workspace {
+	// inputs
+	const ulonglong2 *a;      // anchors (mm128_t) [n_anchors]
+	const int64_t *offs;      // [n_reads+1]
+	int32_t n_reads, n_anchors;
+	// prep
+	float *avg;               // [n_reads] avg_qspan (chain.c:47)
+	Unit *units;              // [n_anchors/2 + 1]
+	int32_t *counters;        // [CNT_N]
+	// fill (chain.c:52-90)
+	int32_t *f, *p, *v;       // [n_anchors]; p is a batch-wide index (or -1)
+	int32_t *t;               // [n_anchors] marks during the fill, then "first referencer" during compaction
+	// compaction (chain.c:93-122)
+	int32_t *newid;           // [n_anchors] old -> new index within the read, -1 = dropped
+	new_seed *rec;            // [n_anchors] records of read r at rec + offs[r]
+	int32_t *recp;            // [n_anchors] copy of rec[].p for the pointer walks
+	uint32_t *new_i;          // [n_reads]
+	// tail (chain.c:127-214)
+	uint8_t *succ, *claimed;  // [n_anchors]
+	int32_t *members;         // [n_anchors] v[] of chain.c:168
+	uint64_t *cand;           // [n_anchors] u[] before filtering (chain.c:153); reused as sort keys of the x-order
+	uint64_t *chain_u;        // [n_anchors] u[] after filtering, score order (chain.c:174-176)
+	uint64_t *wy;             // [n_anchors] payload of w[] (chain.c:201)
+	int32_t *voff;            // [n_anchors] start of chain k in members[]
+	int32_t *order;           // [n_anchors] chain index at final position i
+	int32_t *ooff;            // [n_anchors] anchor offset of final position i within the read's output
+	int32_t *stk;             // [n_anchors] explicit stack of the radix-sort emulation
+	int32_t *n_u;             // [n_reads]
+	int32_t *n_v;             // [n_reads]
+	// packed outputs
+	int64_t *u_off, *b_off;   // [n_reads+1]
+	int64_t *totals;          // [4]: sum n_u, sum n_v, n_units, sum new_i
+	int64_t *rec_off;         // [n_reads+1] (fill_batch only)
+	uint64_t *u_out;          // [n_anchors]
+	ulonglong2 *b_out;        // [n_anchors]
+	new_seed *rec_out;        // aliases b_out/u_out region? no: own buffer [n_anchors] (fill_batch only, lazily allocated)
+};
+
+struct LaunchCfg {
+	int sm_count;
+	int fill_blocks_per_sm;
+};
+
+// launchers (chain_kernels.cu); every launcher returns the number of kernels it enqueued
+int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
+int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg &cfg, bool generic, cudaStream_t s);
+int launch_compact(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
+int launch_split_records(const Workspace &w, cudaStream_t s);   // bottom_batch: rec[] uploaded by the host
+int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
+int launch_gather(const Workspace &w, cudaStream_t s);
+int launch_pack_records(const Workspace &w, cudaStream_t s);
+int launch_localize_p(const Workspace &w, cudaStream_t s);      // debug: p[] -> per-read indices
+void query_launch_cfg(LaunchCfg *cfg);
+
+} // namespace mm2b200

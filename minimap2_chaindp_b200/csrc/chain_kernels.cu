@@ -1,0 +1,682 @@
+// chain_kernels.cu -- sm_100a kernels for minimap2's anchor-chaining DP (reference: chain.c:23-216).
+//
+// Stage map (reference lines -> kernel):
+//   chain.c:46-47  avg_qspan, run splitting          k_prep            warp per read
+//   chain.c:52-90  DP fill f/p/v with the max_skip early exit       k_fill<GENERIC>   warp per run, persistent
+//   chain.c:93-122 compaction to new_seed[] + new indices           k_first_ref, k_compact
+//   chain.c:127-180 chain ends, peaks, ordering, backtrack, filters k_tail            CTA per read
+//   chain.c:186-214 gather + first-anchor-x order                   k_tail (order), k_scan_reads, k_gather
+//
+// Everything is integer work on 16-byte anchors; nothing here is GEMM-shaped, so no tensor cores.  The one
+// floating-point expression, (int)(dd * .01 * avg_qspan) (chain.c:73,78), is evaluated with explicit
+// round-to-nearest double multiplies in the reference's association order so the result is bit-identical.
+#include "chain_internal.h"
+
+namespace mm2b200 {
+
+#define FULL 0xffffffffu
+
+static __device__ __forceinline__ unsigned lanemask_lt(int lane) { return (1u << lane) - 1u; }           // lane in [0,31]
+static __device__ __forceinline__ unsigned mask_below(int n) { return n >= 32 ? FULL : ((1u << n) - 1u); } // n in [0,32]
+
+// ---------------------------------------------------------------------------------------------------------
+// k_prep: per read -- avg_qspan (chain.c:46-47), singleton defaults for f/p/v, mark reset, and the list of
+// independent runs (consecutive x gap <= max_dist_x; chain.c:58 makes st jump to the run start).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
+{
+	const int lane = threadIdx.x & 31;
+	const int gw = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+	const int nw = (int)((gridDim.x * (unsigned)blockDim.x) >> 5);
+	const unsigned long long mdx = (unsigned long long)(long long)max_dist_x;
+	for (int r = gw; r < w.n_reads; r += nw) {
+		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
+		unsigned long long sum = 0, prev_last_x = 0;
+		int carry_start = b, multiseg = 0;
+		for (int base = b; base < e; base += 32) {
+			const int i = base + lane;
+			const bool valid = i < e;
+			ulonglong2 ai = valid ? w.a[i] : make_ulonglong2(0ull, 0ull);
+			unsigned long long xp = __shfl_up_sync(FULL, ai.x, 1);
+			if (lane == 0) xp = prev_last_x;
+			const bool start = valid && (i == b || ai.x - xp > mdx);
+			prev_last_x = __shfl_sync(FULL, ai.x, 31);
+			if (valid) {
+				const int span = (int)((ai.y >> 32) & 0xff);
+				sum += (unsigned)span;
+				w.f[i] = span; w.p[i] = -1; w.v[i] = span; w.t[i] = -1;
+				if ((ai.y >> 48) & 0xff) multiseg = 1;
+			}
+			const unsigned smask = __ballot_sync(FULL, start);
+			const unsigned below = smask & lanemask_lt(lane);
+			const int prev_start = below ? base + (31 - __clz(below)) : carry_start;
+			const bool emit = start && i != b && (i - prev_start) >= 2;   // this start closes the run [prev_start, i)
+			const unsigned emask = __ballot_sync(FULL, emit);
+			if (emask) {
+				int slot0 = 0;
+				if (lane == 0) slot0 = atomicAdd(&w.counters[CNT_UNITS], __popc(emask));
+				slot0 = __shfl_sync(FULL, slot0, 0);
+				if (emit) {
+					Unit u; u.start = prev_start; u.len = i - prev_start; u.read = r; u.pad = 0;
+					w.units[slot0 + __popc(emask & lanemask_lt(lane))] = u;
+				}
+			}
+			if (smask) carry_start = base + (31 - __clz(smask));
+		}
+		for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(FULL, sum, d);
+		multiseg = __any_sync(FULL, multiseg);
+		if (lane == 0) {
+			if (e - carry_start >= 2) {
+				Unit u; u.start = carry_start; u.len = e - carry_start; u.read = r; u.pad = 0;
+				w.units[atomicAdd(&w.counters[CNT_UNITS], 1)] = u;
+			}
+			// (float)sum_qspan / n  (chain.c:47): u64->float, int64->float, IEEE float divide
+			w.avg[r] = e > b ? __fdiv_rn(__ull2float_rn(sum), __ll2float_rn((long long)(e - b))) : 0.0f;
+			if (multiseg) atomicOr(&w.counters[CNT_MULTISEG], 1);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_fill: the DP fill (chain.c:52-90), one warp per run, runs pulled from a device-side queue.
+//
+// For anchor i the 32 lanes score 32 predecessors j = jb - lane (descending j, chain.c:59) in parallel
+// (SURVEY B.2), publish the marks t[p[j]] = i, synchronise, read t[j] (B.3), and then resolve the sequential
+// state machine of chain.c:80-87 exactly (B.4): IMPROVE lanes are the strict prefix maxima, n_skip is replayed
+// over the ballot masks segment by segment between IMPROVE lanes, and the break lane is the first MARKED-MISS
+// lane that pushes n_skip past max_skip.  The winner is the last IMPROVE lane before the break, which is also
+// the reference's "largest j wins ties" rule.
+//
+// Window test: within a run consecutive gaps are <= max_dist_x < 2^31, so the true distance of the first lane
+// that falls out of the window is < 2^32 and the low 32 bits of x decide it exactly; lanes past it are dropped.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __forceinline__ int lin_cost(int dd, double avg)
+{	// (int)(dd * .01 * avg_qspan): ((double)dd * 0.01) * (double)avg, truncation toward zero
+	return __double2int_rz(__dmul_rn(__dmul_rn(__int2double_rn(dd), 0.01), avg));
+}
+
+template <bool GENERIC>
+__global__ void __launch_bounds__(128) k_fill(Workspace w, mm2b200_params_t prm)
+{
+	// the two variants are both launched; the device-side flag decides which one does the work
+	const bool need_generic = prm.is_cdna || (w.counters[CNT_MULTISEG] != 0);
+	if (need_generic != GENERIC) return;
+
+	const int lane = threadIdx.x & 31;
+	const int n_units = w.counters[CNT_UNITS];
+	const unsigned mdx = (unsigned)prm.max_dist_x;
+	const int dq_max = prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x;   // same-segment bound (chain.c:64)
+	const unsigned dr_max = (prm.n_segs > 1 && !prm.is_cdna) ? (unsigned)prm.max_dist_y : 0xffffffffu;  // chain.c:67
+	const int max_skip = prm.max_skip, bw = prm.bw;
+	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
+	const ulonglong2 *__restrict__ a = w.a;
+	int32_t *f = w.f, *p = w.p, *v = w.v, *t = w.t;
+
+	for (;;) {
+		int u = 0;
+		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
+		u = __shfl_sync(FULL, u, 0);
+		if (u >= n_units) break;
+		const Unit un = w.units[u];
+		const int s = un.start, e = un.start + un.len;
+		const double avg = (double)w.avg[un.read];
+
+		for (int i = s + 1; i < e; ++i) {
+			const ulonglong2 ai = a[i];
+			const unsigned xi = (unsigned)ai.x;
+			const int qi = (int)(unsigned)ai.y;
+			const int span = (int)((ai.y >> 32) & 0xff);
+			const int sidi = (int)((ai.y >> 48) & 0xff);
+			int max_f = span, max_j = -1, n_skip = 0;
+			bool done = false;
+			const int jlo = (i - s > max_iter) ? i - max_iter : s;      // optional max_iter clamp (0 = off)
+
+			for (int jb = i - 1; jb >= jlo && !done; jb -= 32) {
+				const int j = jb - lane;
+				const bool valid = j >= jlo;
+				ulonglong2 aj = make_ulonglong2(0ull, 0ull);
+				int fj = 0, pj = -1;
+				if (valid) { aj = a[j]; fj = f[j]; pj = p[j]; }
+				const unsigned dr = xi - (unsigned)aj.x;
+				const unsigned wmask = __ballot_sync(FULL, valid && dr <= mdx);
+				int nwin = 32;
+				if (wmask != FULL) { nwin = __ffs(~wmask) - 1; done = true; }
+				if (nwin == 0) break;
+				const bool act = lane < nwin;
+
+				// ---- pair score (chain.c:60-79) ----
+				const int dq = qi - (int)(unsigned)aj.y;
+				bool skip;
+				int sc;
+				if (!GENERIC) {
+					skip = !act || dr == 0 || dq <= 0 || dq > dq_max || dr > dr_max;
+					const int dd = abs((int)dr - dq);
+					skip = skip || dd > bw;
+					sc = min(min(dq, (int)dr), span);
+					const int log_dd = dd ? 31 - __clz(dd) : 0;
+					sc -= lin_cost(dd, avg) + (log_dd >> 1);
+				} else {
+					const bool same = sidi == (int)((aj.y >> 48) & 0xff);
+					skip = !act || (same && dr == 0) || dq <= 0;
+					skip = skip || (same && dq > prm.max_dist_y) || dq > prm.max_dist_x;
+					const int dd = abs((int)dr - dq);
+					skip = skip || (same && dd > bw);
+					skip = skip || (prm.n_segs > 1 && !prm.is_cdna && same && dr > (unsigned)prm.max_dist_y);
+					sc = min(min(dq, (int)dr), span);
+					const int log_dd = dd ? 31 - __clz(dd) : 0;
+					const int c_lin = lin_cost(dd, avg);
+					if (prm.is_cdna || !same) {
+						if (!same && dr == 0) ++sc;
+						else if ((int)dr > dq || !same) sc -= min(c_lin, log_dd);
+						else sc -= c_lin + (log_dd >> 1);
+					} else sc -= c_lin + (log_dd >> 1);
+				}
+				sc += fj;
+
+				// ---- marks (chain.c:83,87): publish, synchronise, read ----
+				if (!skip && pj >= 0) t[pj] = i;
+				__syncwarp();
+				const bool marked = !skip && t[j] == i;
+
+				// ---- IMPROVE lanes = strict prefix maxima over the visit order (chain.c:80) ----
+				int pm = skip ? (int)0x80000000 : sc;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const int o = __shfl_up_sync(FULL, pm, d);
+					if (lane >= d) pm = max(pm, o);
+				}
+				int ex = __shfl_up_sync(FULL, pm, 1);
+				ex = lane == 0 ? max_f : max(ex, max_f);
+				const bool improve = !skip && sc > ex;
+				const unsigned imp = __ballot_sync(FULL, improve);
+				const unsigned mm = __ballot_sync(FULL, marked && !improve);
+
+				// ---- replay n_skip (chain.c:82,84) over the masks; find the break lane ----
+				int brk = -1;
+				{
+					unsigned rem = imp;
+					int pos = 0;
+					for (;;) {
+						const int nxt = rem ? __ffs(rem) - 1 : 32;
+						const unsigned seg = mm & mask_below(nxt) & ~mask_below(pos);
+						const int cnt = __popc(seg);
+						const int need = max(max_skip - n_skip + 1, 1);
+						if (cnt >= need) {
+							const int c = __popc(seg & (lanemask_lt(lane) | (1u << lane)));
+							const unsigned hit = __ballot_sync(FULL, ((seg >> lane) & 1u) && c == need);
+							brk = __ffs(hit) - 1;
+							break;
+						}
+						n_skip += cnt;
+						if (nxt == 32) break;
+						if (n_skip > 0) --n_skip;
+						rem &= rem - 1;
+						pos = nxt + 1;
+					}
+				}
+				const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
+				if (impb) {
+					const int L = 31 - __clz(impb);
+					max_f = __shfl_sync(FULL, sc, L);
+					max_j = jb - L;
+				}
+				if (brk >= 0) done = true;
+			}
+			if (lane == 0) {
+				f[i] = max_f; p[i] = max_j;
+				int vi = max_f;
+				if (max_j >= 0) { const int vj = v[max_j]; if (vj > max_f) vi = vj; }   // chain.c:90
+				v[i] = vi;
+			}
+			__syncwarp();
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// compaction (chain.c:93-122)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_first_ref(Workspace w)
+{	// r(k) = min{ i : p[i] == k } into t[] (preset to 0x7f7f7f7f)
+	const int n = w.n_anchors;
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const int pi = w.p[i];
+		if (pi >= 0) atomicMin(&w.t[pi], i);
+	}
+}
+
+static __device__ __forceinline__ void store_rec(new_seed *dst, ulonglong2 seed, int32_t p, int32_t f)
+{
+	unsigned long long *q = reinterpret_cast<unsigned long long*>(dst);
+	q[0] = seed.x; q[1] = seed.y;
+	q[2] = (unsigned long long)(unsigned)p | ((unsigned long long)(unsigned)f << 32);
+}
+
+__global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
+{
+	const int lane = threadIdx.x & 31;
+	const int gw = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+	const int nw = (int)((gridDim.x * (unsigned)blockDim.x) >> 5);
+	for (int r = gw; r < w.n_reads; r += nw) {
+		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
+		new_seed *rec = w.rec + b;
+		int32_t *recp = w.recp + b;
+		int n_new = 0;
+		for (int base = b; base < e; base += 32) {
+			const int i = base + lane;
+			const bool valid = i < e;
+			int pi = -1, vi = 0, fi = 0;
+			if (valid) { pi = w.p[i]; vi = w.v[i]; fi = w.f[i]; }
+			const bool E = valid && (vi >= min_sc || pi >= 0);                  // chain.c:109
+			bool late = false;
+			int vp = 0, fp = 0;
+			if (pi >= 0) {
+				vp = w.v[pi]; fp = w.f[pi];
+				late = !(vp >= min_sc || w.p[pi] >= 0) && w.t[pi] == i;         // chain.c:93-107: first referencer emits it
+			}
+			const int cnt = (E ? 1 : 0) + (late ? 1 : 0);
+			int incl = cnt;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const int o = __shfl_up_sync(FULL, incl, d);
+				if (lane >= d) incl += o;
+			}
+			const int slot = n_new + incl - cnt;          // first record this lane emits
+			const int my_new = slot + (late ? 1 : 0);
+			if (valid) w.newid[i] = E ? my_new : -1;
+			__syncwarp();
+			if (late) w.newid[pi] = slot;
+			__syncwarp();
+			if (late) {
+				const int32_t pw = (int32_t)(0xfffffffcu | (vp >= min_sc ? 1u : 0u) | (fp < vp ? 2u : 0u));
+				store_rec(&rec[slot], w.a[pi], pw, fp);
+				recp[slot] = pw;
+			}
+			if (E) {
+				const int pn = pi >= 0 ? w.newid[pi] : -1;
+				const int32_t pw = (int32_t)(((unsigned)pn << 2) | (vi >= min_sc ? 1u : 0u) | (fi < vi ? 2u : 0u));
+				store_rec(&rec[my_new], w.a[i], pw, fi);
+				recp[my_new] = pw;
+			}
+			n_new += __shfl_sync(FULL, incl, 31);
+		}
+		if (lane == 0) w.new_i[r] = (uint32_t)n_new;
+	}
+}
+
+// bottom_batch: records come from the host; derive recp[] and new_i[]
+__global__ void __launch_bounds__(256) k_split_records(Workspace w)
+{
+	const int n = w.n_anchors;
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) w.recp[i] = w.rec[i].p;
+	for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < w.n_reads; r += gridDim.x * blockDim.x)
+		w.new_i[r] = (uint32_t)(w.offs[r + 1] - w.offs[r]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_tail: chain.c:127-214 for one read per CTA.
+// ---------------------------------------------------------------------------------------------------------
+#define TAIL_T 128
+#define RS_MIN 64   // RS_MIN_SIZE, ksort.h:98
+
+// ascending in-place sort of z[0..n) by the whole CTA ("flip" bitonic network: every compare-exchange is
+// ascending, so a virtual +inf padding beyond n never has to move)
+static __device__ void cta_sort_u64(uint64_t *z, int n)
+{
+	const int tid = threadIdx.x;
+	for (int k = 2; (k >> 1) < n; k <<= 1) {
+		for (int i = tid; i < n; i += TAIL_T) {
+			const int l = i ^ (k - 1);
+			if (l > i && l < n) { const uint64_t x = z[i], y = z[l]; if (x > y) { z[i] = y; z[l] = x; } }
+		}
+		__syncthreads();
+		for (int j = k >> 2; j > 0; j >>= 1) {
+			for (int i = tid; i < n; i += TAIL_T) {
+				const int l = i ^ j;
+				if (l > i && l < n) { const uint64_t x = z[i], y = z[l]; if (x > y) { z[i] = y; z[l] = x; } }
+			}
+			__syncthreads();
+		}
+	}
+}
+
+// rs_insertsort (ksort.h:105-115) on parallel arrays (key, payload)
+static __device__ void ins_sort_kv(uint64_t *kx, uint64_t *ky, int beg, int end)
+{
+	for (int i = beg + 1; i < end; ++i) {
+		if (kx[i] < kx[i - 1]) {
+			const uint64_t tx = kx[i], ty = ky[i];
+			int j = i;
+			for (; j > beg && tx < kx[j - 1]; --j) { kx[j] = kx[j - 1]; ky[j] = ky[j - 1]; }
+			kx[j] = tx; ky[j] = ty;
+		}
+	}
+}
+
+// radix_sort_128x (ksort.h:116-151, misc.c:136-137) replayed step for step by one thread so that the
+// (unstable) order of equal keys matches the reference.  Sub-buckets are independent, so the recursion is
+// replaced by an explicit stack of (beg, end, shift) in stk[].
+static __device__ void radix_sort_kv_exact(uint64_t *kx, uint64_t *ky, int n, int32_t *stk, int *head, int *tail)
+{
+	if (n <= RS_MIN) { ins_sort_kv(kx, ky, 0, n); return; }
+	int sp = 0;
+	stk[0] = 0; stk[1] = n; stk[2] = 56; sp = 3;
+	while (sp) {
+		sp -= 3;
+		const int beg = stk[sp], end = stk[sp + 1], shift = stk[sp + 2];
+		for (int k = 0; k < 256; ++k) head[k] = 0;
+		for (int i = beg; i < end; ++i) ++head[(kx[i] >> shift) & 0xff];
+		for (int k = 0, acc = beg; k < 256; ++k) { const int c = head[k]; head[k] = acc; acc += c; tail[k] = acc; }
+		for (int k = 0; k < 256;) {
+			if (head[k] != tail[k]) {
+				int l = (int)((kx[head[k]] >> shift) & 0xff);
+				if (l != k) {
+					uint64_t tx = kx[head[k]], ty = ky[head[k]];
+					do {
+						const uint64_t sx = tx, sy = ty;
+						tx = kx[head[l]]; ty = ky[head[l]];
+						kx[head[l]] = sx; ky[head[l]] = sy; ++head[l];
+						l = (int)((tx >> shift) & 0xff);
+					} while (l != k);
+					kx[head[k]] = tx; ky[head[k]] = ty; ++head[k];
+				} else ++head[k];
+			} else ++k;
+		}
+		if (shift) {
+			const int next = shift > 8 ? shift - 8 : 0;
+			for (int k = 0, st = beg; k < 256; ++k) {
+				const int en = tail[k], sz = en - st;
+				if (sz > RS_MIN) { stk[sp] = st; stk[sp + 1] = en; stk[sp + 2] = next; sp += 3; }
+				else if (sz > 1) ins_sort_kv(kx, ky, st, en);
+				st = en;
+			}
+		}
+	}
+}
+
+__global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, int32_t min_sc)
+{
+	__shared__ int s_cnt, s_nu, s_nv;
+	__shared__ int s_head[256], s_tail[256];
+	const int tid = threadIdx.x;
+	for (int r = blockIdx.x; r < w.n_reads; r += gridDim.x) {
+		const int base = (int)w.offs[r];
+		const int cap = (int)(w.offs[r + 1] - w.offs[r]);
+		const int m = (int)w.new_i[r];
+		if (m == 0) {
+			if (tid == 0) { w.n_u[r] = 0; w.n_v[r] = 0; }
+			continue;
+		}
+		const int32_t *rp = w.recp + base;
+		const new_seed *rec = w.rec + base;
+		uint8_t *succ = w.succ + base, *claimed = w.claimed + base;
+		int32_t *members = w.members + base, *voff = w.voff + base, *order = w.order + base, *ooff = w.ooff + base;
+		uint64_t *cand = w.cand + base, *chain_u = w.chain_u + base, *wy = w.wy + base;
+
+		// chain.c:128-131: who is somebody's predecessor
+		for (int i = tid; i < m; i += TAIL_T) { succ[i] = 0; claimed[i] = 0; }
+		if (tid == 0) s_cnt = 0;
+		__syncthreads();
+		for (int i = tid; i < m; i += TAIL_T) { const int pp = rp[i]; if (pp >= 0) succ[pp >> 2] = 1; }
+		__syncthreads();
+		// chain.c:132-155: ends (bit0 set, no successor) -> peak (walk while bit1 set)
+		for (int i = tid; i < m; i += TAIL_T) {
+			int pp = rp[i];
+			if ((pp & 1) && !succ[i]) {
+				int j = i;
+				while (j >= 0 && (pp & 2)) { j = pp >> 2; if (j >= 0) pp = rp[j]; }
+				if (j < 0) j = i;
+				cand[atomicAdd(&s_cnt, 1)] = ((uint64_t)(uint32_t)rec[j].f << 32) | (uint32_t)j;
+			}
+		}
+		__syncthreads();
+		const int n_end = s_cnt;
+		if (n_end == 0) {
+			if (tid == 0) { w.n_u[r] = 0; w.n_v[r] = 0; }
+			__syncthreads();
+			continue;
+		}
+		// chain.c:156-160: descending (peak score, peak index) == ascending sort read backwards
+		cta_sort_u64(cand, n_end);
+
+		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains
+		if (tid == 0) {
+			int n_v = 0, k = 0;
+			for (int ii = n_end - 1; ii >= 0; --ii) {
+				const uint64_t c = cand[ii];
+				const int peak_sc = (int)(c >> 32);
+				int j = (int)(uint32_t)c;
+				const int n0 = n_v;
+				do {
+					if (n_v < cap) members[n_v] = j;
+					++n_v;
+					claimed[j] = 1;
+					j = rp[j] >> 2;
+				} while (j >= 0 && !claimed[j]);
+				const int cnt = n_v - n0;
+				bool keep = false;
+				uint64_t val = 0;
+				if (n_v > cap) { /* would overrun the reference's v[] as well (chain.c:168); drop */ }
+				else if (j < 0) {
+					if (cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)peak_sc << 32) | (uint32_t)cnt; }
+				} else {
+					const int d = peak_sc - rec[j].f;
+					if (d >= min_sc && cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)d << 32) | (uint32_t)cnt; }
+				}
+				if (keep) { chain_u[k] = val; voff[k] = n0; ++k; }
+				else n_v = n0;
+			}
+			s_nu = k; s_nv = n_v;
+			w.n_u[r] = k; w.n_v[r] = n_v;
+		}
+		__syncthreads();
+		const int n_u = s_nu;
+		if (n_u > 0) {
+			// chain.c:199-204: w[k] = { x of the chain's first anchor, offset<<32 | k }, sorted by x only
+			uint64_t *wx = cand;   // candidates are consumed; reuse as sort keys
+			for (int k = tid; k < n_u; k += TAIL_T) {
+				const int cnt = (int)(uint32_t)chain_u[k];
+				wx[k] = rec[members[voff[k] + cnt - 1]].seed.x;
+				wy[k] = ((uint64_t)(uint32_t)voff[k] << 32) | (uint32_t)k;
+			}
+			__syncthreads();
+			if (n_u <= RS_MIN) {
+				// insertion sort is stable: rank = #{smaller} + #{equal and earlier}
+				for (int k = tid; k < n_u; k += TAIL_T) {
+					const uint64_t xk = wx[k];
+					int rank = 0;
+					for (int k2 = 0; k2 < n_u; ++k2) { const uint64_t x2 = wx[k2]; rank += (x2 < xk) || (x2 == xk && k2 < k); }
+					order[rank] = k;
+				}
+			} else {
+				if (tid == 0) radix_sort_kv_exact(wx, wy, n_u, w.stk + base, s_head, s_tail);
+				__syncthreads();
+				for (int k = tid; k < n_u; k += TAIL_T) order[k] = (int)(uint32_t)wy[k];
+			}
+			__syncthreads();
+			if (tid == 0) {
+				int acc = 0;
+				for (int i = 0; i < n_u; ++i) { ooff[i] = acc; acc += (int)(uint32_t)chain_u[order[i]]; }
+			}
+		}
+		__syncthreads();
+	}
+}
+
+// exclusive scans over reads: n_u -> u_off, n_v -> b_off, new_i -> rec_off; totals
+__global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
+{
+	__shared__ long long s_part[3][32];
+	__shared__ long long s_carry[3];
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	if (tid < 3) s_carry[tid] = 0;
+	__syncthreads();
+	for (int base = 0; base < w.n_reads; base += 1024) {
+		const int r = base + tid;
+		long long val[3] = {0, 0, 0}, incl[3];
+		if (r < w.n_reads) {
+			if (have_tail) { val[0] = w.n_u[r]; val[1] = w.n_v[r]; }
+			val[2] = w.new_i[r];
+		}
+#pragma unroll
+		for (int q = 0; q < 3; ++q) {
+			long long x = val[q];
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, x, d); if (lane >= d) x += o; }
+			incl[q] = x;
+			if (lane == 31) s_part[q][wid] = x;
+		}
+		__syncthreads();
+		if (wid == 0) {
+#pragma unroll
+			for (int q = 0; q < 3; ++q) {
+				long long x = s_part[q][lane];
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, x, d); if (lane >= d) x += o; }
+				s_part[q][lane] = x;   // inclusive over warps
+			}
+		}
+		__syncthreads();
+		long long ex[3];
+#pragma unroll
+		for (int q = 0; q < 3; ++q) ex[q] = s_carry[q] + (wid ? s_part[q][wid - 1] : 0) + incl[q] - val[q];
+		if (r < w.n_reads) { w.u_off[r] = ex[0]; w.b_off[r] = ex[1]; w.rec_off[r] = ex[2]; }
+		__syncthreads();
+		if (tid < 3) s_carry[tid] += s_part[tid][31];
+		__syncthreads();
+	}
+	if (tid == 0) {
+		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
+		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS]; w.totals[3] = s_carry[2];
+	}
+}
+
+// chain.c:187-192,205-213: write the final packed u[] and b[]
+__global__ void __launch_bounds__(TAIL_T) k_gather(Workspace w)
+{
+	const int tid = threadIdx.x;
+	for (int r = blockIdx.x; r < w.n_reads; r += gridDim.x) {
+		const int n_u = w.n_u[r];
+		if (n_u == 0) continue;
+		const int base = (int)w.offs[r];
+		const long long ub = w.u_off[r], bb = w.b_off[r];
+		const new_seed *rec = w.rec + base;
+		const int32_t *members = w.members + base;
+		for (int i = 0; i < n_u; ++i) {
+			const int src = w.order[base + i];
+			const uint64_t cu = w.chain_u[base + src];
+			const int cnt = (int)(uint32_t)cu, vo = w.voff[base + src], oo = w.ooff[base + i];
+			if (tid == 0) w.u_out[ub + i] = cu;
+			for (int k = tid; k < cnt; k += TAIL_T) {
+				const new_seed *s = &rec[members[vo + cnt - 1 - k]];
+				w.b_out[bb + oo + k] = make_ulonglong2(s->seed.x, s->seed.y);
+			}
+		}
+	}
+}
+
+// fill_batch: pack the per-read record arrays (chain.c:324-326 surface)
+__global__ void __launch_bounds__(TAIL_T) k_pack_records(Workspace w)
+{
+	const int tid = threadIdx.x;
+	for (int r = blockIdx.x; r < w.n_reads; r += gridDim.x) {
+		const int m = (int)w.new_i[r];
+		const unsigned long long *src = reinterpret_cast<const unsigned long long*>(w.rec + w.offs[r]);
+		unsigned long long *dst = reinterpret_cast<unsigned long long*>(w.rec_out + w.rec_off[r]);
+		for (int k = tid; k < 3 * m; k += TAIL_T) dst[k] = src[k];
+	}
+}
+
+// debug: convert p[] from batch-wide to per-read indices (what the reference's p[] holds, chain.c:89)
+__global__ void __launch_bounds__(256) k_localize_p(Workspace w)
+{
+	const int lane = threadIdx.x & 31;
+	const int gw = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+	const int nw = (int)((gridDim.x * (unsigned)blockDim.x) >> 5);
+	for (int r = gw; r < w.n_reads; r += nw) {
+		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
+		for (int i = b + lane; i < e; i += 32) { const int pi = w.p[i]; if (pi >= 0) w.p[i] = pi - b; }
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------------------
+static inline int blocks_for(long long items, int per_block, int cap)
+{
+	long long b = (items + per_block - 1) / per_block;
+	if (b < 1) b = 1;
+	if (b > cap) b = cap;
+	return (int)b;
+}
+
+void query_launch_cfg(LaunchCfg *cfg)
+{
+	int dev = 0, sms = 148, occ = 0;
+	cudaGetDevice(&dev);
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+	cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill<false>, 128, 0);
+	if (occ < 1) occ = 1;
+	cfg->sm_count = sms;
+	cfg->fill_blocks_per_sm = occ;
+}
+
+int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
+{
+	cudaMemsetAsync(w.counters, 0, CNT_N * sizeof(int32_t), s);
+	k_prep<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.max_dist_x);
+	return 1;
+}
+
+int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg &cfg, bool host_generic, cudaStream_t s)
+{
+	const int grid = cfg.sm_count * cfg.fill_blocks_per_sm;
+	int n = 0;
+	// Both variants are enqueued unless the host already knows the generic one is needed; the one that does not
+	// match the device-side segment flag returns immediately.
+	if (!host_generic) { k_fill<false><<<grid, 128, 0, s>>>(w, prm); ++n; }
+	k_fill<true><<<grid, 128, 0, s>>>(w, prm); ++n;
+	return n;
+}
+
+int launch_compact(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
+{
+	cudaMemsetAsync(w.t, 0x7f, (size_t)w.n_anchors * sizeof(int32_t), s);
+	k_first_ref<<<blocks_for(w.n_anchors, 256 * 4, 148 * 16), 256, 0, s>>>(w);
+	k_compact<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.min_sc);
+	return 2;
+}
+
+int launch_split_records(const Workspace &w, cudaStream_t s)
+{
+	k_split_records<<<blocks_for(w.n_anchors > w.n_reads ? w.n_anchors : w.n_reads, 256 * 4, 148 * 16), 256, 0, s>>>(w);
+	return 1;
+}
+
+int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
+{
+	k_tail<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w, prm.min_cnt, prm.min_sc);
+	k_scan_reads<<<1, 1024, 0, s>>>(w, 1);
+	return 2;
+}
+
+int launch_gather(const Workspace &w, cudaStream_t s)
+{
+	k_gather<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w);
+	return 1;
+}
+
+int launch_pack_records(const Workspace &w, cudaStream_t s)
+{
+	k_scan_reads<<<1, 1024, 0, s>>>(w, 0);
+	k_pack_records<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w);
+	return 2;
+}
+
+int launch_localize_p(const Workspace &w, cudaStream_t s)
+{
+	k_localize_p<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w);
+	return 1;
+}
+
+} // namespace mm2b200

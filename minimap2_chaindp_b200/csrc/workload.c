@@ -1,0 +1,145 @@
+/*
+ * workload.c -- deterministic synthetic anchor generator "G-anc" (SURVEY.md section 8d).
+ *
+ * Produces, for each synthetic read, the sorted mm128_t anchor array that the reference's collect_seed_hits
+ * (map.c:187-236) would hand to mm_chain_dp: x = strand<<63 | rid<<32 | rpos, y = q_span<<32 | qpos
+ * (map.c:217-229), sorted ascending by x (map.c:233).  One independent PRNG stream per read:
+ * seed = splitmix64(base_seed) ^ read_id, so any subset of reads can be regenerated on any rank.
+ *
+ * Host-only C (no CUDA); built into libmm2workload.so by __graft_entry__.build().
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef struct { uint64_t x, y; } wl_anchor_t;
+
+typedef struct {
+	uint64_t seed;          /* base seed (config id folded in by the caller) */
+	int32_t read_len;       /* L: query length in bases */
+	int32_t gap_max;        /* w: minimizer gaps ~ U{1..w} */
+	double  p_survive;      /* probability a minimizer still matches: (1-e)^k */
+	double  p_drift;        /* probability the diagonal drifts by +-1..3 at a minimizer (indels) */
+	int32_t span_lo, span_hi; /* q_span ~ U{span_lo..span_hi} */
+	int32_t n_contigs;      /* R reference sequences */
+	int32_t contig_len;     /* length of each */
+	double  p_background;   /* per minimizer: probability of a burst of random hits */
+	double  bg_mean;        /* mean burst size (geometric) */
+	double  p_repeat;       /* per minimizer: probability of a near-diagonal local repeat hit */
+	int32_t repeat_radius;  /* +- bp around the true locus */
+	int32_t repeat_band;    /* +- bp off the diagonal */
+	int32_t n_loci;         /* >1: ava mode -- the read overlaps this many (target,strand) loci on average */
+	int32_t reserved;
+} wl_spec_t;
+
+static inline uint64_t splitmix64(uint64_t *s)
+{
+	uint64_t z = (*s += 0x9E3779B97F4A7C15ULL);
+	z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+	z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+	return z ^ (z >> 31);
+}
+static inline double u01(uint64_t *s) { return (double)(splitmix64(s) >> 11) * (1.0 / 9007199254740992.0); }
+static inline uint32_t below(uint64_t *s, uint32_t n) { return n ? (uint32_t)(((splitmix64(s) >> 32) * (uint64_t)n) >> 32) : 0; }
+
+static int cmp_x(const void *pa, const void *pb)
+{
+	const wl_anchor_t *a = (const wl_anchor_t*)pa, *b = (const wl_anchor_t*)pb;
+	if (a->x != b->x) return a->x < b->x ? -1 : 1;
+	return a->y < b->y ? -1 : a->y > b->y;
+}
+
+static inline void emit(wl_anchor_t *out, int64_t *k, uint32_t strand, uint32_t rid, uint32_t rpos, int32_t span, int32_t qpos)
+{
+	if (out) {
+		out[*k].x = (uint64_t)strand << 63 | (uint64_t)rid << 32 | rpos;
+		out[*k].y = (uint64_t)(uint32_t)span << 32 | (uint32_t)qpos;
+	}
+	++*k;
+}
+
+/* one colinear locus: query interval [q0,q1) laid on (strand, rid) starting at reference position r0 */
+static void gen_locus(const wl_spec_t *sp, uint64_t *rng, wl_anchor_t *out, int64_t *k,
+                      uint32_t strand, uint32_t rid, int64_t r0, int32_t q0, int32_t q1)
+{
+	int32_t q = q0;
+	int64_t diag = r0 - q0;
+	while (1) {
+		int32_t span = sp->span_lo + (int32_t)below(rng, (uint32_t)(sp->span_hi - sp->span_lo + 1));
+		q += 1 + (int32_t)below(rng, (uint32_t)sp->gap_max);
+		if (q >= q1) break;
+		if (u01(rng) < sp->p_drift) {
+			int32_t d = 1 + (int32_t)below(rng, 3);
+			diag += (splitmix64(rng) & 1) ? d : -d;
+		}
+		if (u01(rng) < sp->p_survive) {
+			int64_t r = diag + q;
+			if (r >= 0 && r < sp->contig_len) emit(out, k, strand, rid, (uint32_t)r, span, q);
+		}
+		if (u01(rng) < sp->p_background) {           /* burst of unrelated hits (repeat k-mers elsewhere) */
+			double p = 1.0 / (sp->bg_mean > 1.0 ? sp->bg_mean : 1.0);
+			do {
+				emit(out, k, (uint32_t)(splitmix64(rng) & 1), below(rng, (uint32_t)sp->n_contigs),
+				     below(rng, (uint32_t)sp->contig_len), span, q);
+			} while (u01(rng) >= p);
+		}
+		if (u01(rng) < sp->p_repeat) {               /* local repeat: lands inside windows, exercises the skip logic */
+			int64_t dq = (int64_t)below(rng, 2u * (uint32_t)sp->repeat_radius + 1) - sp->repeat_radius;
+			int64_t off = (int64_t)below(rng, 2u * (uint32_t)sp->repeat_band + 1) - sp->repeat_band;
+			int64_t r = diag + q + dq + off;
+			if (r >= 0 && r < sp->contig_len) emit(out, k, strand, rid, (uint32_t)r, span, q);
+		}
+	}
+}
+
+static int64_t gen_read(const wl_spec_t *sp, int64_t read_id, wl_anchor_t *out)
+{
+	uint64_t s0 = sp->seed, rng;
+	int64_t k = 0;
+	rng = splitmix64(&s0) ^ (uint64_t)read_id;
+	splitmix64(&rng);
+	if (sp->n_loci <= 1) {
+		uint32_t strand = (uint32_t)(splitmix64(&rng) & 1), rid = below(&rng, (uint32_t)sp->n_contigs);
+		int64_t room = (int64_t)sp->contig_len - sp->read_len;
+		int64_t r0 = room > 0 ? (int64_t)below(&rng, (uint32_t)room) : 0;
+		gen_locus(sp, &rng, out, &k, strand, rid, r0, 0, sp->read_len);
+	} else {
+		/* ava: Poisson-ish number of overlapping targets (uniform in [n/2, 3n/2]); each overlap covers a
+		 * prefix or suffix of the query of random length, on a random target at a random offset */
+		int32_t n = sp->n_loci / 2 + (int32_t)below(&rng, (uint32_t)sp->n_loci + 1), l;
+		for (l = 0; l < n; ++l) {
+			uint32_t strand = (uint32_t)(splitmix64(&rng) & 1), rid = below(&rng, (uint32_t)sp->n_contigs);
+			int32_t ov = 1 + (int32_t)below(&rng, (uint32_t)sp->read_len);
+			int head = (int)(splitmix64(&rng) & 1);
+			int32_t q0 = head ? 0 : sp->read_len - ov, q1 = head ? ov : sp->read_len;
+			int64_t r0 = head ? (int64_t)sp->contig_len - ov : 0;
+			if (r0 < 0) r0 = 0;
+			gen_locus(sp, &rng, out, &k, strand, rid, r0, q0, q1);
+		}
+	}
+	if (out && k > 1) qsort(out, (size_t)k, sizeof(wl_anchor_t), cmp_x);
+	return k;
+}
+
+/* pass 1: offs[0..n_reads] for reads [first, first+n_reads).  Returns total anchors. */
+int64_t wl_count(const wl_spec_t *sp, int64_t first, int64_t n_reads, int64_t *offs)
+{
+	int64_t r, tot = 0;
+#pragma omp parallel for schedule(dynamic, 64)
+	for (r = 0; r < n_reads; ++r) offs[r + 1] = gen_read(sp, first + r, 0);
+	offs[0] = 0;
+	for (r = 0; r < n_reads; ++r) { tot += offs[r + 1]; offs[r + 1] = tot; }
+	return tot;
+}
+
+/* pass 2: fill a[offs[r]..offs[r+1]) for every read (same streams as pass 1) */
+void wl_fill(const wl_spec_t *sp, int64_t first, int64_t n_reads, const int64_t *offs, wl_anchor_t *a)
+{
+	int64_t r;
+#pragma omp parallel for schedule(dynamic, 64)
+	for (r = 0; r < n_reads; ++r) gen_read(sp, first + r, a + offs[r]);
+}

@@ -1,0 +1,113 @@
+"""Synthetic anchor workloads "G-anc" for the BASELINE.json configs.
+
+ctypes wrapper over ``libmm2workload.so`` (csrc/workload.c).  One deterministic PRNG stream per read, so a rank
+can generate exactly its own shard: ``generate(spec, first, n_reads)``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, replace
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+WL_PATH = os.path.join(PKG, "libmm2workload.so")
+
+
+class _Spec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("read_len", C.c_int32), ("gap_max", C.c_int32), ("p_survive", C.c_double),
+                ("p_drift", C.c_double), ("span_lo", C.c_int32), ("span_hi", C.c_int32), ("n_contigs", C.c_int32),
+                ("contig_len", C.c_int32), ("p_background", C.c_double), ("bg_mean", C.c_double),
+                ("p_repeat", C.c_double), ("repeat_radius", C.c_int32), ("repeat_band", C.c_int32),
+                ("n_loci", C.c_int32), ("reserved", C.c_int32)]
+
+
+@dataclass(frozen=True)
+class WorkloadSpec:
+    name: str
+    preset: str            # DP parameter preset (api.PRESETS)
+    n_reads: int
+    seed: int
+    read_len: int
+    gap_max: int
+    p_survive: float
+    p_drift: float
+    span_lo: int
+    span_hi: int
+    n_contigs: int
+    contig_len: int
+    p_background: float = 0.05
+    bg_mean: float = 4.0
+    p_repeat: float = 0.02
+    repeat_radius: int = 2000
+    repeat_band: int = 500
+    n_loci: int = 1
+
+    def c_spec(self) -> _Spec:
+        return _Spec(self.seed, self.read_len, self.gap_max, self.p_survive, self.p_drift, self.span_lo, self.span_hi,
+                     self.n_contigs, self.contig_len, self.p_background, self.bg_mean, self.p_repeat,
+                     self.repeat_radius, self.repeat_band, self.n_loci, 0)
+
+    def scaled(self, n_reads: int) -> "WorkloadSpec":
+        return replace(self, n_reads=int(n_reads))
+
+
+_SEED = 0x5EED0000
+
+# BASELINE.json configs[1..4] (configs[0] is the MT-human/MT-orang fixture under tests/golden/)
+CONFIGS = {
+    # map-ont: 100k synthetic 10 kb Nanopore-like reads (~10 % error) vs 100 x 1 Mb contigs; k=15, w=10
+    "map-ont-100k": WorkloadSpec("map-ont-100k", "map-ont", 100_000, _SEED + 2, 10_000, 10, 0.9 ** 15, 0.10 / 3,
+                                 15, 15, 100, 1_000_000),
+    # ava-ont: 50k x 10 kb reads, ~50 overlapping (target,strand) loci per query; k=15, w=5, both reads noisy
+    "ava-ont-50k": WorkloadSpec("ava-ont-50k", "ava-ont", 50_000, _SEED + 3, 10_000, 5, 0.12, 0.20 / 3,
+                                15, 15, 50_000, 10_000, p_background=0.01, n_loci=50),
+    # map-pb ultra-long: 20k x 100 kb reads, HPC spans 19..40, dense (n >= 50k anchors per read)
+    "map-pb-ul-20k": WorkloadSpec("map-pb-ul-20k", "map-pb", 20_000, _SEED + 4, 100_000, 3, 0.80, 0.15 / 3,
+                                  19, 40, 100, 2_000_000, p_background=0.05, p_repeat=0.10),
+    # asm5: 50 Mb contigs at 1 % divergence; k=19, w=19 -> one serial run of ~4 M anchors per contig
+    "asm5-50mb": WorkloadSpec("asm5-50mb", "asm5", 8, _SEED + 5, 50_000_000, 19, 0.99 ** 19, 0.01 / 3,
+                              19, 19, 8, 60_000_000, p_background=0.002, p_repeat=0.002),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(WL_PATH):
+            from . import build
+            build.build_workload()
+        L = C.CDLL(WL_PATH)
+        L.wl_count.restype = C.c_int64
+        L.wl_count.argtypes = [C.POINTER(_Spec), C.c_int64, C.c_int64, C.c_void_p]
+        L.wl_fill.restype = None
+        L.wl_fill.argtypes = [C.POINTER(_Spec), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def count(spec: WorkloadSpec, first: int = 0, n_reads: int | None = None) -> np.ndarray:
+    """offs[n_reads+1] for reads [first, first+n_reads)."""
+    n_reads = spec.n_reads - first if n_reads is None else n_reads
+    offs = np.zeros(n_reads + 1, dtype=np.int64)
+    cs = spec.c_spec()
+    lib().wl_count(C.byref(cs), first, n_reads, offs.ctypes.data)
+    return offs
+
+
+def fill(spec: WorkloadSpec, offs: np.ndarray, out: np.ndarray, first: int = 0) -> None:
+    """Write the anchors of reads [first, first+len(offs)-1) into out[(offs[-1], 2) uint64] (may be pinned)."""
+    assert out.dtype == np.uint64 and out.flags.c_contiguous and out.size >= 2 * int(offs[-1])
+    cs = spec.c_spec()
+    lib().wl_fill(C.byref(cs), first, offs.shape[0] - 1, offs.ctypes.data, out.ctypes.data)
+
+
+def generate(spec: WorkloadSpec, first: int = 0, n_reads: int | None = None):
+    """-> (offs[n_reads+1] int64, anchors[(n, 2)] uint64)."""
+    offs = count(spec, first, n_reads)
+    a = np.zeros((int(offs[-1]), 2), dtype=np.uint64)
+    fill(spec, offs, a, first)
+    return offs, a

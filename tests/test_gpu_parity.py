@@ -1,0 +1,164 @@
+"""Parity of the CUDA path against the oracle, through the C ABI (bit-exact: integer/index work)."""
+import numpy as np
+import pytest
+
+import oracle
+from minimap2_chaindp_b200 import api, workload
+from util import assert_same, concat_reads, many_chain_reads, random_colinear, random_dense
+
+pytestmark = pytest.mark.gpu
+
+
+def _both(ctx, preset, offs, a, **over):
+    got = ctx.chain_batch(api.params(preset, **over), offs, a)
+    want = oracle.chain_batch(oracle.params(preset, **over), offs, a)
+    return got, want
+
+
+def test_fill_arrays_match_oracle(ctx):
+    """f[], p[], v[] and the new_seed records (the fork's device/host boundary, chain.c:218-327)."""
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 0, 300)
+    prm = api.params(spec.preset)
+    rec_off, rec, f, p, v = ctx.fill_batch(prm, offs, a, want_fpv=True)
+    oprm = oracle.params(spec.preset)
+    for r in range(offs.shape[0] - 1):
+        ar = a[offs[r]:offs[r + 1]]
+        o = oracle.fill(oprm, ar)
+        s = slice(offs[r], offs[r + 1])
+        assert np.array_equal(f[s], o.f), f"read {r}: f differs"
+        assert np.array_equal(p[s], o.p), f"read {r}: p differs"
+        assert np.array_equal(v[s], o.v), f"read {r}: v differs"
+        orec, _ = oracle.compact(oprm.min_sc, ar, o.f, o.p, o.v)
+        got = rec[rec_off[r]:rec_off[r + 1]]
+        assert got.shape == orec.shape and np.array_equal(got, orec), f"read {r}: new_seed records differ"
+
+
+@pytest.mark.parametrize("name,n_reads", [("map-ont-100k", 3000), ("ava-ont-50k", 150), ("map-pb-ul-20k", 12)])
+def test_configs_sample(ctx, name, n_reads):
+    spec = workload.CONFIGS[name]
+    offs, a = workload.generate(spec, 0, n_reads)
+    got, want = _both(ctx, spec.preset, offs, a)
+    assert_same(got, want, name)
+    assert got.n_units > 0
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_adversarial_dense(ctx, seed):
+    """Tiny coordinate space: ties everywhere, dr == 0, dq <= 0, many equal scores, many short chains."""
+    rng = np.random.default_rng(1000 + seed)
+    reads = [random_dense(rng, int(n)) for n in rng.integers(0, 400, 200)]
+    offs, a = concat_reads(reads)
+    for over in (dict(), dict(min_cnt=1, min_sc=0), dict(max_skip=0), dict(max_skip=3, bw=50), dict(max_dist_x=200, max_dist_y=150)):
+        got, want = _both(ctx, "map-ont", offs, a, **over)
+        assert_same(got, want, f"dense seed {seed} {over}")
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_deep_windows(ctx, seed):
+    """Noisy diagonals with repeats: windows of hundreds of predecessors, the skip/break logic across chunks."""
+    rng = np.random.default_rng(2000 + seed)
+    reads = [random_colinear(rng, int(n), noise=float(rng.random()) * 0.6, step=int(rng.integers(1, 12)))
+             for n in rng.integers(2, 3000, 40)]
+    offs, a = concat_reads(reads)
+    for over in (dict(), dict(max_skip=5), dict(max_skip=100), dict(n_segs=5000), dict(max_iter=50), dict(bw=2000)):
+        got, want = _both(ctx, "map-ont", offs, a, **over)
+        assert_same(got, want, f"deep seed {seed} {over}")
+
+
+def test_generic_path_cdna_and_segments(ctx):
+    """is_cdna and multi-segment anchors take the generic kernel (chain.c:71-77)."""
+    rng = np.random.default_rng(3000)
+    reads = [random_dense(rng, int(n), segs=2) for n in rng.integers(0, 300, 100)]
+    offs, a = concat_reads(reads)
+    for preset, over in (("sr", dict()), ("splice", dict()), ("map-ont", dict(n_segs=2)), ("splice", dict(bw=300))):
+        got, want = _both(ctx, preset, offs, a, **over)
+        assert_same(got, want, f"generic {preset} {over}")
+    reads = [random_colinear(rng, 500, noise=0.3) for _ in range(20)]
+    offs, a = concat_reads(reads)
+    got, want = _both(ctx, "splice", offs, a)
+    assert_same(got, want, "splice colinear")
+
+
+def test_empty_and_tiny(ctx):
+    rng = np.random.default_rng(7)
+    reads = [np.zeros((0, 2), np.uint64), random_dense(rng, 1), np.zeros((0, 2), np.uint64), random_dense(rng, 2),
+             random_colinear(rng, 3), np.zeros((0, 2), np.uint64)]
+    offs, a = concat_reads(reads)
+    got, want = _both(ctx, "map-ont", offs, a, min_cnt=1, min_sc=0)
+    assert_same(got, want, "tiny")
+    got = ctx.chain_batch(api.params("map-ont"), np.zeros(1, np.int64), np.zeros((0, 2), np.uint64))
+    assert got.n_u.shape[0] == 0 and got.u.shape[0] == 0
+
+
+def test_many_chains_unstable_order(ctx):
+    """> 64 kept chains with equal first-anchor x: the x-order must replay ksort's unstable radix sort."""
+    reads = many_chain_reads(np.random.default_rng(11))
+    offs, a = concat_reads(reads)
+    got, want = _both(ctx, "map-ont", offs, a, min_sc=10, min_cnt=2)
+    assert int(want.n_u.max()) > 64
+    assert_same(got, want, "many chains")
+
+
+def test_sub_batching_is_invisible():
+    """Small slots force many sub-batches and slot reuse; results must not depend on the split."""
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 100, 1200)
+    want = oracle.chain_batch(oracle.params(spec.preset), offs, a)
+    for slots, cap in ((1, 20000), (2, 50000), (3, 7000)):
+        with api.ChainContext(device=0, n_slots=slots, slot_anchors=cap) as c:
+            got = c.chain_batch(api.params(spec.preset), offs, a)
+            assert got.n_sub_batches > 3
+            assert_same(got, want, f"slots={slots} cap={cap}")
+            got = c.chain_batch(api.params(spec.preset), offs, a)      # arena reuse
+            assert_same(got, want, f"slots={slots} cap={cap} (second call)")
+
+
+def test_pinned_input_path(ctx):
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs = workload.count(spec, 5000, 500)
+    pa = api.PinnedArray((int(offs[-1]), 2), np.uint64)
+    workload.fill(spec, offs, pa.array, 5000)
+    got = ctx.chain_batch(api.params(spec.preset), offs, pa.array)
+    want = oracle.chain_batch(oracle.params(spec.preset), offs, pa.array.copy())
+    assert_same(got, want, "pinned")
+    pa.free()
+
+
+def test_reference_entry_points(ctx):
+    """mm_chain_dp / mm_chain_dp_fpga / mm_chain_dp_bottom symbols with the reference's calling convention."""
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 42, 8)
+    prm, oprm = api.params(spec.preset), oracle.params(spec.preset)
+    for r in range(8):
+        ar = a[offs[r]:offs[r + 1]]
+        wu, wb = oracle.chain_dp(oprm, ar)
+        u, b = api.mm_chain_dp(prm, ar)
+        assert np.array_equal(u, wu) and np.array_equal(b, wb)
+        rec = api.mm_chain_dp_fpga(prm, ar)
+        o = oracle.fill(oprm, ar)
+        orec, _ = oracle.compact(oprm.min_sc, ar, o.f, o.p, o.v)
+        assert np.array_equal(rec, orec)
+        u2, b2 = api.mm_chain_dp_bottom(prm, rec)
+        assert np.array_equal(u2, wu) and np.array_equal(b2, wb)
+    u, b = api.mm_chain_dp(prm, np.zeros((0, 2), np.uint64))        # n == 0 (test/t2.fa, q2.fa)
+    assert u.shape[0] == 0 and b.shape[0] == 0
+
+
+def test_concurrent_callers_are_batched(ctx):
+    """Many host threads calling mm_chain_dp at once (kt_for workers): every caller gets its own read's answer."""
+    import threading
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 7000, 64)
+    prm, oprm = api.params(spec.preset), oracle.params(spec.preset)
+    out = [None] * 64
+
+    def work(r):
+        out[r] = api.mm_chain_dp(prm, a[offs[r]:offs[r + 1]])
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(64)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for r in range(64):
+        wu, wb = oracle.chain_dp(oprm, a[offs[r]:offs[r + 1]])
+        assert np.array_equal(out[r][0], wu) and np.array_equal(out[r][1], wb), f"read {r}"
