@@ -78,7 +78,8 @@ typedef struct {
 	int32_t n_slots;             /* in-flight sub-batches (streams) for H2D / compute / D2H overlap; 0 = default (3) */
 	int64_t slot_anchors;        /* anchors per sub-batch; 0 = default (8 Mi).  A longer read grows its slot. */
 	int32_t profile;             /* 1: record CUDA events around every kernel (see mm2b200_stage_ms) */
-	int32_t reserved;
+	int32_t count_visited;       /* 1: the fill kernel also counts the (i,j) pairs the reference loop visits
+	                                (mm2b200_result_t.n_visited, the throughput metric's numerator); off by default */
 } mm2b200_config_t;
 
 int  mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **ctx);
@@ -106,6 +107,7 @@ typedef struct {
 	const mm128_t  *b;       /* [b_off[n_reads]] */
 	int64_t n_units;         /* independent anchor runs (len >= 2) the fill kernel processed */
 	int64_t n_sub_batches;
+	int64_t n_visited;       /* (i,j) pairs the reference loop visits (bodies of chain.c:59-88); needs cfg.count_visited */
 } mm2b200_result_t;
 
 /* mm_chain_dp over n_reads reads: read r owns a[offs[r] .. offs[r+1]) (each sorted by x, map.c:233).
@@ -138,7 +140,7 @@ typedef struct {
 	const int64_t  *d_b_off;  /* [n_reads+1] */
 	const uint64_t *d_u;
 	const mm128_t  *d_b;
-	const int64_t  *d_totals; /* [4] */
+	const int64_t  *d_totals; /* [8]: [0..2] as above, [3] = sum new_i, [4] = visited (i,j) pairs */
 } mm2b200_dev_result_t;
 
 /* Whole path on anchors already resident in HBM: d_a[n_anchors] and d_offs[n_reads+1] are device pointers.
@@ -154,6 +156,10 @@ int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx);
  * stage since the last reset.  Stage names: "prep", "fill", "compact", "tail", "gather". */
 int  mm2b200_stage_ms(mm2b200_ctx_t *ctx, const char *stage, double *ms, int64_t *launches);
 void mm2b200_stage_reset(mm2b200_ctx_t *ctx);
+
+/* Measured integer-issue peak of the device (lane-ops/s): the roofline denominator for the predecessor scan.
+ * mode 0 = ALU-pipe only (add/xor), mode 1 = ALU + FMA-pipe integer ops interleaved (the issue-port ceiling). */
+int mm2b200_int_peak(mm2b200_ctx_t *ctx, int mode, double *lane_ops_per_s);
 
 const char *mm2b200_version(void);
 

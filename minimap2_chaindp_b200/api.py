@@ -33,7 +33,8 @@ EXPORTED_SYMBOLS = (
     "mm2b200_create", "mm2b200_destroy", "mm2b200_last_error", "mm2b200_device_count",
     "mm2b200_pinned_alloc", "mm2b200_pinned_free",
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
-    "mm2b200_chain_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_version",
+    "mm2b200_chain_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
+    "mm2b200_version",
 )
 
 
@@ -70,12 +71,13 @@ def params(preset: str = "map-ont", **over) -> Params:
 
 class _Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("n_slots", C.c_int32), ("slot_anchors", C.c_int64),
-                ("profile", C.c_int32), ("reserved", C.c_int32)]
+                ("profile", C.c_int32), ("count_visited", C.c_int32)]
 
 
 class _Result(C.Structure):
     _fields_ = [("n_reads", C.c_int64), ("n_u", C.c_void_p), ("u_off", C.c_void_p), ("b_off", C.c_void_p),
-                ("u", C.c_void_p), ("b", C.c_void_p), ("n_units", C.c_int64), ("n_sub_batches", C.c_int64)]
+                ("u", C.c_void_p), ("b", C.c_void_p), ("n_units", C.c_int64), ("n_sub_batches", C.c_int64),
+                ("n_visited", C.c_int64)]
 
 
 class _Records(C.Structure):
@@ -119,6 +121,7 @@ def lib() -> C.CDLL:
         L.mm2b200_stage_ms.argtypes = [vp, C.c_char_p, C.POINTER(C.c_double), C.POINTER(i64)]
         L.mm2b200_stage_reset.argtypes = [vp]
         L.mm2b200_stage_reset.restype = None
+        L.mm2b200_int_peak.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
         # reference entry points
         L.mm_chain_dp.restype = vp
         L.mm_chain_dp.argtypes = [C.c_int] * 8 + [i64, vp, C.POINTER(C.c_int), C.POINTER(vp), vp]
@@ -166,6 +169,7 @@ class BatchResult:
     b: np.ndarray
     n_units: int = 0
     n_sub_batches: int = 0
+    n_visited: int = 0
 
     def read(self, r: int):
         return self.u[self.u_off[r]:self.u_off[r + 1]], self.b[self.b_off[r]:self.b_off[r + 1]]
@@ -201,9 +205,11 @@ class PinnedArray:
 class ChainContext:
     """mm2b200_ctx_t: one device, its streams, workspaces and pinned result arenas."""
 
-    def __init__(self, device: int = 0, n_slots: int = 0, slot_anchors: int = 0, profile: bool = False):
+    def __init__(self, device: int = 0, n_slots: int = 0, slot_anchors: int = 0, profile: bool = False,
+                 count_visited: bool = False):
         self._h = C.c_void_p()
-        cfg = _Config(device=device, n_slots=n_slots, slot_anchors=slot_anchors, profile=int(profile), reserved=0)
+        cfg = _Config(device=device, n_slots=n_slots, slot_anchors=slot_anchors, profile=int(profile),
+                      count_visited=int(count_visited))
         _check(lib().mm2b200_create(C.byref(cfg), C.byref(self._h)))
         self.device = device
 
@@ -247,7 +253,7 @@ class ChainContext:
             u_off, b_off = np.zeros(1, np.int64), np.zeros(1, np.int64)
         return BatchResult(_view(res.n_u, nr, np.int32), u_off, b_off,
                            _view(res.u, int(u_off[-1]), np.uint64), _view(res.b, int(b_off[-1]), np.uint64, (2,)),
-                           int(res.n_units), int(res.n_sub_batches))
+                           int(res.n_units), int(res.n_sub_batches), int(res.n_visited))
 
     def fill_batch(self, prm: Params, offs, a, want_fpv: bool = False):
         """mm_chain_dp_fpga (chain.c:218) over a batch -> (rec_off, records[, f, p, v])."""
@@ -297,6 +303,12 @@ class ChainContext:
 
     def stage_reset(self):
         lib().mm2b200_stage_reset(self._h)
+
+    def int_peak(self, mode: int = 1) -> float:
+        """Measured integer lane-ops/s of the device (mode 0: ALU pipe only; 1: ALU+FMA-pipe mix)."""
+        v = C.c_double()
+        _check(lib().mm2b200_int_peak(self._h, mode, C.byref(v)))
+        return v.value
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -117,15 +117,15 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 	void *pa = nullptr, *poffs = nullptr;
 	Item items[] = {
 		{ &pa, 16 * A }, { &poffs, 8 * (R + 1) },
-		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N },
-		{ (void**)&w.f, 4 * A }, { (void**)&w.p, 4 * A }, { (void**)&w.v, 4 * A }, { (void**)&w.t, 4 * A },
+		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N }, { (void**)&w.visited, 8 },
+		{ (void**)&w.wrec, 16 * A }, { (void**)&w.f, 4 * A }, { (void**)&w.p, 4 * A }, { (void**)&w.v, 4 * A }, { (void**)&w.t, 4 * A },
 		{ (void**)&w.newid, 4 * A }, { (void**)&w.rec, 24 * A }, { (void**)&w.recp, 4 * A }, { (void**)&w.new_i, 4 * R },
 		{ (void**)&w.succ, A }, { (void**)&w.claimed, A }, { (void**)&w.members, 4 * A },
 		{ (void**)&w.cand, 8 * A }, { (void**)&w.chain_u, 8 * A }, { (void**)&w.wy, 8 * A },
 		{ (void**)&w.voff, 4 * A }, { (void**)&w.order, 4 * A }, { (void**)&w.ooff, 4 * A }, { (void**)&w.stk, 4 * A },
 		{ (void**)&w.n_u, 4 * R }, { (void**)&w.n_v, 4 * R },
 		{ (void**)&w.u_off, 8 * (R + 1) }, { (void**)&w.b_off, 8 * (R + 1) }, { (void**)&w.rec_off, 8 * (R + 1) },
-		{ (void**)&w.totals, 8 * 4 }, { (void**)&w.u_out, 8 * A }, { (void**)&w.b_out, 16 * A },
+		{ (void**)&w.totals, 8 * 8 }, { (void**)&w.u_out, 8 * A }, { (void**)&w.b_out, 16 * A },
 	};
 	size_t total = 0;
 	for (auto &it : items) total += align_up(it.bytes, 256);
@@ -273,6 +273,7 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 		}
 	}
 	query_launch_cfg(&ctx->lc);
+	ctx->lc.count_visited = c.count_visited;
 	*out = ctx;
 	return MM2B200_OK;
 }
@@ -339,7 +340,7 @@ struct BatchJob {
 	bool src_pinned;
 	int32_t *dbg_f, *dbg_p, *dbg_v;   // fill mode only
 	int64_t ubase = 0, bbase = 0;     // running output positions
-	int64_t n_units = 0, n_chunks = 0;
+	int64_t n_units = 0, n_chunks = 0, n_visited = 0;
 };
 
 static bool is_pinned(const void *p)
@@ -357,6 +358,7 @@ static int finish_a(BatchJob &job, Slot &s)
 	const int64_t *tot = s.h_totals.as<int64_t>();
 	const int64_t tu = tot[0], tb = tot[1];
 	job.n_units += tot[2];
+	job.n_visited += tot[4];
 	s.ubase = job.ubase; s.bbase = job.bbase;
 	// (result arenas were reserved to their upper bounds in run_batch, so nothing here can move a buffer that an
 	// earlier chunk's copy is still writing to; per-chunk offset copies cover n_reads entries so chunks never overlap)
@@ -470,11 +472,11 @@ static int run_batch(BatchJob &job)
 			else {
 				StageTimer t(ctx, s.stream, ST_GATHER);
 				int nl = launch_pack_records(w, s.stream);
-				if (job.dbg_p) nl += launch_localize_p(w, s.stream);
+				if (job.dbg_p || job.dbg_f) nl += launch_export_fp(w, s.stream);
 				t.done(nl);
 			}
 		}
-		CUDA_TRY(cudaMemcpyAsync(s.h_totals.ptr, w.totals, 32, cudaMemcpyDeviceToHost, s.stream));
+		CUDA_TRY(cudaMemcpyAsync(s.h_totals.ptr, w.totals, 64, cudaMemcpyDeviceToHost, s.stream));
 		CUDA_TRY(cudaEventRecord(s.ev_totals, s.stream));
 		CUDA_TRY(cudaGetLastError());
 		s.state = 1;
@@ -516,7 +518,7 @@ extern "C" int mm2b200_chain_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *p
 	res->n_reads = n_reads;
 	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
 	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
-	res->n_units = job.n_units; res->n_sub_batches = job.n_chunks;
+	res->n_units = job.n_units; res->n_sub_batches = job.n_chunks; res->n_visited = job.n_visited;
 	return MM2B200_OK;
 }
 
@@ -546,7 +548,7 @@ extern "C" int mm2b200_bottom_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	res->n_reads = n_reads;
 	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
 	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
-	res->n_units = 0; res->n_sub_batches = job.n_chunks;
+	res->n_units = 0; res->n_sub_batches = job.n_chunks; res->n_visited = 0;
 	return MM2B200_OK;
 }
 
@@ -572,6 +574,35 @@ extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	CUDA_TRY(cudaGetLastError());
 	out->d_n_u = w.n_u; out->d_u_off = w.u_off; out->d_b_off = w.b_off;
 	out->d_u = w.u_out; out->d_b = (const mm128_t*)w.b_out; out->d_totals = w.totals;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_int_peak(mm2b200_ctx_t *ctx, int mode, double *lane_ops_per_s)
+{
+	if (!ctx || !lane_ops_per_s) return fail(MM2B200_ERR_ARG, "NULL argument");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	CUDA_TRY(cudaSetDevice(ctx->device));
+	unsigned *d_out = nullptr;
+	CUDA_TRY(cudaMalloc(&d_out, 64));
+	cudaEvent_t e0, e1;
+	CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+	cudaStream_t st = ctx->slots[0].stream;
+	const int grid = ctx->lc.sm_count * 8;      // 8 CTAs x 256 threads = 64 warps per SM
+	launch_int_peak(mode, grid, 256, d_out, st);   // warm-up
+	double best = 0;
+	for (int rep = 0; rep < 5; ++rep) {
+		cudaEventRecord(e0, st);
+		const long long ops = launch_int_peak(mode, grid, 4096, d_out, st);
+		cudaEventRecord(e1, st);
+		CUDA_TRY(cudaEventSynchronize(e1));
+		float ms = 0;
+		cudaEventElapsedTime(&ms, e0, e1);
+		ctx->launches += 1;
+		if (ms > 0 && ops / (ms * 1e-3) > best) best = ops / (ms * 1e-3);
+	}
+	cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out);
+	CUDA_TRY(cudaGetLastError());
+	*lane_ops_per_s = best;
 	return MM2B200_OK;
 }
 

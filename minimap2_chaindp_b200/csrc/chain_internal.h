@@ -28,8 +28,11 @@ struct Workspace {
 	float *avg;               // [n_reads] avg_qspan (chain.c:47)
 	Unit *units;              // [n_anchors/2 + 1]
 	int32_t *counters;        // [CNT_N]
+	unsigned long long *visited; // [1] reference-visited (i,j) pairs (chain.c:59-88 loop bodies) of this sub-batch
 	// fill (chain.c:52-90)
-	int32_t *f, *p, *v;       // [n_anchors]; p is a batch-wide index (or -1)
+	int4 *wrec;               // [n_anchors] working record {low32(x), qpos, f, p}; p is a batch-wide index (or -1)
+	int32_t *v;               // [n_anchors] peak score along the best chain ending here (chain.c:90)
+	int32_t *f, *p;           // [n_anchors] debug export only (fill_batch with f/p/v requested)
 	int32_t *t;               // [n_anchors] marks during the fill, then "first referencer" during compaction
 	// compaction (chain.c:93-122)
 	int32_t *newid;           // [n_anchors] old -> new index within the read, -1 = dropped
@@ -50,7 +53,7 @@ struct Workspace {
 	int32_t *n_v;             // [n_reads]
 	// packed outputs
 	int64_t *u_off, *b_off;   // [n_reads+1]
-	int64_t *totals;          // [4]: sum n_u, sum n_v, n_units, sum new_i
+	int64_t *totals;          // [8]: sum n_u, sum n_v, n_units, sum new_i, visited pairs
 	int64_t *rec_off;         // [n_reads+1] (fill_batch only)
 	uint64_t *u_out;          // [n_anchors]
 	ulonglong2 *b_out;        // [n_anchors]
@@ -59,7 +62,8 @@ struct Workspace {
 
 struct LaunchCfg {
 	int sm_count;
-	int fill_blocks_per_sm;
+	int fill_blocks_per_sm;      // generic kernel
+	int count_visited;           // instrumented fast kernel (metric numerator) instead of the plain one
 };
 
 // launchers (chain_kernels.cu); every launcher returns the number of kernels it enqueued
@@ -70,7 +74,8 @@ int launch_split_records(const Workspace &w, cudaStream_t s);   // bottom_batch:
 int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
 int launch_gather(const Workspace &w, cudaStream_t s);
 int launch_pack_records(const Workspace &w, cudaStream_t s);
-int launch_localize_p(const Workspace &w, cudaStream_t s);      // debug: p[] -> per-read indices
+int launch_export_fp(const Workspace &w, cudaStream_t s);       // debug: wrec -> f[], p[] (per-read indices)
 void query_launch_cfg(LaunchCfg *cfg);
+long long launch_int_peak(int mode, int grid, int iters, unsigned *d_out, cudaStream_t s);
 
 } // namespace mm2b200

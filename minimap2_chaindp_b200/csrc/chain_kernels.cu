@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 			if (valid) {
 				const int span = (int)((ai.y >> 32) & 0xff);
 				sum += (unsigned)span;
-				w.f[i] = span; w.p[i] = -1; w.v[i] = span; w.t[i] = -1;
+				w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1);   // singleton defaults: f = span, p = -1
+				w.v[i] = span; w.t[i] = -1;
 				if ((ai.y >> 48) & 0xff) multiseg = 1;
 			}
 			const unsigned smask = __ballot_sync(FULL, start);
@@ -95,22 +96,46 @@ static __device__ __forceinline__ int lin_cost(int dd, double avg)
 	return __double2int_rz(__dmul_rn(__dmul_rn(__int2double_rn(dd), 0.01), avg));
 }
 
-template <bool GENERIC>
-__global__ void __launch_bounds__(128) k_fill(Workspace w, mm2b200_params_t prm)
+// The sequential state machine of chain.c:80-87 replayed over one chunk's ballot masks.
+//   imp : IMPROVE lanes (strict prefix maxima), mm : MARKED-MISS lanes (never overlap imp)
+// Walks the segments between IMPROVE lanes; returns the break lane (or -1) and updates n_skip.  Warp-uniform.
+static __device__ __forceinline__ int replay_skip(unsigned imp, unsigned mm, int max_skip, int lane, int &n_skip)
 {
-	// the two variants are both launched; the device-side flag decides which one does the work
+	unsigned rem = imp;
+	int pos = 0;
+	for (;;) {
+		const int nxt = rem ? __ffs(rem) - 1 : 32;
+		const unsigned seg = mm & mask_below(nxt) & ~mask_below(pos);
+		const int cnt = __popc(seg);
+		const int need = max(max_skip - n_skip + 1, 1);
+		if (cnt >= need) {   // the need-th MARKED-MISS of this segment breaks (chain.c:84-85)
+			const int c = __popc(seg & (lanemask_lt(lane) | (1u << lane)));
+			const unsigned hit = __ballot_sync(FULL, ((seg >> lane) & 1u) && c == need);
+			return __ffs(hit) - 1;
+		}
+		n_skip += cnt;
+		if (nxt == 32) return -1;
+		if (n_skip > 0) --n_skip;   // chain.c:82
+		rem &= rem - 1;
+		pos = nxt + 1;
+	}
+}
+
+// ---- generic variant: cDNA / multi-segment scoring (chain.c:71-77); everything through global memory --------
+__global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_params_t prm)
+{
+	// both variants are launched; the device-side flag decides which one does the work
 	const bool need_generic = prm.is_cdna || (w.counters[CNT_MULTISEG] != 0);
-	if (need_generic != GENERIC) return;
+	if (!need_generic) return;
 
 	const int lane = threadIdx.x & 31;
 	const int n_units = w.counters[CNT_UNITS];
 	const unsigned mdx = (unsigned)prm.max_dist_x;
-	const int dq_max = prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x;   // same-segment bound (chain.c:64)
-	const unsigned dr_max = (prm.n_segs > 1 && !prm.is_cdna) ? (unsigned)prm.max_dist_y : 0xffffffffu;  // chain.c:67
 	const int max_skip = prm.max_skip, bw = prm.bw;
 	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
 	const ulonglong2 *__restrict__ a = w.a;
-	int32_t *f = w.f, *p = w.p, *v = w.v, *t = w.t;
+	int4 *wrec = w.wrec;
+	int32_t *v = w.v, *t = w.t;
 
 	for (;;) {
 		int u = 0;
@@ -120,6 +145,7 @@ __global__ void __launch_bounds__(128) k_fill(Workspace w, mm2b200_params_t prm)
 		const Unit un = w.units[u];
 		const int s = un.start, e = un.start + un.len;
 		const double avg = (double)w.avg[un.read];
+		long long n_visited = 0;   // loop bodies the reference executes (chain.c:59-88), the metric's numerator
 
 		for (int i = s + 1; i < e; ++i) {
 			const ulonglong2 ai = a[i];
@@ -134,43 +160,34 @@ __global__ void __launch_bounds__(128) k_fill(Workspace w, mm2b200_params_t prm)
 			for (int jb = i - 1; jb >= jlo && !done; jb -= 32) {
 				const int j = jb - lane;
 				const bool valid = j >= jlo;
-				ulonglong2 aj = make_ulonglong2(0ull, 0ull);
-				int fj = 0, pj = -1;
-				if (valid) { aj = a[j]; fj = f[j]; pj = p[j]; }
-				const unsigned dr = xi - (unsigned)aj.x;
+				unsigned long long ajy = 0;
+				int4 rj = make_int4(0, 0, 0, -1);
+				if (valid) { ajy = a[j].y; rj = wrec[j]; }
+				const int fj = rj.z, pj = rj.w;
+				const unsigned dr = xi - (unsigned)rj.x;
 				const unsigned wmask = __ballot_sync(FULL, valid && dr <= mdx);
 				int nwin = 32;
 				if (wmask != FULL) { nwin = __ffs(~wmask) - 1; done = true; }
 				if (nwin == 0) break;
+				n_visited += nwin;
 				const bool act = lane < nwin;
 
 				// ---- pair score (chain.c:60-79) ----
-				const int dq = qi - (int)(unsigned)aj.y;
-				bool skip;
-				int sc;
-				if (!GENERIC) {
-					skip = !act || dr == 0 || dq <= 0 || dq > dq_max || dr > dr_max;
-					const int dd = abs((int)dr - dq);
-					skip = skip || dd > bw;
-					sc = min(min(dq, (int)dr), span);
-					const int log_dd = dd ? 31 - __clz(dd) : 0;
-					sc -= lin_cost(dd, avg) + (log_dd >> 1);
-				} else {
-					const bool same = sidi == (int)((aj.y >> 48) & 0xff);
-					skip = !act || (same && dr == 0) || dq <= 0;
-					skip = skip || (same && dq > prm.max_dist_y) || dq > prm.max_dist_x;
-					const int dd = abs((int)dr - dq);
-					skip = skip || (same && dd > bw);
-					skip = skip || (prm.n_segs > 1 && !prm.is_cdna && same && dr > (unsigned)prm.max_dist_y);
-					sc = min(min(dq, (int)dr), span);
-					const int log_dd = dd ? 31 - __clz(dd) : 0;
-					const int c_lin = lin_cost(dd, avg);
-					if (prm.is_cdna || !same) {
-						if (!same && dr == 0) ++sc;
-						else if ((int)dr > dq || !same) sc -= min(c_lin, log_dd);
-						else sc -= c_lin + (log_dd >> 1);
-					} else sc -= c_lin + (log_dd >> 1);
-				}
+				const int dq = qi - rj.y;
+				const bool same = sidi == (int)((ajy >> 48) & 0xff);
+				bool skip = !act || (same && dr == 0) || dq <= 0;
+				skip = skip || (same && dq > prm.max_dist_y) || dq > prm.max_dist_x;
+				const int dd = abs((int)dr - dq);
+				skip = skip || (same && dd > bw);
+				skip = skip || (prm.n_segs > 1 && !prm.is_cdna && same && dr > (unsigned)prm.max_dist_y);
+				int sc = min(min(dq, (int)dr), span);
+				const int log_dd = dd ? 31 - __clz(dd) : 0;
+				const int c_lin = lin_cost(dd, avg);
+				if (prm.is_cdna || !same) {
+					if (!same && dr == 0) ++sc;
+					else if ((int)dr > dq || !same) sc -= min(c_lin, log_dd);
+					else sc -= c_lin + (log_dd >> 1);
+				} else sc -= c_lin + (log_dd >> 1);
 				sc += fj;
 
 				// ---- marks (chain.c:83,87): publish, synchronise, read ----
@@ -191,45 +208,224 @@ __global__ void __launch_bounds__(128) k_fill(Workspace w, mm2b200_params_t prm)
 				const unsigned imp = __ballot_sync(FULL, improve);
 				const unsigned mm = __ballot_sync(FULL, marked && !improve);
 
-				// ---- replay n_skip (chain.c:82,84) over the masks; find the break lane ----
-				int brk = -1;
-				{
-					unsigned rem = imp;
-					int pos = 0;
-					for (;;) {
-						const int nxt = rem ? __ffs(rem) - 1 : 32;
-						const unsigned seg = mm & mask_below(nxt) & ~mask_below(pos);
-						const int cnt = __popc(seg);
-						const int need = max(max_skip - n_skip + 1, 1);
-						if (cnt >= need) {
-							const int c = __popc(seg & (lanemask_lt(lane) | (1u << lane)));
-							const unsigned hit = __ballot_sync(FULL, ((seg >> lane) & 1u) && c == need);
-							brk = __ffs(hit) - 1;
-							break;
-						}
-						n_skip += cnt;
-						if (nxt == 32) break;
-						if (n_skip > 0) --n_skip;
-						rem &= rem - 1;
-						pos = nxt + 1;
-					}
-				}
+				const int brk = replay_skip(imp, mm, max_skip, lane, n_skip);
 				const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
 				if (impb) {
 					const int L = 31 - __clz(impb);
 					max_f = __shfl_sync(FULL, sc, L);
 					max_j = jb - L;
 				}
-				if (brk >= 0) done = true;
+				if (brk >= 0) { done = true; n_visited -= nwin - (brk + 1); }
 			}
 			if (lane == 0) {
-				f[i] = max_f; p[i] = max_j;
 				int vi = max_f;
 				if (max_j >= 0) { const int vj = v[max_j]; if (vj > max_f) vi = vj; }   // chain.c:90
+				wrec[i] = make_int4((int)xi, qi, max_f, max_j);
 				v[i] = vi;
 			}
 			__syncwarp();
 		}
+		if (lane == 0) atomicAdd(w.visited, (unsigned long long)n_visited);
+	}
+}
+
+// ---- fast variant: single segment, not cDNA (every long-read preset) ------------------------------------------
+//
+// Issue-slot budget is what bounds this kernel (ncu: 3.0 of 4 issue slots/clk busy, HBM < 5 %), so the design
+// minimises instructions per (anchor, 32-predecessor chunk):
+//  * each warp keeps the last 64 anchors of its run in a shared-memory ring of packed records {x, q, f, p} (+ v):
+//    one LDS.128 feeds a lane; chunks deeper than 64 read the same records from global memory (L1/L2);
+//  * the gap cost (int)(dd*.01*avg_qspan) + (ilog2(dd)>>1) of every dd <= bw (chain.c:66 guarantees dd <= bw for
+//    a scored pair) comes from a per-warp shared-memory table built with the reference's double arithmetic and
+//    rebuilt only when avg_qspan changes (TABLE; bw <= 1023);
+//  * marks inside the chunk never touch memory: lane k' contributes bit (jb - p[j']) to a warp OR-reduce
+//    (redux.sync); only marks that land beyond the chunk go through t[] in global memory;
+//  * IMPROVE lanes: one redux.max finds the chunk maximum M and the first lane L that attains it; if no earlier
+//    lane beats the running maximum, L is the only IMPROVE lane (the common case) and no prefix scan is needed.
+#define FILL_WARPS 4
+#define RING 64
+
+template <bool TABLE, bool COUNT>
+__global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
+{
+	extern __shared__ __align__(16) unsigned char smem[];
+	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
+
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	int4 *ring = reinterpret_cast<int4*>(smem) + wib * RING;
+	int *vring = reinterpret_cast<int*>(smem + FILL_WARPS * RING * 16) + wib * RING;
+	unsigned short *tab = reinterpret_cast<unsigned short*>(smem + FILL_WARPS * RING * 20) + wib * tab_entries;
+
+	const int n_units = w.counters[CNT_UNITS];
+	const unsigned mdx = (unsigned)prm.max_dist_x;
+	const unsigned dq_max = (unsigned)(prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x);   // chain.c:64
+	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
+	const int max_skip = prm.max_skip, bw = prm.bw;
+	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
+	const ulonglong2 *__restrict__ a = w.a;
+	int4 *wrec = w.wrec;
+	int32_t *vg = w.v, *t = w.t;
+	unsigned tab_key = 0;
+	bool have_tab = false;
+
+	for (;;) {
+		int u = 0;
+		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
+		u = __shfl_sync(FULL, u, 0);
+		if (u >= n_units) break;
+		const Unit un = w.units[u];
+		const int s = un.start, e = un.start + un.len;
+		const float avgf = w.avg[un.read];
+		const double avg = (double)avgf;
+		long long n_visited = 0;
+
+		if (TABLE && (!have_tab || __float_as_uint(avgf) != tab_key)) {
+			__syncwarp();
+			for (int dd = lane; dd <= bw; dd += 32)
+				tab[dd] = (unsigned short)(lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1));
+			tab_key = __float_as_uint(avgf);
+			have_tab = true;
+		}
+		// seed the ring with the run's first anchor (f = span, p = -1, v = span: chain.c:56,89-90 with no predecessor)
+		ulonglong2 nxt = a[s];
+		if (lane == 0) {
+			const int sp = (int)((nxt.y >> 32) & 0xff);
+			ring[s & (RING - 1)] = make_int4((int)(unsigned)nxt.x, (int)(unsigned)nxt.y, sp, -1);
+			vring[s & (RING - 1)] = sp;
+		}
+		nxt = a[s + 1];
+		__syncwarp();
+
+		for (int i = s + 1; i < e; ++i) {
+			const ulonglong2 ai = nxt;
+			if (i + 1 < e) nxt = a[i + 1];              // prefetch: not needed before the next iteration
+			const unsigned xi = (unsigned)ai.x;
+			const int qi = (int)(unsigned)ai.y;
+			const int span = (int)((ai.y >> 32) & 0xff);
+			int max_f = span, max_j = -1, n_skip = 0, vbest = (int)0x80000000;
+			const int jlo = max(s, i - max_iter);
+			bool done = false;
+
+			for (int jb = i - 1; jb >= jlo && !done; jb -= 32) {
+				const int j = jb - lane;
+				int4 rj;
+				int vj;
+				bool marked_mem = false;
+				if (jb >= i - RING) {                         // the last 64 anchors live in the ring (uniform branch)
+					rj = ring[j & (RING - 1)];
+					vj = vring[j & (RING - 1)];
+					if (jb != i - 1) { __syncwarp(); if (j >= jlo) marked_mem = t[j] == i; }
+				} else {
+					__syncwarp();
+					rj = make_int4(0, 0, 0, -1); vj = 0;
+					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; marked_mem = t[j] == i; }
+				}
+				const unsigned dr = xi - (unsigned)rj.x;
+				const unsigned wmask = __ballot_sync(FULL, j >= jlo && dr <= mdx);
+				int nwin = 32;
+				if (wmask != FULL) {
+					nwin = __ffs(~wmask) - 1;
+					done = true;
+					if (nwin == 0) break;
+				}
+				if (COUNT) n_visited += nwin;
+
+				// ---- pair score (chain.c:60-79, same-segment non-cDNA branch) ----
+				const int dq = qi - rj.y;
+				const int dd = abs((int)dr - dq);
+				// dr == 0 || dr > dr_max  <=>  dr-1 >= dr_max (unsigned);  dq <= 0 || dq > dq_max  <=>  dq-1 >= dq_max (unsigned)
+				const bool skip = lane >= nwin || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
+				int cost;
+				if (TABLE) cost = tab[min(dd, bw)];
+				else cost = lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
+				const int sc = min(min(dq, (int)dr), span) - cost + rj.z;
+
+				// ---- marks (chain.c:83,87) ----
+				const int pj = rj.w;
+				const unsigned kt = (unsigned)(jb - pj);          // lane that scores anchor p[j], if it is in this chunk
+				const bool mk = !skip && pj >= 0;
+				const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << kt) : 0u);
+				const bool far = mk && kt >= 32u;
+				if (__any_sync(FULL, far)) { if (far) t[pj] = i; }
+				const bool marked = ((mloc >> lane) & 1u) || marked_mem;
+
+				// ---- IMPROVE lanes (chain.c:80): strict prefix maxima of the scores in visit order ----
+				const int scx = skip ? (int)0x80000000 : sc;
+				const int M = __reduce_max_sync(FULL, scx);
+				unsigned imp = 0;
+				if (M > max_f) {
+					const int L = __ffs(__ballot_sync(FULL, scx == M)) - 1;
+					const unsigned early = __ballot_sync(FULL, scx > max_f) & mask_below(L);
+					if (early == 0) imp = 1u << L;
+					else {   // several candidates before L: full exclusive prefix-max scan
+						int pm = scx;
+#pragma unroll
+						for (int d = 1; d < 32; d <<= 1) {
+							const int o = __shfl_up_sync(FULL, pm, d);
+							if (lane >= d) pm = max(pm, o);
+						}
+						int ex = __shfl_up_sync(FULL, pm, 1);
+						ex = lane == 0 ? max_f : max(ex, max_f);
+						imp = __ballot_sync(FULL, !skip && sc > ex);
+					}
+				}
+				const unsigned mm = __ballot_sync(FULL, marked && !skip) & ~imp;
+
+				// ---- replay n_skip and the break (chain.c:82-85) ----
+				int brk = -1;
+				if ((imp & (imp - 1)) == 0) {
+					// at most one IMPROVE lane L: [marked misses before L] [L] [marked misses after L]
+					const int L = imp ? __ffs(imp) - 1 : 32;
+					const unsigned seg1 = mm & mask_below(L);
+					const int c1 = __popc(seg1);
+					const int need1 = max(max_skip - n_skip + 1, 1);
+					if (c1 >= need1) {
+						done = true;
+						if (COUNT) {
+							const int c = __popc(seg1 & (lanemask_lt(lane) | (1u << lane)));
+							brk = __ffs(__ballot_sync(FULL, ((seg1 >> lane) & 1u) && c == need1)) - 1;
+						}
+					} else {
+						n_skip += c1;
+						if (imp) {
+							max_f = M; max_j = jb - L;
+							vbest = __shfl_sync(FULL, vj, L);
+							if (n_skip > 0) --n_skip;
+							const unsigned seg2 = mm & ~mask_below(L + 1);
+							const int c2 = __popc(seg2);
+							const int need2 = max(max_skip - n_skip + 1, 1);
+							if (c2 >= need2) {
+								done = true;
+								if (COUNT) {
+									const int c = __popc(seg2 & (lanemask_lt(lane) | (1u << lane)));
+									brk = __ffs(__ballot_sync(FULL, ((seg2 >> lane) & 1u) && c == need2)) - 1;
+								}
+							} else n_skip += c2;
+						}
+					}
+				} else {
+					brk = replay_skip(imp, mm, max_skip, lane, n_skip);
+					const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
+					if (impb) {
+						const int L = 31 - __clz(impb);
+						max_f = __shfl_sync(FULL, sc, L);
+						max_j = jb - L;
+						vbest = __shfl_sync(FULL, vj, L);
+					}
+					if (brk >= 0) done = true;
+				}
+				if (COUNT && brk >= 0) n_visited -= nwin - (brk + 1);
+			}
+			// chain.c:89-90
+			if (lane == 0) {
+				const int4 ri = make_int4((int)xi, qi, max_f, max_j);
+				const int vi = max(vbest, max_f);
+				ring[i & (RING - 1)] = ri; vring[i & (RING - 1)] = vi;
+				wrec[i] = ri; vg[i] = vi;
+			}
+			__syncwarp();
+		}
+		if (COUNT && lane == 0) atomicAdd(w.visited, (unsigned long long)n_visited);
 	}
 }
 
@@ -240,7 +436,7 @@ __global__ void __launch_bounds__(256) k_first_ref(Workspace w)
 {	// r(k) = min{ i : p[i] == k } into t[] (preset to 0x7f7f7f7f)
 	const int n = w.n_anchors;
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		const int pi = w.p[i];
+		const int pi = w.wrec[i].w;
 		if (pi >= 0) atomicMin(&w.t[pi], i);
 	}
 }
@@ -266,13 +462,14 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 			const int i = base + lane;
 			const bool valid = i < e;
 			int pi = -1, vi = 0, fi = 0;
-			if (valid) { pi = w.p[i]; vi = w.v[i]; fi = w.f[i]; }
+			if (valid) { const int4 ri = w.wrec[i]; pi = ri.w; fi = ri.z; vi = w.v[i]; }
 			const bool E = valid && (vi >= min_sc || pi >= 0);                  // chain.c:109
 			bool late = false;
 			int vp = 0, fp = 0;
 			if (pi >= 0) {
-				vp = w.v[pi]; fp = w.f[pi];
-				late = !(vp >= min_sc || w.p[pi] >= 0) && w.t[pi] == i;         // chain.c:93-107: first referencer emits it
+				const int4 rp = w.wrec[pi];
+				vp = w.v[pi]; fp = rp.z;
+				late = !(vp >= min_sc || rp.w >= 0) && w.t[pi] == i;           // chain.c:93-107: first referencer emits it
 			}
 			const int cnt = (E ? 1 : 0) + (late ? 1 : 0);
 			int incl = cnt;
@@ -548,6 +745,7 @@ __global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
 	if (tid == 0) {
 		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
 		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS]; w.totals[3] = s_carry[2];
+		w.totals[4] = (long long)*w.visited;
 	}
 }
 
@@ -587,16 +785,59 @@ __global__ void __launch_bounds__(TAIL_T) k_pack_records(Workspace w)
 	}
 }
 
-// debug: convert p[] from batch-wide to per-read indices (what the reference's p[] holds, chain.c:89)
-__global__ void __launch_bounds__(256) k_localize_p(Workspace w)
+// debug: export f[] and p[] (per-read indices, what the reference's arrays hold at chain.c:89) from the records
+__global__ void __launch_bounds__(256) k_export_fp(Workspace w)
 {
 	const int lane = threadIdx.x & 31;
 	const int gw = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
 	const int nw = (int)((gridDim.x * (unsigned)blockDim.x) >> 5);
 	for (int r = gw; r < w.n_reads; r += nw) {
 		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
-		for (int i = b + lane; i < e; i += 32) { const int pi = w.p[i]; if (pi >= 0) w.p[i] = pi - b; }
+		for (int i = b + lane; i < e; i += 32) {
+			const int4 ri = w.wrec[i];
+			w.f[i] = ri.z;
+			w.p[i] = ri.w >= 0 ? ri.w - b : -1;
+		}
 	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Integer-issue microbenchmark: the denominator of the predecessor-scan roofline.  Eight
+// independent dependency chains per thread; MODE 0 = ALU pipe only (add/xor), MODE 1 = ALU + FMA-pipe integer
+// (mad.lo) interleaved, which is what can saturate the 1 instruction/clk/SMSP issue port.
+// ---------------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(256) k_int_peak(unsigned *out, int iters, unsigned seed)
+{
+	unsigned a0 = threadIdx.x + seed, a1 = a0 * 3u + 1u, a2 = a0 * 5u + 2u, a3 = a0 * 7u + 3u;
+	unsigned a4 = a0 * 11u + 4u, a5 = a0 * 13u + 5u, a6 = a0 * 17u + 6u, a7 = a0 * 19u + 7u;
+	const unsigned c = seed | 1u, d = seed * 2654435761u + 12345u;
+	for (int it = 0; it < iters; ++it) {
+#pragma unroll
+		for (int k = 0; k < 8; ++k) {
+			if (MODE == 0) {
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a0) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a1) : "r"(d));
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a2) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a3) : "r"(d));
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a4) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a5) : "r"(d));
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a6) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a7) : "r"(d));
+			} else {
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a0) : "r"(c));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a1) : "r"(c), "r"(d));
+				asm volatile("xor.b32 %0, %0, %1;" : "+r"(a2) : "r"(d));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a3) : "r"(c), "r"(d));
+				asm volatile("add.u32 %0, %0, %1;" : "+r"(a4) : "r"(c));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a5) : "r"(c), "r"(d));
+				asm volatile("xor.b32 %0, %0, %1;" : "+r"(a6) : "r"(d));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a7) : "r"(c), "r"(d));
+			}
+		}
+	}
+	const unsigned r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+	if (r == 0x12345678u) out[0] = r;   // keep the chains alive
+}
+
+// returns lane-ops issued by one launch (grid * 256 threads * iters * 64)
+long long launch_int_peak(int mode, int grid, int iters, unsigned *d_out, cudaStream_t s)
+{
+	if (mode == 0) k_int_peak<0><<<grid, 256, 0, s>>>(d_out, iters, 77u);
+	else k_int_peak<1><<<grid, 256, 0, s>>>(d_out, iters, 77u);
+	return (long long)grid * 256 * (long long)iters * 64;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -610,12 +851,35 @@ static inline int blocks_for(long long items, int per_block, int cap)
 	return (int)b;
 }
 
+static int fill_smem_bytes(int tab_entries) { return FILL_WARPS * (RING * 20 + tab_entries * 2); }
+static int fill_tab_entries(const mm2b200_params_t &prm)
+{	// 16-bit table of bw+1 gap costs per warp, only while it stays small (<= 2 KB per warp) and the costs fit
+	if (prm.bw < 0 || prm.bw > 1023) return 0;
+	return (prm.bw + 1 + 7) & ~7;
+}
+
+template <bool TABLE, bool COUNT>
+static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
+{
+	const int smem = fill_smem_bytes(tab_entries);
+	auto kern = k_fill_fast<TABLE, COUNT>;
+	static thread_local int occ_cache[4][2] = {{0, -1}, {0, -1}, {0, -1}, {0, -1}};
+	int *oc = occ_cache[(TABLE ? 2 : 0) + (COUNT ? 1 : 0)];
+	if (oc[1] != smem) {
+		cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+		int occ = 0;
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, FILL_WARPS * 32, smem);
+		oc[0] = occ < 1 ? 1 : occ; oc[1] = smem;
+	}
+	kern<<<sms * oc[0], FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries);
+}
+
 void query_launch_cfg(LaunchCfg *cfg)
 {
 	int dev = 0, sms = 148, occ = 0;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill<false>, 128, 0);
+	cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill_generic, 128, 0);
 	if (occ < 1) occ = 1;
 	cfg->sm_count = sms;
 	cfg->fill_blocks_per_sm = occ;
@@ -624,18 +888,23 @@ void query_launch_cfg(LaunchCfg *cfg)
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
 	cudaMemsetAsync(w.counters, 0, CNT_N * sizeof(int32_t), s);
+	cudaMemsetAsync(w.visited, 0, sizeof(unsigned long long), s);
 	k_prep<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.max_dist_x);
 	return 1;
 }
 
 int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg &cfg, bool host_generic, cudaStream_t s)
 {
-	const int grid = cfg.sm_count * cfg.fill_blocks_per_sm;
 	int n = 0;
 	// Both variants are enqueued unless the host already knows the generic one is needed; the one that does not
 	// match the device-side segment flag returns immediately.
-	if (!host_generic) { k_fill<false><<<grid, 128, 0, s>>>(w, prm); ++n; }
-	k_fill<true><<<grid, 128, 0, s>>>(w, prm); ++n;
+	if (!host_generic) {
+		const int te = fill_tab_entries(prm);
+		if (te) { if (cfg.count_visited) launch_fill_fast<true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false>(w, prm, cfg.sm_count, te, s); }
+		else { if (cfg.count_visited) launch_fill_fast<false, true>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false>(w, prm, cfg.sm_count, 0, s); }
+		++n;
+	}
+	k_fill_generic<<<cfg.sm_count * cfg.fill_blocks_per_sm, 128, 0, s>>>(w, prm); ++n;
 	return n;
 }
 
@@ -673,9 +942,9 @@ int launch_pack_records(const Workspace &w, cudaStream_t s)
 	return 2;
 }
 
-int launch_localize_p(const Workspace &w, cudaStream_t s)
+int launch_export_fp(const Workspace &w, cudaStream_t s)
 {
-	k_localize_p<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w);
+	k_export_fp<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w);
 	return 1;
 }
 

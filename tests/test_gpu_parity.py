@@ -80,6 +80,26 @@ def test_generic_path_cdna_and_segments(ctx):
     assert_same(got, want, "splice colinear")
 
 
+def test_visited_pair_counter():
+    """The device-side count of reference-visited (i,j) pairs (the metric's numerator) equals the oracle's."""
+    with api.ChainContext(device=0, count_visited=True) as c:
+        for name, n_reads in (("map-ont-100k", 800), ("ava-ont-50k", 40), ("map-pb-ul-20k", 4)):
+            spec = workload.CONFIGS[name]
+            offs, a = workload.generate(spec, 11, n_reads)
+            got = c.chain_batch(api.params(spec.preset), offs, a)
+            want = oracle.chain_batch(oracle.params(spec.preset), offs, a)
+            assert_same(got, want, name)
+            assert got.n_visited == want.visited, name
+        rng = np.random.default_rng(5)
+        reads = [random_colinear(rng, int(n), noise=0.4, step=3) for n in rng.integers(2, 2000, 30)]
+        offs, a = concat_reads(reads)
+        for over in (dict(), dict(max_skip=2), dict(bw=2000), dict(max_iter=40)):
+            got = c.chain_batch(api.params("map-ont", **over), offs, a)
+            want = oracle.chain_batch(oracle.params("map-ont", **over), offs, a)
+            assert_same(got, want, f"count {over}")
+            assert got.n_visited == want.visited, over
+
+
 def test_empty_and_tiny(ctx):
     rng = np.random.default_rng(7)
     reads = [np.zeros((0, 2), np.uint64), random_dense(rng, 1), np.zeros((0, 2), np.uint64), random_dense(rng, 2),
