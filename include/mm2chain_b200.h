@@ -130,6 +130,20 @@ int mm2b200_fill_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t 
 int mm2b200_bottom_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, const int64_t *rec_off,
                          const struct new_seed *rec, mm2b200_result_t *res);
 
+/* ---- Section 3b: read-batch sharding over several GPUs of one box ------------------------------------------- */
+
+/* Splits reads [0, n_reads) into n_parts contiguous ranges of near-equal anchor count (the cost model of SURVEY 8e:
+ * work ~ anchors).  cuts[n_parts+1] receives the range boundaries (cuts[0] = 0, cuts[n_parts] = n_reads).
+ * Pure host arithmetic: usable without a GPU. */
+int mm2b200_partition_reads(int64_t n_reads, const int64_t *offs, int32_t n_parts, int64_t *cuts);
+
+/* mm_chain_dp over a batch sharded across n_ctx contexts (normally one per GPU): one host thread per context,
+ * no collective -- reads are independent.  Shard k = reads [cuts[k], cuts[k+1]) (cuts[n_ctx+1], filled by the call);
+ * res[k] is that shard's result, owned by ctxs[k], with offsets relative to the shard.  Results stay in submission
+ * order: shard 0's reads first. */
+int mm2b200_chain_batch_multi(mm2b200_ctx_t *const *ctxs, int32_t n_ctx, const mm2b200_params_t *prm, int64_t n_reads,
+                              const int64_t *offs, const mm128_t *a, int64_t *cuts, mm2b200_result_t *res);
+
 /* ---- Section 4: device-resident entry points, instrumentation ---------------------------------------------- */
 
 /* Device pointers valid until the next call on the context.  Sizes live on the device (totals[0] = sum n_u,

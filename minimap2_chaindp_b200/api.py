@@ -33,6 +33,7 @@ EXPORTED_SYMBOLS = (
     "mm2b200_create", "mm2b200_destroy", "mm2b200_last_error", "mm2b200_device_count",
     "mm2b200_pinned_alloc", "mm2b200_pinned_free",
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
+    "mm2b200_partition_reads", "mm2b200_chain_batch_multi",
     "mm2b200_chain_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
     "mm2b200_version",
 )
@@ -115,6 +116,8 @@ def lib() -> C.CDLL:
         L.mm2b200_chain_batch.argtypes = [vp, C.POINTER(Params), i64, vp, vp, C.POINTER(_Result)]
         L.mm2b200_fill_batch.argtypes = [vp, C.POINTER(Params), i64, vp, vp, C.POINTER(_Records), vp, vp, vp]
         L.mm2b200_bottom_batch.argtypes = [vp, C.POINTER(Params), i64, vp, vp, C.POINTER(_Result)]
+        L.mm2b200_partition_reads.argtypes = [i64, vp, i32, vp]
+        L.mm2b200_chain_batch_multi.argtypes = [vp, i32, C.POINTER(Params), i64, vp, vp, vp, vp]
         L.mm2b200_chain_device.argtypes = [vp, C.POINTER(Params), i64, i64, vp, vp, vp, C.POINTER(_DevResult)]
         L.mm2b200_launch_count.argtypes = [vp]
         L.mm2b200_launch_count.restype = i64
@@ -309,6 +312,29 @@ class ChainContext:
         v = C.c_double()
         _check(lib().mm2b200_int_peak(self._h, mode, C.byref(v)))
         return v.value
+
+
+def partition_reads(offs, n_parts: int) -> np.ndarray:
+    """mm2b200_partition_reads: contiguous read ranges of near-equal anchor count -> cuts[n_parts+1]."""
+    offs = np.ascontiguousarray(offs, dtype=np.int64)
+    cuts = np.zeros(n_parts + 1, dtype=np.int64)
+    _check(lib().mm2b200_partition_reads(offs.shape[0] - 1, offs.ctypes.data, n_parts, cuts.ctypes.data))
+    return cuts
+
+
+def chain_batch_multi(ctxs, prm: Params, offs, a):
+    """mm2b200_chain_batch_multi: one batch sharded over several contexts (one per GPU), results merged in read order."""
+    a = _anchors(a)
+    offs = np.ascontiguousarray(offs, dtype=np.int64)
+    nr, n = offs.shape[0] - 1, len(ctxs)
+    handles = (C.c_void_p * n)(*[c._h for c in ctxs])
+    cuts = np.zeros(n + 1, dtype=np.int64)
+    res = (_Result * n)()
+    _check(lib().mm2b200_chain_batch_multi(handles, n, C.byref(prm), nr, offs.ctypes.data, a.ctypes.data,
+                                           cuts.ctypes.data, res))
+    parts = [ChainContext._result(res[k], int(cuts[k + 1] - cuts[k])) for k in range(n)]
+    from .shard import merge_results
+    return merge_results(parts), cuts
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -552,6 +552,46 @@ extern "C" int mm2b200_bottom_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	return MM2B200_OK;
 }
 
+extern "C" int mm2b200_partition_reads(int64_t n_reads, const int64_t *offs, int32_t n_parts, int64_t *cuts)
+{
+	if (n_reads < 0 || n_parts < 1 || !cuts || (n_reads > 0 && !offs)) return fail(MM2B200_ERR_ARG, "bad partition arguments");
+	const int64_t base = n_reads ? offs[0] : 0, total = n_reads ? offs[n_reads] - base : 0;
+	cuts[0] = 0;
+	int64_t r = 0;
+	for (int32_t k = 1; k < n_parts; ++k) {
+		// first read whose start reaches k/n_parts of the anchors (ties resolved towards equal read counts when total == 0)
+		const int64_t target = total ? (int64_t)(((__int128)total * k) / n_parts) : 0;
+		if (total == 0) r = n_reads * k / n_parts;
+		else while (r < n_reads && offs[r] - base < target) ++r;
+		cuts[k] = r;
+	}
+	cuts[n_parts] = n_reads;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_chain_batch_multi(mm2b200_ctx_t *const *ctxs, int32_t n_ctx, const mm2b200_params_t *prm, int64_t n_reads,
+                                         const int64_t *offs, const mm128_t *a, int64_t *cuts, mm2b200_result_t *res)
+{
+	if (!ctxs || n_ctx < 1 || !cuts || !res) return fail(MM2B200_ERR_ARG, "bad multi-context arguments");
+	int rc = mm2b200_partition_reads(n_reads, offs, n_ctx, cuts);
+	if (rc) return rc;
+	std::vector<int> rcs((size_t)n_ctx, 0);
+	std::vector<std::string> errs((size_t)n_ctx);
+	std::vector<std::thread> th;
+	for (int32_t k = 0; k < n_ctx; ++k) {
+		th.emplace_back([&, k] {
+			const int64_t r0 = cuts[k], r1 = cuts[k + 1];
+			// offs + r0 is a valid offsets array for the shard: the batch code rebases on its first entry
+			rcs[k] = mm2b200_chain_batch(ctxs[k], prm, r1 - r0, offs + r0, a, &res[k]);
+			if (rcs[k]) errs[k] = g_err;
+		});
+	}
+	for (auto &t : th) t.join();
+	for (int32_t k = 0; k < n_ctx; ++k)
+		if (rcs[k]) { g_err = "shard " + std::to_string(k) + ": " + errs[k]; return rcs[k]; }
+	return MM2B200_OK;
+}
+
 extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
                                     const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_result_t *out)
 {

@@ -1,0 +1,91 @@
+"""CPU-only checks of the boundary: the C-ABI library loads without a GPU and exports every symbol the header
+declares; compute entry points fail loudly (no CPU fallback); the read partitioner; the product never touches oracle/."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from minimap2_chaindp_b200 import api, shard, workload
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "mm2chain_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(mm2b200_[a-z0-9_]+|mm_chain_dp[a-z_]*)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared_symbols()
+    assert len(names) >= 18 and "mm_chain_dp" in names and "mm2b200_chain_batch" in names
+    L = api.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mm2chain_b200.h but not exported"
+    assert sorted(api.EXPORTED_SYMBOLS) == names
+    assert b"sm_100a" in L.mm2b200_version()
+
+
+def test_struct_layouts_match_the_reference():
+    assert api.SEED_DTYPE.itemsize == 24                      # struct new_seed, minimap.h:51-55
+    assert [api.SEED_DTYPE.fields[k][1] for k in ("x", "y", "p", "f")] == [0, 8, 16, 20]
+    import ctypes as C
+    assert C.sizeof(api.Params) == 36
+
+
+def test_no_cpu_fallback_without_gpu():
+    """Without a CUDA device the context cannot be created and the drop-in reports an error instead of computing."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    assert api.lib().mm2b200_device_count() == 0
+    with pytest.raises(api.ChainError) as ei:
+        api.ChainContext(device=0)
+    assert ei.value.code == api.ERR_CUDA
+    a = np.array([[100, (15 << 32) | 10], [120, (15 << 32) | 30], [140, (15 << 32) | 50]], np.uint64)
+    with pytest.raises(api.ChainError):
+        api.mm_chain_dp(api.params("map-ont", min_sc=0, min_cnt=1), a)
+
+
+def test_product_does_not_use_the_oracle():
+    pkg = os.path.join(ROOT, "minimap2_chaindp_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".c", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text and "chain_oracle" not in text \
+                    and "libmm2ref" not in text, f"{f} references the oracle"
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_partition_reads_balances_anchors(world):
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs = workload.count(spec, 0, 5000)
+    cuts = api.partition_reads(offs, world)
+    assert cuts[0] == 0 and cuts[-1] == 5000 and np.all(np.diff(cuts) >= 0)
+    load = np.array([offs[cuts[k + 1]] - offs[cuts[k]] for k in range(world)], np.float64)
+    assert load.sum() == offs[-1]
+    assert load.max() <= load.mean() * 1.02 + 2000           # within one read of perfect balance
+    # absolute offsets (a shard of a larger array) and degenerate inputs
+    cuts2 = api.partition_reads(offs[100:1101], world)
+    assert cuts2[0] == 0 and cuts2[-1] == 1000
+    assert api.partition_reads(np.zeros(1, np.int64), world).tolist() == [0] * (world + 1)
+    assert api.partition_reads(np.zeros(11, np.int64), 2).tolist() == [0, 5, 10]
+
+
+def test_merge_results_rebases_offsets():
+    import oracle
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 0, 300)
+    prm = oracle.params(spec.preset)
+    whole = oracle.chain_batch(prm, offs, a)
+    cuts = api.partition_reads(offs, 3)
+    parts = []
+    for k in range(3):
+        o = offs[cuts[k]:cuts[k + 1] + 1]
+        r = oracle.chain_batch(prm, o - o[0], a[o[0]:o[-1]])
+        parts.append(api.BatchResult(r.n_u, r.u_off, r.b_off, r.u, r.b))
+    merged = shard.merge_results(parts)
+    for name in ("n_u", "u_off", "b_off", "u", "b"):
+        assert np.array_equal(getattr(merged, name), getattr(whole, name)), name
