@@ -10,6 +10,7 @@
 // Everything is integer work on 16-byte anchors; nothing here is GEMM-shaped, so no tensor cores.  The one
 // floating-point expression, (int)(dd * .01 * avg_qspan) (chain.c:73,78), is evaluated with explicit
 // round-to-nearest double multiplies in the reference's association order so the result is bit-identical.
+#include <cstdlib>
 #include "chain_internal.h"
 
 namespace mm2b200 {
@@ -245,22 +246,138 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 #define FILL_WARPS 4
 #define RING 64
 
+// One 32-predecessor chunk of anchor i (lane = jb - j).  State carried across chunks of the same anchor:
+//   max_f/max_j/vbest  running best predecessor (chain.c:80-81) and its peak score v[]
+//   budget             marked misses still allowed before the break: max_skip + 1 - n_skip (chain.c:82-85)
+// Returns true when the scan of anchor i is finished (break, or the window ended inside the chunk).
+struct ScanState { int max_f, max_j, vbest, budget; long long visited; };
+
+template <bool COUNT>
+static __device__ __forceinline__ bool scan_chunk(ScanState &st, const int i, const int jb, const int jlo, const int lane,
+                                                   const int4 rj, const int vj, const bool marked_mem,
+                                                   const unsigned xi, const int qi, const int span,
+                                                   const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
+                                                   const int cost, const int B0, const int max_skip, int32_t *t)
+{
+	const int j = jb - lane;
+	const unsigned dr = xi - (unsigned)rj.x;
+	bool inw = (j >= jlo) && (dr <= mdx);
+	bool done = false;
+	int nwin = 32;
+	if (!__all_sync(FULL, inw)) {                         // the window (chain.c:58) ends inside this chunk
+		nwin = __ffs(~__ballot_sync(FULL, inw)) - 1;      // lanes past the first one out of the window are dropped
+		done = true;
+		if (nwin == 0) return true;
+		inw = lane < nwin;
+	}
+	if (COUNT) st.visited += nwin;
+
+	// ---- pair score (chain.c:60-79, same-segment non-cDNA branch) ----
+	const int dq = qi - rj.y;
+	const int dd = abs((int)dr - dq);
+	// dr == 0 || dr > dr_max  <=>  dr-1 >= dr_max (unsigned);  dq <= 0 || dq > dq_max  <=>  dq-1 >= dq_max (unsigned)
+	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
+	const int sc = min(min(dq, (int)dr), span) - cost + rj.z;
+	const int scx = skip ? (int)0x80000000 : sc;
+
+	// ---- marks (chain.c:83,87): inside the chunk via a warp OR-reduce, beyond it via t[] ----
+	const int pj = rj.w;
+	const unsigned kt = (unsigned)(jb - pj);              // lane that scores anchor p[j], if it is in this chunk
+	const bool mk = !skip && pj >= 0;
+	const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << (kt & 31u)) : 0u);
+	const bool far = mk && kt >= 32u;
+	if (__any_sync(FULL, far)) { if (far) t[pj] = i; }
+	const bool marked = ((mloc >> lane) & 1u) || marked_mem;
+
+	// ---- IMPROVE lanes (chain.c:80): strict prefix maxima of the scores in visit order ----
+	const int M = __reduce_max_sync(FULL, scx);
+	unsigned imp = 0;
+	if (M > st.max_f) {
+		const unsigned eq = __ballot_sync(FULL, scx == M);
+		const unsigned gt = __ballot_sync(FULL, scx > st.max_f);
+		const unsigned low = eq & (0u - eq);              // first lane that attains the chunk maximum
+		if ((gt & (low - 1u)) == 0u) imp = low;           // nobody before it beats the running maximum: the only IMPROVE
+		else {                                            // several candidates: full exclusive prefix-max scan
+			int pm = scx;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const int o = __shfl_up_sync(FULL, pm, d);
+				if (lane >= d) pm = max(pm, o);
+			}
+			int ex = __shfl_up_sync(FULL, pm, 1);
+			ex = lane == 0 ? st.max_f : max(ex, st.max_f);
+			imp = __ballot_sync(FULL, scx > ex);
+		}
+	}
+	const unsigned mm = __ballot_sync(FULL, marked && !skip) & ~imp;   // MARKED-MISS lanes
+
+	// ---- replay n_skip and the break (chain.c:82-85) ----
+	int brk = -1;
+	if ((imp & (imp - 1u)) == 0u) {
+		// at most one IMPROVE lane L: [marked misses before L] [L] [marked misses after L]; imp-1 = lanes below L
+		const unsigned below = imp - 1u;                  // imp == 0 -> all lanes
+		const unsigned seg1 = mm & below;
+		const int c1 = __popc(seg1);
+		if (c1 >= st.budget) {
+			done = true;
+			if (COUNT) {
+				const int c = __popc(seg1 & (lanemask_lt(lane) | (1u << lane)));
+				brk = __ffs(__ballot_sync(FULL, ((seg1 >> lane) & 1u) && c == st.budget)) - 1;
+			}
+		} else {
+			st.budget -= c1;
+			if (imp) {
+				const int L = 31 - __clz(imp);
+				st.max_f = M; st.max_j = jb - L;
+				st.vbest = __shfl_sync(FULL, vj, L);
+				st.budget = min(st.budget + 1, B0);       // if (n_skip > 0) --n_skip
+				const unsigned seg2 = mm & ~(imp | below);
+				const int c2 = __popc(seg2);
+				if (c2 >= st.budget) {
+					done = true;
+					if (COUNT) {
+						const int c = __popc(seg2 & (lanemask_lt(lane) | (1u << lane)));
+						brk = __ffs(__ballot_sync(FULL, ((seg2 >> lane) & 1u) && c == st.budget)) - 1;
+					}
+				} else st.budget -= c2;
+			}
+		}
+	} else {
+		int n_skip = B0 - st.budget;
+		brk = replay_skip(imp, mm, max_skip, lane, n_skip);
+		st.budget = B0 - n_skip;
+		const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
+		if (impb) {
+			const int L = 31 - __clz(impb);
+			st.max_f = __shfl_sync(FULL, sc, L);
+			st.max_j = jb - L;
+			st.vbest = __shfl_sync(FULL, vj, L);
+		}
+		if (brk >= 0) done = true;
+	}
+	if (COUNT && brk >= 0) st.visited -= nwin - (brk + 1);
+	return done;
+}
+
 template <bool TABLE, bool COUNT>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
-	extern __shared__ __align__(16) unsigned char smem[];
+	// dynamic shared memory, indexed (not pointed into) so that accesses stay plain LDS/STS:
+	//   [0, FILL_WARPS*RING) int4 ring records | FILL_WARPS*RING ints of v | FILL_WARPS*tab_entries u16 gap costs
+	extern __shared__ int4 smem4[];
 	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	int4 *ring = reinterpret_cast<int4*>(smem) + wib * RING;
-	int *vring = reinterpret_cast<int*>(smem + FILL_WARPS * RING * 16) + wib * RING;
-	unsigned short *tab = reinterpret_cast<unsigned short*>(smem + FILL_WARPS * RING * 20) + wib * tab_entries;
+	int *const smem_v = reinterpret_cast<int*>(smem4 + FILL_WARPS * RING);
+	unsigned short *const smem_tab = reinterpret_cast<unsigned short*>(smem_v + FILL_WARPS * RING);
+	const int rbase = wib * RING, tbase = wib * tab_entries;
 
 	const int n_units = w.counters[CNT_UNITS];
 	const unsigned mdx = (unsigned)prm.max_dist_x;
 	const unsigned dq_max = (unsigned)(prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x);   // chain.c:64
 	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
 	const int max_skip = prm.max_skip, bw = prm.bw;
+	const int B0 = max(max_skip + 1, 1);
 	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
 	const ulonglong2 *__restrict__ a = w.a;
 	int4 *wrec = w.wrec;
@@ -277,12 +394,13 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 		const int s = un.start, e = un.start + un.len;
 		const float avgf = w.avg[un.read];
 		const double avg = (double)avgf;
-		long long n_visited = 0;
+		ScanState st;
+		st.visited = 0;
 
 		if (TABLE && (!have_tab || __float_as_uint(avgf) != tab_key)) {
 			__syncwarp();
 			for (int dd = lane; dd <= bw; dd += 32)
-				tab[dd] = (unsigned short)(lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1));
+				smem_tab[tbase + dd] = (unsigned short)(lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1));
 			tab_key = __float_as_uint(avgf);
 			have_tab = true;
 		}
@@ -290,142 +408,65 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 		ulonglong2 nxt = a[s];
 		if (lane == 0) {
 			const int sp = (int)((nxt.y >> 32) & 0xff);
-			ring[s & (RING - 1)] = make_int4((int)(unsigned)nxt.x, (int)(unsigned)nxt.y, sp, -1);
-			vring[s & (RING - 1)] = sp;
+			smem4[rbase + (s & (RING - 1))] = make_int4((int)(unsigned)nxt.x, (int)(unsigned)nxt.y, sp, -1);
+			smem_v[rbase + (s & (RING - 1))] = sp;
 		}
 		nxt = a[s + 1];
 		__syncwarp();
 
 		for (int i = s + 1; i < e; ++i) {
-			const ulonglong2 ai = nxt;
+			const unsigned xi = (unsigned)nxt.x;
+			const int qi = (int)(unsigned)nxt.y;
+			const int span = (int)((nxt.y >> 32) & 0xff);
 			if (i + 1 < e) nxt = a[i + 1];              // prefetch: not needed before the next iteration
-			const unsigned xi = (unsigned)ai.x;
-			const int qi = (int)(unsigned)ai.y;
-			const int span = (int)((ai.y >> 32) & 0xff);
-			int max_f = span, max_j = -1, n_skip = 0, vbest = (int)0x80000000;
 			const int jlo = max(s, i - max_iter);
-			bool done = false;
+			st.max_f = span; st.max_j = -1; st.vbest = (int)0x80000000; st.budget = B0;
 
-			for (int jb = i - 1; jb >= jlo && !done; jb -= 32) {
-				const int j = jb - lane;
-				int4 rj;
-				int vj;
-				bool marked_mem = false;
-				if (jb >= i - RING) {                         // the last 64 anchors live in the ring (uniform branch)
-					rj = ring[j & (RING - 1)];
-					vj = vring[j & (RING - 1)];
-					if (jb != i - 1) { __syncwarp(); if (j >= jlo) marked_mem = t[j] == i; }
-				} else {
+			// chunk 0: anchors i-1 .. i-32 from the ring; no earlier chunk can have marked them
+			const int slot0 = rbase + ((i - 1 - lane) & (RING - 1));
+			int4 rj = smem4[slot0];
+			int vj = smem_v[slot0];
+			int cost;
+			{
+				const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+				cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
+			}
+			bool done = scan_chunk<COUNT>(st, i, i - 1, jlo, lane, rj, vj, false, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
+			if (!done && i - 33 >= jlo) {
+				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
+				__syncwarp();
+				const int j1 = i - 33 - lane;
+				rj = smem4[slot0 ^ 32];
+				vj = smem_v[slot0 ^ 32];
+				const bool mmem = j1 >= jlo && t[j1] == i;
+				{
+					const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+					cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
+				}
+				done = scan_chunk<COUNT>(st, i, i - 33, jlo, lane, rj, vj, mmem, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
+				// deeper chunks: the same records from global memory (this warp wrote them; L1/L2 hits)
+				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
 					__syncwarp();
+					const int j = jb - lane;
 					rj = make_int4(0, 0, 0, -1); vj = 0;
-					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; marked_mem = t[j] == i; }
+					bool mg = false;
+					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
+					const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+					cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
+					done = scan_chunk<COUNT>(st, i, jb, jlo, lane, rj, vj, mg, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
 				}
-				const unsigned dr = xi - (unsigned)rj.x;
-				const unsigned wmask = __ballot_sync(FULL, j >= jlo && dr <= mdx);
-				int nwin = 32;
-				if (wmask != FULL) {
-					nwin = __ffs(~wmask) - 1;
-					done = true;
-					if (nwin == 0) break;
-				}
-				if (COUNT) n_visited += nwin;
-
-				// ---- pair score (chain.c:60-79, same-segment non-cDNA branch) ----
-				const int dq = qi - rj.y;
-				const int dd = abs((int)dr - dq);
-				// dr == 0 || dr > dr_max  <=>  dr-1 >= dr_max (unsigned);  dq <= 0 || dq > dq_max  <=>  dq-1 >= dq_max (unsigned)
-				const bool skip = lane >= nwin || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
-				int cost;
-				if (TABLE) cost = tab[min(dd, bw)];
-				else cost = lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
-				const int sc = min(min(dq, (int)dr), span) - cost + rj.z;
-
-				// ---- marks (chain.c:83,87) ----
-				const int pj = rj.w;
-				const unsigned kt = (unsigned)(jb - pj);          // lane that scores anchor p[j], if it is in this chunk
-				const bool mk = !skip && pj >= 0;
-				const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << kt) : 0u);
-				const bool far = mk && kt >= 32u;
-				if (__any_sync(FULL, far)) { if (far) t[pj] = i; }
-				const bool marked = ((mloc >> lane) & 1u) || marked_mem;
-
-				// ---- IMPROVE lanes (chain.c:80): strict prefix maxima of the scores in visit order ----
-				const int scx = skip ? (int)0x80000000 : sc;
-				const int M = __reduce_max_sync(FULL, scx);
-				unsigned imp = 0;
-				if (M > max_f) {
-					const int L = __ffs(__ballot_sync(FULL, scx == M)) - 1;
-					const unsigned early = __ballot_sync(FULL, scx > max_f) & mask_below(L);
-					if (early == 0) imp = 1u << L;
-					else {   // several candidates before L: full exclusive prefix-max scan
-						int pm = scx;
-#pragma unroll
-						for (int d = 1; d < 32; d <<= 1) {
-							const int o = __shfl_up_sync(FULL, pm, d);
-							if (lane >= d) pm = max(pm, o);
-						}
-						int ex = __shfl_up_sync(FULL, pm, 1);
-						ex = lane == 0 ? max_f : max(ex, max_f);
-						imp = __ballot_sync(FULL, !skip && sc > ex);
-					}
-				}
-				const unsigned mm = __ballot_sync(FULL, marked && !skip) & ~imp;
-
-				// ---- replay n_skip and the break (chain.c:82-85) ----
-				int brk = -1;
-				if ((imp & (imp - 1)) == 0) {
-					// at most one IMPROVE lane L: [marked misses before L] [L] [marked misses after L]
-					const int L = imp ? __ffs(imp) - 1 : 32;
-					const unsigned seg1 = mm & mask_below(L);
-					const int c1 = __popc(seg1);
-					const int need1 = max(max_skip - n_skip + 1, 1);
-					if (c1 >= need1) {
-						done = true;
-						if (COUNT) {
-							const int c = __popc(seg1 & (lanemask_lt(lane) | (1u << lane)));
-							brk = __ffs(__ballot_sync(FULL, ((seg1 >> lane) & 1u) && c == need1)) - 1;
-						}
-					} else {
-						n_skip += c1;
-						if (imp) {
-							max_f = M; max_j = jb - L;
-							vbest = __shfl_sync(FULL, vj, L);
-							if (n_skip > 0) --n_skip;
-							const unsigned seg2 = mm & ~mask_below(L + 1);
-							const int c2 = __popc(seg2);
-							const int need2 = max(max_skip - n_skip + 1, 1);
-							if (c2 >= need2) {
-								done = true;
-								if (COUNT) {
-									const int c = __popc(seg2 & (lanemask_lt(lane) | (1u << lane)));
-									brk = __ffs(__ballot_sync(FULL, ((seg2 >> lane) & 1u) && c == need2)) - 1;
-								}
-							} else n_skip += c2;
-						}
-					}
-				} else {
-					brk = replay_skip(imp, mm, max_skip, lane, n_skip);
-					const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
-					if (impb) {
-						const int L = 31 - __clz(impb);
-						max_f = __shfl_sync(FULL, sc, L);
-						max_j = jb - L;
-						vbest = __shfl_sync(FULL, vj, L);
-					}
-					if (brk >= 0) done = true;
-				}
-				if (COUNT && brk >= 0) n_visited -= nwin - (brk + 1);
 			}
 			// chain.c:89-90
 			if (lane == 0) {
-				const int4 ri = make_int4((int)xi, qi, max_f, max_j);
-				const int vi = max(vbest, max_f);
-				ring[i & (RING - 1)] = ri; vring[i & (RING - 1)] = vi;
+				const int4 ri = make_int4((int)xi, qi, st.max_f, st.max_j);
+				const int vi = max(st.vbest, st.max_f);
+				const int slot = rbase + (i & (RING - 1));
+				smem4[slot] = ri; smem_v[slot] = vi;
 				wrec[i] = ri; vg[i] = vi;
 			}
 			__syncwarp();
 		}
-		if (COUNT && lane == 0) atomicAdd(w.visited, (unsigned long long)n_visited);
+		if (COUNT && lane == 0) atomicAdd(w.visited, (unsigned long long)st.visited);
 	}
 }
 
