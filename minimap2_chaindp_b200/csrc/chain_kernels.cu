@@ -245,32 +245,69 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 //    lane beats the running maximum, L is the only IMPROVE lane (the common case) and no prefix scan is needed.
 #define FILL_WARPS 4
 #define RING 64
+// dynamic shared memory of k_fill_fast, byte offsets from the CTA's base (per warp: 1 KB ring + 1 KB v + 512 B anchors)
+#define SM_RING   0                               // int4 {x, q, f, p} of the last RING anchors, 16 B each
+#define SM_VRING  (FILL_WARPS * RING * 16)        // v[] of the same anchors, 16-byte stride so one register addresses both
+#define SM_ABUF   (2 * FILL_WARPS * RING * 16)    // {x, q, span, -} of the current 32-aligned block of anchors
+#define SM_TAB    (SM_ABUF + FILL_WARPS * 32 * 16) // 16-bit gap costs, tab_entries per warp
 
-// One 32-predecessor chunk of anchor i (lane = jb - j).  State carried across chunks of the same anchor:
-//   max_f/max_j/vbest  running best predecessor (chain.c:80-81) and its peak score v[]
-//   budget             marked misses still allowed before the break: max_skip + 1 - n_skip (chain.c:82-85)
-// Returns true when the scan of anchor i is finished (break, or the window ended inside the chunk).
-struct ScanState { int max_f, max_j, vbest, budget; long long visited; };
+// explicit 32-bit shared addresses: every access is one LDS/STS with an immediate offset, no generic-address math
+template <int OFF> static __device__ __forceinline__ int4 lds128(unsigned addr)
+{
+	int4 v;
+	asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4+%5];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr), "n"(OFF));
+	return v;
+}
+template <int OFF> static __device__ __forceinline__ int lds32(unsigned addr)
+{
+	int v;
+	asm volatile("ld.shared.s32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+	return v;
+}
+static __device__ __forceinline__ int lds_u16(unsigned addr)
+{
+	unsigned short v;
+	asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+	return (int)v;
+}
+template <int OFF> static __device__ __forceinline__ void sts128(unsigned addr, int4 v)
+{
+	asm volatile("st.shared.v4.s32 [%0+%1], {%2,%3,%4,%5};" :: "r"(addr), "n"(OFF), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+template <int OFF> static __device__ __forceinline__ void sts32(unsigned addr, int v)
+{
+	asm volatile("st.shared.s32 [%0+%1], %2;" :: "r"(addr), "n"(OFF), "r"(v) : "memory");
+}
+static __device__ __forceinline__ void sts_u16(unsigned addr, int v)
+{
+	asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "h"((unsigned short)v) : "memory");
+}
 
+// One 32-predecessor chunk of anchor i (lane = jb - j).  State carried across the chunks of one anchor:
+//   max_f / max_j / vbest  running best predecessor (chain.c:80-81) and its peak score v[]
+//   budget                 marked misses still allowed before the break: max_skip + 1 - n_skip (chain.c:82-85)
+// Returns nonzero when the scan of anchor i is finished (break, or the window ended inside the chunk).
+// `far` reports lanes whose mark lands beyond this chunk; the caller publishes those to t[] only if the scan goes on.
 template <bool COUNT>
-static __device__ __forceinline__ bool scan_chunk(ScanState &st, const int i, const int jb, const int jlo, const int lane,
-                                                   const int4 rj, const int vj, const bool marked_mem,
-                                                   const unsigned xi, const int qi, const int span,
-                                                   const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
-                                                   const int cost, const int B0, const int max_skip, int32_t *t)
+static __device__ __forceinline__ int scan_chunk(int &max_f, int &max_j, int &vbest, int &budget, long long &visited, bool &far,
+                                                  const int jb, const int jlo, const int lane,
+                                                  const int4 rj, const int vj, const bool marked_mem,
+                                                  const unsigned xi, const int qi, const int span,
+                                                  const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
+                                                  const int cost, const int B0, const int max_skip)
 {
 	const int j = jb - lane;
 	const unsigned dr = xi - (unsigned)rj.x;
 	bool inw = (j >= jlo) && (dr <= mdx);
-	bool done = false;
-	int nwin = 32;
+	int done = 0, nwin = 32;
+	far = false;
 	if (!__all_sync(FULL, inw)) {                         // the window (chain.c:58) ends inside this chunk
 		nwin = __ffs(~__ballot_sync(FULL, inw)) - 1;      // lanes past the first one out of the window are dropped
-		done = true;
-		if (nwin == 0) return true;
+		done = 1;
+		if (nwin == 0) return 1;
 		inw = lane < nwin;
 	}
-	if (COUNT) st.visited += nwin;
+	if (COUNT) visited += nwin;
 
 	// ---- pair score (chain.c:60-79, same-segment non-cDNA branch) ----
 	const int dq = qi - rj.y;
@@ -285,16 +322,15 @@ static __device__ __forceinline__ bool scan_chunk(ScanState &st, const int i, co
 	const unsigned kt = (unsigned)(jb - pj);              // lane that scores anchor p[j], if it is in this chunk
 	const bool mk = !skip && pj >= 0;
 	const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << (kt & 31u)) : 0u);
-	const bool far = mk && kt >= 32u;
-	if (__any_sync(FULL, far)) { if (far) t[pj] = i; }
+	far = mk && kt >= 32u;
 	const bool marked = ((mloc >> lane) & 1u) || marked_mem;
 
 	// ---- IMPROVE lanes (chain.c:80): strict prefix maxima of the scores in visit order ----
 	const int M = __reduce_max_sync(FULL, scx);
 	unsigned imp = 0;
-	if (M > st.max_f) {
+	if (M > max_f) {
 		const unsigned eq = __ballot_sync(FULL, scx == M);
-		const unsigned gt = __ballot_sync(FULL, scx > st.max_f);
+		const unsigned gt = __ballot_sync(FULL, scx > max_f);
 		const unsigned low = eq & (0u - eq);              // first lane that attains the chunk maximum
 		if ((gt & (low - 1u)) == 0u) imp = low;           // nobody before it beats the running maximum: the only IMPROVE
 		else {                                            // several candidates: full exclusive prefix-max scan
@@ -305,7 +341,7 @@ static __device__ __forceinline__ bool scan_chunk(ScanState &st, const int i, co
 				if (lane >= d) pm = max(pm, o);
 			}
 			int ex = __shfl_up_sync(FULL, pm, 1);
-			ex = lane == 0 ? st.max_f : max(ex, st.max_f);
+			ex = lane == 0 ? max_f : max(ex, max_f);
 			imp = __ballot_sync(FULL, scx > ex);
 		}
 	}
@@ -318,59 +354,59 @@ static __device__ __forceinline__ bool scan_chunk(ScanState &st, const int i, co
 		const unsigned below = imp - 1u;                  // imp == 0 -> all lanes
 		const unsigned seg1 = mm & below;
 		const int c1 = __popc(seg1);
-		if (c1 >= st.budget) {
-			done = true;
+		if (c1 >= budget) {
+			done = 1;
 			if (COUNT) {
 				const int c = __popc(seg1 & (lanemask_lt(lane) | (1u << lane)));
-				brk = __ffs(__ballot_sync(FULL, ((seg1 >> lane) & 1u) && c == st.budget)) - 1;
+				brk = __ffs(__ballot_sync(FULL, ((seg1 >> lane) & 1u) && c == budget)) - 1;
 			}
 		} else {
-			st.budget -= c1;
+			budget -= c1;
 			if (imp) {
-				const int L = 31 - __clz(imp);
-				st.max_f = M; st.max_j = jb - L;
-				st.vbest = __shfl_sync(FULL, vj, L);
-				st.budget = min(st.budget + 1, B0);       // if (n_skip > 0) --n_skip
+				const int L = __popc(below);
+				max_f = M; max_j = jb - L;
+				vbest = __shfl_sync(FULL, vj, L);
+				budget = min(budget + 1, B0);             // if (n_skip > 0) --n_skip
 				const unsigned seg2 = mm & ~(imp | below);
 				const int c2 = __popc(seg2);
-				if (c2 >= st.budget) {
-					done = true;
+				if (c2 >= budget) {
+					done = 1;
 					if (COUNT) {
 						const int c = __popc(seg2 & (lanemask_lt(lane) | (1u << lane)));
-						brk = __ffs(__ballot_sync(FULL, ((seg2 >> lane) & 1u) && c == st.budget)) - 1;
+						brk = __ffs(__ballot_sync(FULL, ((seg2 >> lane) & 1u) && c == budget)) - 1;
 					}
-				} else st.budget -= c2;
+				} else budget -= c2;
 			}
 		}
 	} else {
-		int n_skip = B0 - st.budget;
+		int n_skip = B0 - budget;
 		brk = replay_skip(imp, mm, max_skip, lane, n_skip);
-		st.budget = B0 - n_skip;
+		budget = B0 - n_skip;
 		const unsigned impb = brk >= 0 ? (imp & mask_below(brk)) : imp;
 		if (impb) {
 			const int L = 31 - __clz(impb);
-			st.max_f = __shfl_sync(FULL, sc, L);
-			st.max_j = jb - L;
-			st.vbest = __shfl_sync(FULL, vj, L);
+			max_f = __shfl_sync(FULL, sc, L);
+			max_j = jb - L;
+			vbest = __shfl_sync(FULL, vj, L);
 		}
-		if (brk >= 0) done = true;
+		if (brk >= 0) done = 1;
 	}
-	if (COUNT && brk >= 0) st.visited -= nwin - (brk + 1);
+	if (COUNT && brk >= 0) visited -= nwin - (brk + 1);
 	return done;
 }
 
-template <bool TABLE, bool COUNT>
+// FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
+template <bool TABLE, bool FULLV>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
-	// dynamic shared memory, indexed (not pointed into) so that accesses stay plain LDS/STS:
-	//   [0, FILL_WARPS*RING) int4 ring records | FILL_WARPS*RING ints of v | FILL_WARPS*tab_entries u16 gap costs
 	extern __shared__ int4 smem4[];
 	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	int *const smem_v = reinterpret_cast<int*>(smem4 + FILL_WARPS * RING);
-	unsigned short *const smem_tab = reinterpret_cast<unsigned short*>(smem_v + FILL_WARPS * RING);
-	const int rbase = wib * RING, tbase = wib * tab_entries;
+	const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem4);
+	const unsigned ring_w = sbase + SM_RING + wib * (RING * 16);
+	const unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
+	const unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
 
 	const int n_units = w.counters[CNT_UNITS];
 	const unsigned mdx = (unsigned)prm.max_dist_x;
@@ -378,7 +414,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
 	const int max_skip = prm.max_skip, bw = prm.bw;
 	const int B0 = max(max_skip + 1, 1);
-	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
+	const int max_iter = (FULLV && prm.max_iter > 0) ? prm.max_iter : 0x7fffffff;
 	const ulonglong2 *__restrict__ a = w.a;
 	int4 *wrec = w.wrec;
 	int32_t *vg = w.v, *t = w.t;
@@ -386,87 +422,103 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	bool have_tab = false;
 
 	for (;;) {
+		// next run from the device-side queue; the redux makes the index provably warp-uniform for the compiler
 		int u = 0;
 		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
-		u = __shfl_sync(FULL, u, 0);
+		u = __reduce_max_sync(FULL, u);
 		if (u >= n_units) break;
 		const Unit un = w.units[u];
 		const int s = un.start, e = un.start + un.len;
 		const float avgf = w.avg[un.read];
 		const double avg = (double)avgf;
-		ScanState st;
-		st.visited = 0;
+		long long visited = 0;
 
 		if (TABLE && (!have_tab || __float_as_uint(avgf) != tab_key)) {
 			__syncwarp();
 			for (int dd = lane; dd <= bw; dd += 32)
-				smem_tab[tbase + dd] = (unsigned short)(lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1));
+				sts_u16(tab_w + dd * 2, lin_cost(dd, avg) + ((31 - __clz(dd | 1)) >> 1));
 			tab_key = __float_as_uint(avgf);
 			have_tab = true;
 		}
 		// seed the ring with the run's first anchor (f = span, p = -1, v = span: chain.c:56,89-90 with no predecessor)
-		ulonglong2 nxt = a[s];
-		if (lane == 0) {
-			const int sp = (int)((nxt.y >> 32) & 0xff);
-			smem4[rbase + (s & (RING - 1))] = make_int4((int)(unsigned)nxt.x, (int)(unsigned)nxt.y, sp, -1);
-			smem_v[rbase + (s & (RING - 1))] = sp;
+		{
+			const ulonglong2 a0 = a[s];
+			const int sp = (int)((a0.y >> 32) & 0xff);
+			const unsigned slot = ring_w + (unsigned)(s & (RING - 1)) * 16u;
+			sts128<0>(slot, make_int4((int)(unsigned)a0.x, (int)(unsigned)a0.y, sp, -1));
+			sts32<SM_VRING>(slot, sp);
 		}
-		nxt = a[s + 1];
-		__syncwarp();
 
 		for (int i = s + 1; i < e; ++i) {
-			const unsigned xi = (unsigned)nxt.x;
-			const int qi = (int)(unsigned)nxt.y;
-			const int span = (int)((nxt.y >> 32) & 0xff);
-			if (i + 1 < e) nxt = a[i + 1];              // prefetch: not needed before the next iteration
-			const int jlo = max(s, i - max_iter);
-			st.max_f = span; st.max_j = -1; st.vbest = (int)0x80000000; st.budget = B0;
+			// anchors arrive in 32-aligned blocks: lane l loads a[blk + l] once, every step broadcasts its own from shared
+			if ((i & 31) == 0 || i == s + 1) {
+				__syncwarp();
+				const int idx = (i & ~31) + lane;
+				if (idx < e) {
+					const ulonglong2 ab = a[idx];
+					sts128<0>(abuf_w + lane * 16, make_int4((int)(unsigned)ab.x, (int)(unsigned)ab.y, (int)((ab.y >> 32) & 0xff), 0));
+				}
+				__syncwarp();
+			}
+			const int4 ai = lds128<0>(abuf_w + (unsigned)(i & 31) * 16u);
+			const unsigned xi = (unsigned)ai.x;
+			const int qi = ai.y, span = ai.z;
+			const int jlo = FULLV ? max(s, i - max_iter) : s;
+			int max_f = span, max_j = -1, vbest = (int)0x80000000, budget = B0;
+			bool far;
 
 			// chunk 0: anchors i-1 .. i-32 from the ring; no earlier chunk can have marked them
-			const int slot0 = rbase + ((i - 1 - lane) & (RING - 1));
-			int4 rj = smem4[slot0];
-			int vj = smem_v[slot0];
-			int cost;
-			{
-				const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-				cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
-			}
-			bool done = scan_chunk<COUNT>(st, i, i - 1, jlo, lane, rj, vj, false, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
+			const unsigned off0 = (unsigned)((i - 1 - lane) & (RING - 1)) * 16u;
+			int4 rj = lds128<0>(ring_w + off0);
+			int vj = lds32<SM_VRING>(ring_w + off0);
+			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+			int cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+			int done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
+			                             xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
 			if (!done && i - 33 >= jlo) {
+				if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
 				__syncwarp();
 				const int j1 = i - 33 - lane;
-				rj = smem4[slot0 ^ 32];
-				vj = smem_v[slot0 ^ 32];
+				rj = lds128<0>(ring_w + (off0 ^ 512u));
+				vj = lds32<SM_VRING>(ring_w + (off0 ^ 512u));
 				const bool mmem = j1 >= jlo && t[j1] == i;
-				{
-					const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-					cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
-				}
-				done = scan_chunk<COUNT>(st, i, i - 33, jlo, lane, rj, vj, mmem, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
-				// deeper chunks: the same records from global memory (this warp wrote them; L1/L2 hits)
+				dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+				cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+				done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
+				                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
+				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
 				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
+					if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 					__syncwarp();
 					const int j = jb - lane;
 					rj = make_int4(0, 0, 0, -1); vj = 0;
 					bool mg = false;
 					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
-					const int dd = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-					cost = TABLE ? (int)smem_tab[tbase + min(dd, bw)] : lin_cost(dd, avg) + ((dd ? 31 - __clz(dd) : 0) >> 1);
-					done = scan_chunk<COUNT>(st, i, jb, jlo, lane, rj, vj, mg, xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip, t);
+					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+					cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+					done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
+					                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
 				}
 			}
-			// chain.c:89-90
-			if (lane == 0) {
-				const int4 ri = make_int4((int)xi, qi, st.max_f, st.max_j);
-				const int vi = max(st.vbest, st.max_f);
-				const int slot = rbase + (i & (RING - 1));
-				smem4[slot] = ri; smem_v[slot] = vi;
-				wrec[i] = ri; vg[i] = vi;
+			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
+			{
+				const unsigned slot = ring_w + (unsigned)(i & (RING - 1)) * 16u;
+				sts128<0>(slot, make_int4((int)xi, qi, max_f, max_j));
+				sts32<SM_VRING>(slot, max(vbest, max_f));
 			}
 			__syncwarp();
+			// results go to global memory one 32-aligned block at a time (coalesced): deep windows and later kernels read them
+			if ((i & 31) == 31 || i == e - 1) {
+				const int idx = (i & ~31) + lane;
+				if (idx > s && idx <= i) {
+					const unsigned slot = ring_w + (unsigned)(idx & (RING - 1)) * 16u;
+					wrec[idx] = lds128<0>(slot);
+					vg[idx] = lds32<SM_VRING>(slot);
+				}
+			}
 		}
-		if (COUNT && lane == 0) atomicAdd(w.visited, (unsigned long long)st.visited);
+		if (FULLV && lane == 0) atomicAdd(w.visited, (unsigned long long)visited);
 	}
 }
 
@@ -892,20 +944,20 @@ static inline int blocks_for(long long items, int per_block, int cap)
 	return (int)b;
 }
 
-static int fill_smem_bytes(int tab_entries) { return FILL_WARPS * (RING * 20 + tab_entries * 2); }
+static int fill_smem_bytes(int tab_entries) { return SM_TAB + FILL_WARPS * tab_entries * 2; }
 static int fill_tab_entries(const mm2b200_params_t &prm)
 {	// 16-bit table of bw+1 gap costs per warp, only while it stays small (<= 2 KB per warp) and the costs fit
 	if (prm.bw < 0 || prm.bw > 1023) return 0;
 	return (prm.bw + 1 + 7) & ~7;
 }
 
-template <bool TABLE, bool COUNT>
+template <bool TABLE, bool FULLV>
 static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
 	const int smem = fill_smem_bytes(tab_entries);
-	auto kern = k_fill_fast<TABLE, COUNT>;
+	auto kern = k_fill_fast<TABLE, FULLV>;
 	static thread_local int occ_cache[4][2] = {{0, -1}, {0, -1}, {0, -1}, {0, -1}};
-	int *oc = occ_cache[(TABLE ? 2 : 0) + (COUNT ? 1 : 0)];
+	int *oc = occ_cache[(TABLE ? 2 : 0) + (FULLV ? 1 : 0)];
 	if (oc[1] != smem) {
 		cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
 		int occ = 0;
@@ -941,8 +993,9 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 	// match the device-side segment flag returns immediately.
 	if (!host_generic) {
 		const int te = fill_tab_entries(prm);
-		if (te) { if (cfg.count_visited) launch_fill_fast<true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false>(w, prm, cfg.sm_count, te, s); }
-		else { if (cfg.count_visited) launch_fill_fast<false, true>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false>(w, prm, cfg.sm_count, 0, s); }
+		const bool full = cfg.count_visited || prm.max_iter > 0;   // instrumented / max_iter-aware variant
+		if (te) { if (full) launch_fill_fast<true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false>(w, prm, cfg.sm_count, te, s); }
+		else { if (full) launch_fill_fast<false, true>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false>(w, prm, cfg.sm_count, 0, s); }
 		++n;
 	}
 	k_fill_generic<<<cfg.sm_count * cfg.fill_blocks_per_sm, 128, 0, s>>>(w, prm); ++n;
