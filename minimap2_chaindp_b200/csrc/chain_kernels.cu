@@ -684,7 +684,143 @@ static __device__ void radix_sort_kv_exact(uint64_t *kx, uint64_t *ky, int n, in
 	}
 }
 
-__global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, int32_t min_sc)
+// ascending in-place sort of z[0..n) by one warp (same flip-bitonic network as cta_sort_u64)
+static __device__ void warp_sort_u64(uint64_t *z, int n, int lane)
+{
+	for (int k = 2; (k >> 1) < n; k <<= 1) {
+		for (int i = lane; i < n; i += 32) {
+			const int l = i ^ (k - 1);
+			if (l > i && l < n) { const uint64_t x = z[i], y = z[l]; if (x > y) { z[i] = y; z[l] = x; } }
+		}
+		__syncwarp();
+		for (int j = k >> 2; j > 0; j >>= 1) {
+			for (int i = lane; i < n; i += 32) {
+				const int l = i ^ j;
+				if (l > i && l < n) { const uint64_t x = z[i], y = z[l]; if (x > y) { z[i] = y; z[l] = x; } }
+			}
+			__syncwarp();
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_tail_warp: chain.c:127-214 for reads with at most TW_CAP records, one WARP per read.  The predecessor words
+// and the successor / claim flags of the read are staged in shared memory, so the two pointer walks of the
+// reference (end -> peak, chain.c:151; peak -> chain start, chain.c:167-172) cost one LDS per step instead of a
+// dependent global load.  Larger reads are left to k_tail (CTA per read, global memory).
+// ---------------------------------------------------------------------------------------------------------
+#define TW_CAP 1024
+#define TW_WARPS 8
+
+__global__ void __launch_bounds__(TW_WARPS * 32) k_tail_warp(Workspace w, int32_t min_cnt, int32_t min_sc)
+{
+	__shared__ int s_rp_all[TW_WARPS][TW_CAP];          // rec[].p words; reused as head/tail of the radix replay
+	__shared__ uint8_t s_flag_all[TW_WARPS][TW_CAP];    // "has a successor", then "claimed"
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	int *s_rp = s_rp_all[wib];
+	uint8_t *s_flag = s_flag_all[wib];
+	const int gw = blockIdx.x * TW_WARPS + wib, nw = gridDim.x * TW_WARPS;
+	for (int r = gw; r < w.n_reads; r += nw) {
+		const int m = (int)w.new_i[r];
+		if (m > TW_CAP) continue;                         // k_tail's job
+		if (m == 0) { if (lane == 0) { w.n_u[r] = 0; w.n_v[r] = 0; } continue; }
+		const int base = (int)w.offs[r];
+		const int cap = (int)(w.offs[r + 1] - w.offs[r]);
+		const new_seed *rec = w.rec + base;
+		int32_t *members = w.members + base, *voff = w.voff + base, *order = w.order + base, *ooff = w.ooff + base;
+		uint64_t *cand = w.cand + base, *chain_u = w.chain_u + base, *wy = w.wy + base;
+
+		__syncwarp();
+		for (int i = lane; i < m; i += 32) { s_rp[i] = w.recp[base + i]; s_flag[i] = 0; }
+		__syncwarp();
+		// chain.c:128-131: who is somebody's predecessor
+		for (int i = lane; i < m; i += 32) { const int pp = s_rp[i]; if (pp >= 0) s_flag[pp >> 2] = 1; }
+		__syncwarp();
+		// chain.c:132-155: ends (bit0 set, no successor) -> peak (walk while bit1 set)
+		int n_end = 0;
+		for (int i0 = 0; i0 < m; i0 += 32) {
+			const int i = i0 + lane;
+			bool is_end = false;
+			int pp = 0;
+			if (i < m) { pp = s_rp[i]; is_end = (pp & 1) && !s_flag[i]; }
+			const unsigned em = __ballot_sync(FULL, is_end);
+			if (is_end) {
+				int j = i;
+				while (j >= 0 && (pp & 2)) { j = pp >> 2; if (j >= 0) pp = s_rp[j]; }
+				if (j < 0) j = i;
+				cand[n_end + __popc(em & lanemask_lt(lane))] = ((uint64_t)(uint32_t)rec[j].f << 32) | (uint32_t)j;
+			}
+			n_end += __popc(em);
+		}
+		if (n_end == 0) { if (lane == 0) { w.n_u[r] = 0; w.n_v[r] = 0; } continue; }
+		__syncwarp();
+		// chain.c:156-160: descending (peak score, peak index) == ascending sort read backwards
+		if (n_end > 1) warp_sort_u64(cand, n_end, lane);
+		for (int i = lane; i < m; i += 32) s_flag[i] = 0;        // from here on: claim marks
+		__syncwarp();
+
+		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains
+		int n_u = 0, n_v = 0;
+		if (lane == 0) {
+			for (int ii = n_end - 1; ii >= 0; --ii) {
+				const uint64_t c = cand[ii];
+				const int peak_sc = (int)(c >> 32);
+				int j = (int)(uint32_t)c;
+				const int n0 = n_v;
+				do {
+					if (n_v < cap) members[n_v] = j;
+					++n_v;
+					s_flag[j] = 1;
+					j = s_rp[j] >> 2;
+				} while (j >= 0 && !s_flag[j]);
+				const int cnt = n_v - n0;
+				bool keep = false;
+				uint64_t val = 0;
+				if (n_v > cap) { /* would overrun the reference's v[] as well (chain.c:168); drop */ }
+				else if (j < 0) {
+					if (cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)peak_sc << 32) | (uint32_t)cnt; }
+				} else {
+					const int d = peak_sc - rec[j].f;
+					if (d >= min_sc && cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)d << 32) | (uint32_t)cnt; }
+				}
+				if (keep) { chain_u[n_u] = val; voff[n_u] = n0; ++n_u; }
+				else n_v = n0;
+			}
+			w.n_u[r] = n_u; w.n_v[r] = n_v;
+		}
+		n_u = __shfl_sync(FULL, n_u, 0);
+		if (n_u == 0) continue;
+		__syncwarp();
+		// chain.c:199-204: w[k] = { x of the chain's first anchor, offset<<32 | k }, sorted by x only
+		uint64_t *wx = cand;
+		for (int k = lane; k < n_u; k += 32) {
+			const int cnt = (int)(uint32_t)chain_u[k];
+			wx[k] = rec[members[voff[k] + cnt - 1]].seed.x;
+			wy[k] = ((uint64_t)(uint32_t)voff[k] << 32) | (uint32_t)k;
+		}
+		__syncwarp();
+		if (n_u <= RS_MIN) {
+			// insertion sort is stable: rank = #{smaller} + #{equal and earlier}
+			for (int k = lane; k < n_u; k += 32) {
+				const uint64_t xk = wx[k];
+				int rank = 0;
+				for (int k2 = 0; k2 < n_u; ++k2) { const uint64_t x2 = wx[k2]; rank += (x2 < xk) || (x2 == xk && k2 < k); }
+				order[rank] = k;
+			}
+		} else {
+			if (lane == 0) radix_sort_kv_exact(wx, wy, n_u, w.stk + base, s_rp, s_rp + 256);
+			__syncwarp();
+			for (int k = lane; k < n_u; k += 32) order[k] = (int)(uint32_t)wy[k];
+		}
+		__syncwarp();
+		if (lane == 0) {
+			int acc = 0;
+			for (int i = 0; i < n_u; ++i) { ooff[i] = acc; acc += (int)(uint32_t)chain_u[order[i]]; }
+		}
+	}
+}
+
+__global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, int32_t min_sc, int32_t min_m)
 {
 	__shared__ int s_cnt, s_nu, s_nv;
 	__shared__ int s_head[256], s_tail[256];
@@ -693,10 +829,7 @@ __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, i
 		const int base = (int)w.offs[r];
 		const int cap = (int)(w.offs[r + 1] - w.offs[r]);
 		const int m = (int)w.new_i[r];
-		if (m == 0) {
-			if (tid == 0) { w.n_u[r] = 0; w.n_v[r] = 0; }
-			continue;
-		}
+		if (m <= min_m) continue;                           // k_tail_warp's job (it also handles m == 0)
 		const int32_t *rp = w.recp + base;
 		const new_seed *rec = w.rec + base;
 		uint8_t *succ = w.succ + base, *claimed = w.claimed + base;
@@ -1018,9 +1151,10 @@ int launch_split_records(const Workspace &w, cudaStream_t s)
 
 int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
-	k_tail<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w, prm.min_cnt, prm.min_sc);
+	k_tail_warp<<<blocks_for(w.n_reads, TW_WARPS, 148 * 16), TW_WARPS * 32, 0, s>>>(w, prm.min_cnt, prm.min_sc);
+	k_tail<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w, prm.min_cnt, prm.min_sc, TW_CAP);
 	k_scan_reads<<<1, 1024, 0, s>>>(w, 1);
-	return 2;
+	return 3;
 }
 
 int launch_gather(const Workspace &w, cudaStream_t s)
