@@ -138,6 +138,7 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 	for (auto &it : items) { *it.pp = cur; cur += align_up(it.bytes, 256); }
 	w.a = (const ulonglong2*)pa;
 	w.offs = (const int64_t*)poffs;
+	w.units_cap = (int32_t)(A / 2 + 1);
 	s.cap_anchors = A; s.cap_reads = R;
 	(void)ctx;
 	return MM2B200_OK;

@@ -26,7 +26,8 @@ struct Workspace {
 	int32_t n_reads, n_anchors;
 	// prep
 	float *avg;               // [n_reads] avg_qspan (chain.c:47)
-	Unit *units;              // [n_anchors/2 + 1]
+	Unit *units;              // [units_cap]: short runs from the front, long runs from the back
+	int32_t units_cap;
 	int32_t *counters;        // [CNT_N]
 	unsigned long long *visited; // [1] reference-visited (i,j) pairs (chain.c:59-88 loop bodies) of this sub-batch
 	// fill (chain.c:52-90)

@@ -20,6 +20,22 @@ namespace mm2b200 {
 static __device__ __forceinline__ unsigned lanemask_lt(int lane) { return (1u << lane) - 1u; }           // lane in [0,31]
 static __device__ __forceinline__ unsigned mask_below(int n) { return n >= 32 ? FULL : ((1u << n) - 1u); } // n in [0,32]
 
+// Run list: short runs are appended from the front, long ones (>= LONG_RUN anchors) from the back of units[], so the
+// fill kernels can start the long runs first (longest-processing-time-first keeps the tail of the kernel short).
+// The compiler aggregates the same-address atomics of a warp into one.
+#define LONG_RUN 128
+static __device__ __forceinline__ void emit_unit(const Workspace &w, int start, int len, int read)
+{
+	Unit u; u.start = start; u.len = len; u.read = read; u.pad = 0;
+	if (len >= LONG_RUN) w.units[w.units_cap - 1 - atomicAdd(&w.counters[CNT_LONG_UNITS], 1)] = u;
+	else w.units[atomicAdd(&w.counters[CNT_UNITS], 1)] = u;
+}
+// queue position q -> run: long runs first
+static __device__ __forceinline__ Unit fetch_unit(const Workspace &w, int q, int n_long)
+{
+	return q < n_long ? w.units[w.units_cap - 1 - q] : w.units[q - n_long];
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // k_prep: per read -- avg_qspan (chain.c:46-47), singleton defaults for f/p/v, mark reset, and the list of
 // independent runs (consecutive x gap <= max_dist_x; chain.c:58 makes st jump to the run start).
@@ -53,25 +69,13 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 			const unsigned below = smask & lanemask_lt(lane);
 			const int prev_start = below ? base + (31 - __clz(below)) : carry_start;
 			const bool emit = start && i != b && (i - prev_start) >= 2;   // this start closes the run [prev_start, i)
-			const unsigned emask = __ballot_sync(FULL, emit);
-			if (emask) {
-				int slot0 = 0;
-				if (lane == 0) slot0 = atomicAdd(&w.counters[CNT_UNITS], __popc(emask));
-				slot0 = __shfl_sync(FULL, slot0, 0);
-				if (emit) {
-					Unit u; u.start = prev_start; u.len = i - prev_start; u.read = r; u.pad = 0;
-					w.units[slot0 + __popc(emask & lanemask_lt(lane))] = u;
-				}
-			}
+			if (emit) emit_unit(w, prev_start, i - prev_start, r);
 			if (smask) carry_start = base + (31 - __clz(smask));
 		}
 		for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(FULL, sum, d);
 		multiseg = __any_sync(FULL, multiseg);
 		if (lane == 0) {
-			if (e - carry_start >= 2) {
-				Unit u; u.start = carry_start; u.len = e - carry_start; u.read = r; u.pad = 0;
-				w.units[atomicAdd(&w.counters[CNT_UNITS], 1)] = u;
-			}
+			if (e - carry_start >= 2) emit_unit(w, carry_start, e - carry_start, r);
 			// (float)sum_qspan / n  (chain.c:47): u64->float, int64->float, IEEE float divide
 			w.avg[r] = e > b ? __fdiv_rn(__ull2float_rn(sum), __ll2float_rn((long long)(e - b))) : 0.0f;
 			if (multiseg) atomicOr(&w.counters[CNT_MULTISEG], 1);
@@ -130,7 +134,8 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 	if (!need_generic) return;
 
 	const int lane = threadIdx.x & 31;
-	const int n_units = w.counters[CNT_UNITS];
+	const int n_long = w.counters[CNT_LONG_UNITS];
+	const int n_units = w.counters[CNT_UNITS] + n_long;
 	const unsigned mdx = (unsigned)prm.max_dist_x;
 	const int max_skip = prm.max_skip, bw = prm.bw;
 	const int max_iter = prm.max_iter > 0 ? prm.max_iter : 0x7fffffff;
@@ -143,7 +148,7 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
 		u = __shfl_sync(FULL, u, 0);
 		if (u >= n_units) break;
-		const Unit un = w.units[u];
+		const Unit un = fetch_unit(w, u, n_long);
 		const int s = un.start, e = un.start + un.len;
 		const double avg = (double)w.avg[un.read];
 		long long n_visited = 0;   // loop bodies the reference executes (chain.c:59-88), the metric's numerator
@@ -408,7 +413,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	const unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
 	const unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
 
-	const int n_units = w.counters[CNT_UNITS];
+	const int n_long = w.counters[CNT_LONG_UNITS];
+	const int n_units = w.counters[CNT_UNITS] + n_long;
 	const unsigned mdx = (unsigned)prm.max_dist_x;
 	const unsigned dq_max = (unsigned)(prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x);   // chain.c:64
 	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
@@ -427,7 +433,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
 		u = __reduce_max_sync(FULL, u);
 		if (u >= n_units) break;
-		const Unit un = w.units[u];
+		const Unit un = fetch_unit(w, u, n_long);
 		const int s = un.start, e = un.start + un.len;
 		const float avgf = w.avg[un.read];
 		const double avg = (double)avgf;
@@ -970,7 +976,7 @@ __global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
 	}
 	if (tid == 0) {
 		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
-		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS]; w.totals[3] = s_carry[2];
+		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS] + w.counters[CNT_LONG_UNITS]; w.totals[3] = s_carry[2];
 		w.totals[4] = (long long)*w.visited;
 	}
 }
