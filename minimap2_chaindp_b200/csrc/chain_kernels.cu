@@ -294,7 +294,7 @@ static __device__ __forceinline__ void sts_u16(unsigned addr, int v)
 // Returns nonzero when the scan of anchor i is finished (break, or the window ended inside the chunk).
 // `far` reports lanes whose mark lands beyond this chunk; the caller publishes those to t[] only if the scan goes on.
 template <bool COUNT>
-static __device__ __forceinline__ int scan_chunk(int &max_f, int &max_j, int &vbest, int &budget, long long &visited, bool &far,
+static __device__ __noinline__ int scan_chunk(int &max_f, int &max_j, int &vbest, int &budget, long long &visited, bool &far,
                                                   const int jb, const int jlo, const int lane,
                                                   const int4 rj, const int vj, const bool marked_mem,
                                                   const unsigned xi, const int qi, const int span,
@@ -400,8 +400,99 @@ static __device__ __forceinline__ int scan_chunk(int &max_f, int &max_j, int &vb
 	return done;
 }
 
+// The common case of a chunk as straight-line code: at most one IMPROVE lane and a window that is exact per lane
+// (max_dist_x < 2^27, so 32 lanes can never wrap the low 32 bits of x).  Everything is computed with selects; the only
+// branch leaves for the general routine above when several lanes before the chunk maximum beat the running maximum.
+template <bool COUNT, bool WIDE>
+static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, int &vbest, int &budget, long long &visited, bool &far,
+                                                       const int jb, const int jlo, const int lane,
+                                                       const int4 rj, const int vj, const bool marked_mem,
+                                                       const unsigned xi, const int qi, const int span,
+                                                       const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
+                                                       const int dd, const int cost, const int B0, const int max_skip)
+{
+	const int j = jb - lane;
+	const unsigned dr = xi - (unsigned)rj.x;
+	const int dq = qi - rj.y;
+	const bool inw = (j >= jlo) && (dr <= mdx);
+	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
+	const int sc = min(min(dq, (int)dr), span) - cost + rj.z;
+	const int scx = skip ? (int)0x80000000 : sc;
+	const int pj = rj.w;
+	const unsigned kt = (unsigned)(jb - pj);
+	const bool mk = !skip && pj >= 0;
+	const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << (kt & 31u)) : 0u);
+	const int M = __reduce_max_sync(FULL, scx);
+	const bool all_in = __all_sync(FULL, inw);
+	const unsigned eq = __ballot_sync(FULL, scx == M);
+	const unsigned gt = __ballot_sync(FULL, scx > max_f);
+	const unsigned low = eq & (0u - eq);
+	if (WIDE)                               // window too wide for the per-lane test: general routine (prefix of in-window lanes)
+		return scan_chunk<COUNT>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, marked_mem,
+		                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
+	far = mk && kt >= 32u;
+	const bool marked = ((mloc >> lane) & 1u) || marked_mem;
+	if ((gt & (low - 1u)) != 0u) {
+		// several lanes before the chunk maximum beat the running maximum => at least two IMPROVE lanes:
+		// exclusive prefix-max scan for the exact set, then the general segment-by-segment replay
+		int pm = scx;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const int o = __shfl_up_sync(FULL, pm, d);
+			if (lane >= d) pm = max(pm, o);
+		}
+		int ex = __shfl_up_sync(FULL, pm, 1);
+		ex = lane == 0 ? max_f : max(ex, max_f);
+		const unsigned impm = __ballot_sync(FULL, scx > ex);
+		const unsigned mmm = __ballot_sync(FULL, marked && !skip) & ~impm;
+		int n_skip = B0 - budget;
+		const int brk = replay_skip(impm, mmm, max_skip, lane, n_skip);
+		budget = B0 - n_skip;
+		const unsigned impb = brk >= 0 ? (impm & mask_below(brk)) : impm;
+		if (impb) {
+			const int Lb = 31 - __clz(impb);
+			max_f = __shfl_sync(FULL, sc, Lb);
+			max_j = jb - Lb;
+			vbest = __shfl_sync(FULL, vj, Lb);
+		}
+		if (COUNT) {
+			const int nwin = __popc(__ballot_sync(FULL, inw));
+			visited += nwin;
+			if (brk >= 0) visited -= nwin - (brk + 1);
+		}
+		return (brk >= 0 || !all_in) ? 1 : 0;
+	}
+	const unsigned imp = M > max_f ? low : 0u;            // the only IMPROVE lane, if any
+	const unsigned below = imp - 1u;                      // lanes visited before it (all lanes when there is none)
+	const unsigned mm = __ballot_sync(FULL, marked && !skip) & ~imp;
+	const unsigned seg1 = mm & below, seg2 = mm & ~(imp | below);
+	const int c1 = __popc(seg1), c2 = __popc(seg2);
+	const bool brk1 = c1 >= budget;                       // break before the IMPROVE lane (chain.c:84-85)
+	const bool take = imp != 0u && !brk1;
+	const int L = __popc(below) & 31;
+	const int vL = __shfl_sync(FULL, vj, L);
+	const int b1 = budget - c1, b2 = min(b1 + 1, B0);     // chain.c:82: if (n_skip > 0) --n_skip
+	const bool brk2 = take && c2 >= b2;
+	if (COUNT) {
+		const int nwin = __popc(__ballot_sync(FULL, inw));
+		visited += nwin;
+		if (brk1 || brk2) {
+			const unsigned seg = brk1 ? seg1 : seg2;
+			const int need = brk1 ? budget : b2;
+			const int c = __popc(seg & (lanemask_lt(lane) | (1u << lane)));
+			const int brk = __ffs(__ballot_sync(FULL, ((seg >> lane) & 1u) && c == need)) - 1;
+			visited -= nwin - (brk + 1);
+		}
+	}
+	max_f = take ? M : max_f;
+	max_j = take ? jb - L : max_j;
+	vbest = take ? vL : vbest;
+	budget = take ? b2 - c2 : b1;
+	return (brk1 || brk2 || !all_in) ? 1 : 0;
+}
+
 // FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
-template <bool TABLE, bool FULLV>
+template <bool TABLE, bool FULLV, bool WIDE>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
 	extern __shared__ int4 smem4[];
@@ -479,8 +570,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			int vj = lds32<SM_VRING>(ring_w + off0);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 			int cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
-			int done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
-			                             xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
+			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
+			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 			if (!done && i - 33 >= jlo) {
 				if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
@@ -491,8 +582,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				const bool mmem = j1 >= jlo && t[j1] == i;
 				dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 				cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
-				done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
-				                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
+				done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
+				                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
 				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
 					if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
@@ -503,8 +594,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
 					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 					cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
-					done = scan_chunk<FULLV>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
-					                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
+					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
+					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				}
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
@@ -513,7 +604,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				sts128<0>(slot, make_int4((int)xi, qi, max_f, max_j));
 				sts32<SM_VRING>(slot, max(vbest, max_f));
 			}
-			__syncwarp();
+			// (no warp sync needed: every lane stored the same words, so a later load by any lane sees at least its own store)
 			// results go to global memory one 32-aligned block at a time (coalesced): deep windows and later kernels read them
 			if ((i & 31) == 31 || i == e - 1) {
 				const int idx = (i & ~31) + lane;
@@ -1090,13 +1181,13 @@ static int fill_tab_entries(const mm2b200_params_t &prm)
 	return (prm.bw + 1 + 7) & ~7;
 }
 
-template <bool TABLE, bool FULLV>
+template <bool TABLE, bool FULLV, bool WIDE>
 static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
 	const int smem = fill_smem_bytes(tab_entries);
-	auto kern = k_fill_fast<TABLE, FULLV>;
-	static thread_local int occ_cache[4][2] = {{0, -1}, {0, -1}, {0, -1}, {0, -1}};
-	int *oc = occ_cache[(TABLE ? 2 : 0) + (FULLV ? 1 : 0)];
+	auto kern = k_fill_fast<TABLE, FULLV, WIDE>;
+	static thread_local int occ_cache[2] = {0, -1};   // one cache per template instance
+	int *oc = occ_cache;
 	if (oc[1] != smem) {
 		cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
 		int occ = 0;
@@ -1133,8 +1224,10 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 	if (!host_generic) {
 		const int te = fill_tab_entries(prm);
 		const bool full = cfg.count_visited || prm.max_iter > 0;   // instrumented / max_iter-aware variant
-		if (te) { if (full) launch_fill_fast<true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false>(w, prm, cfg.sm_count, te, s); }
-		else { if (full) launch_fill_fast<false, true>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false>(w, prm, cfg.sm_count, 0, s); }
+		if (prm.max_dist_x >= (1 << 27)) {                         // per-lane window test not exact: general chunk routine only
+			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, s);
+		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, s); }
+		else { if (full) launch_fill_fast<false, true, false>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false, false>(w, prm, cfg.sm_count, 0, s); }
 		++n;
 	}
 	k_fill_generic<<<cfg.sm_count * cfg.fill_blocks_per_sm, 128, 0, s>>>(w, prm); ++n;
