@@ -500,9 +500,11 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem4);
-	const unsigned ring_w = sbase + SM_RING + wib * (RING * 16);
-	const unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
-	const unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
+	unsigned ring_w = sbase + SM_RING + wib * (RING * 16);
+	unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
+	unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
+	// opaque to the optimiser: keep the three per-warp base addresses in registers instead of re-deriving them per access
+	asm volatile("" : "+r"(ring_w), "+r"(abuf_w), "+r"(tab_w));
 
 	const int n_long = w.counters[CNT_LONG_UNITS];
 	const int n_units = w.counters[CNT_UNITS] + n_long;
