@@ -548,17 +548,17 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			sts32<SM_VRING>(slot, sp);
 		}
 
-		for (int i = s + 1; i < e; ++i) {
-			// anchors arrive in 32-aligned blocks: lane l loads a[blk + l] once, every step broadcasts its own from shared
-			if ((i & 31) == 0 || i == s + 1) {
-				__syncwarp();
-				const int idx = (i & ~31) + lane;
-				if (idx < e) {
-					const ulonglong2 ab = a[idx];
-					sts128<0>(abuf_w + lane * 16, make_int4((int)(unsigned)ab.x, (int)(unsigned)ab.y, (int)((ab.y >> 32) & 0xff), 0));
-				}
-				__syncwarp();
+		// anchors are processed in 32-aligned blocks: lane l loads a[blk + l] once, every step broadcasts its own from
+		// shared memory, and the block's results go back to global memory with one coalesced store per lane
+		for (int blk = (s + 1) & ~31; blk < e; blk += 32) {
+			__syncwarp();
+			if (blk + lane < e) {
+				const ulonglong2 ab = a[blk + lane];
+				sts128<0>(abuf_w + lane * 16, make_int4((int)(unsigned)ab.x, (int)(unsigned)ab.y, (int)((ab.y >> 32) & 0xff), 0));
 			}
+			__syncwarp();
+			const int i1 = min(blk + 32, e);
+		for (int i = max(blk, s + 1); i < i1; ++i) {
 			const int4 ai = lds128<0>(abuf_w + (unsigned)(i & 31) * 16u);
 			const unsigned xi = (unsigned)ai.x;
 			const int qi = ai.y, span = ai.z;
@@ -607,10 +607,11 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				sts32<SM_VRING>(slot, max(vbest, max_f));
 			}
 			// (no warp sync needed: every lane stored the same words, so a later load by any lane sees at least its own store)
-			// results go to global memory one 32-aligned block at a time (coalesced): deep windows and later kernels read them
-			if ((i & 31) == 31 || i == e - 1) {
-				const int idx = (i & ~31) + lane;
-				if (idx > s && idx <= i) {
+		}
+			// flush the block (deep windows and the later kernels read the records from global memory)
+			{
+				const int idx = blk + lane;
+				if (idx > s && idx < i1) {
 					const unsigned slot = ring_w + (unsigned)(idx & (RING - 1)) * 16u;
 					wrec[idx] = lds128<0>(slot);
 					vg[idx] = lds32<SM_VRING>(slot);
