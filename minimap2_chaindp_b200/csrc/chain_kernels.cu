@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			int4 rj = lds128<0>(ring_w + off0);
 			int vj = lds32<SM_VRING>(ring_w + off0);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-			int cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+			int cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
 			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 			if (!done && i - 33 >= jlo) {
@@ -583,7 +583,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				vj = lds32<SM_VRING>(ring_w + (off0 ^ 512u));
 				const bool mmem = j1 >= jlo && t[j1] == i;
 				dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-				cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+				cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 				done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
 				                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
@@ -595,7 +595,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 					bool mg = false;
 					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
 					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-					cost = TABLE ? lds_u16(tab_w + (unsigned)min(dd0, bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
 					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				}
