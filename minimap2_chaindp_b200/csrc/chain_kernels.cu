@@ -859,36 +859,51 @@ __global__ void __launch_bounds__(TW_WARPS * 32) k_tail_warp(Workspace w, int32_
 		for (int i = lane; i < m; i += 32) s_flag[i] = 0;        // from here on: claim marks
 		__syncwarp();
 
-		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains
+		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains.  The walk is sequential by
+		// definition, but most chains link consecutive records (p[k] == k-1), so the warp takes a whole run of
+		// consecutively linked, unclaimed records per iteration: lane l looks at record j-l, the run ends at the first
+		// lane whose record is not the predecessor of the previous one (or is already claimed).
 		int n_u = 0, n_v = 0;
-		if (lane == 0) {
-			for (int ii = n_end - 1; ii >= 0; --ii) {
-				const uint64_t c = cand[ii];
-				const int peak_sc = (int)(c >> 32);
-				int j = (int)(uint32_t)c;
-				const int n0 = n_v;
-				do {
-					if (n_v < cap) members[n_v] = j;
-					++n_v;
-					s_flag[j] = 1;
-					j = s_rp[j] >> 2;
-				} while (j >= 0 && !s_flag[j]);
-				const int cnt = n_v - n0;
-				bool keep = false;
-				uint64_t val = 0;
-				if (n_v > cap) { /* would overrun the reference's v[] as well (chain.c:168); drop */ }
-				else if (j < 0) {
-					if (cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)peak_sc << 32) | (uint32_t)cnt; }
-				} else {
-					const int d = peak_sc - rec[j].f;
-					if (d >= min_sc && cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)d << 32) | (uint32_t)cnt; }
+		for (int ii = n_end - 1; ii >= 0; --ii) {
+			const uint64_t c = cand[ii];
+			const int peak_sc = (int)(c >> 32);
+			int j = (int)(uint32_t)c;
+			const int n0 = n_v;
+			bool first = true;                                   // do { } while: the peak is taken even if claimed
+			for (;;) {
+				const int cl = j - lane;
+				const int wl = cl >= 0 ? s_rp[cl] : -4;
+				const bool claimed_l = cl >= 0 ? (s_flag[cl] != 0) : true;
+				const int wprev = __shfl_up_sync(FULL, wl, 1);
+				const bool ok = lane == 0 ? true : ((wprev >> 2) == cl && cl >= 0 && !claimed_l);
+				(void)first;
+				const int run = __ffs(~__ballot_sync(FULL, ok)) - 1;   // >= 1 (lane 0 is always ok); 32 if all lanes link
+				const int take = run < 0 ? 32 : run;
+				if (lane < take) {
+					if (n_v + lane < cap) members[n_v + lane] = cl;
+					s_flag[cl] = 1;
 				}
-				if (keep) { chain_u[n_u] = val; voff[n_u] = n0; ++n_u; }
-				else n_v = n0;
+				n_v += take;
+				const int jn = __shfl_sync(FULL, wl, take - 1) >> 2;   // predecessor of the last record taken
+				__syncwarp();
+				first = false;
+				j = jn;
+				if (jn < 0 || s_flag[jn]) break;
 			}
-			w.n_u[r] = n_u; w.n_v[r] = n_v;
+			const int cnt = n_v - n0;
+			bool keep = false;
+			uint64_t val = 0;
+			if (n_v > cap) { /* would overrun the reference's v[] as well (chain.c:168); drop */ }
+			else if (j < 0) {
+				if (cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)peak_sc << 32) | (uint32_t)cnt; }
+			} else {
+				const int d = peak_sc - rec[j].f;
+				if (d >= min_sc && cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)d << 32) | (uint32_t)cnt; }
+			}
+			if (keep) { if (lane == 0) { chain_u[n_u] = val; voff[n_u] = n0; } ++n_u; }
+			else n_v = n0;
 		}
-		n_u = __shfl_sync(FULL, n_u, 0);
+		if (lane == 0) { w.n_u[r] = n_u; w.n_v[r] = n_v; }
 		if (n_u == 0) continue;
 		__syncwarp();
 		// chain.c:199-204: w[k] = { x of the chain's first anchor, offset<<32 | k }, sorted by x only
