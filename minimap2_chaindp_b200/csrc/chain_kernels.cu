@@ -3,7 +3,7 @@
 // Stage map (reference lines -> kernel):
 //   chain.c:46-47  avg_qspan, run splitting          k_prep            warp per read
 //   chain.c:52-90  DP fill f/p/v with the max_skip early exit       k_fill<GENERIC>   warp per run, persistent
-//   chain.c:93-122 compaction to new_seed[] + new indices           k_first_ref, k_compact
+//   chain.c:93-122 compaction to new_seed[] + new indices           k_compact         warp per read
 //   chain.c:127-180 chain ends, peaks, ordering, backtrack, filters k_tail            CTA per read
 //   chain.c:186-214 gather + first-anchor-x order                   k_tail (order), k_scan_reads, k_gather
 //
@@ -625,15 +625,6 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 // ---------------------------------------------------------------------------------------------------------
 // compaction (chain.c:93-122)
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_first_ref(Workspace w)
-{	// r(k) = min{ i : p[i] == k } into t[] (preset to 0x7f7f7f7f)
-	const int n = w.n_anchors;
-	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		const int pi = w.wrec[i].w;
-		if (pi >= 0) atomicMin(&w.t[pi], i);
-	}
-}
-
 static __device__ __forceinline__ void store_rec(new_seed *dst, ulonglong2 seed, int32_t p, int32_t f)
 {
 	unsigned long long *q = reinterpret_cast<unsigned long long*>(dst);
@@ -657,13 +648,20 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 			int pi = -1, vi = 0, fi = 0;
 			if (valid) { const int4 ri = w.wrec[i]; pi = ri.w; fi = ri.z; vi = w.v[i]; }
 			const bool E = valid && (vi >= min_sc || pi >= 0);                  // chain.c:109
-			bool late = false;
+			// chain.c:93-107: a predecessor that was not emitted on its own is emitted by its FIRST referencer.  Anchors are
+			// visited in increasing i, so "first" = no earlier tile emitted it (newid still -1) and the lowest lane of this
+			// tile among those that name it.
+			if (valid) w.newid[i] = -1;
+			__syncwarp();
+			bool cand = false;
 			int vp = 0, fp = 0;
 			if (pi >= 0) {
 				const int4 rp = w.wrec[pi];
 				vp = w.v[pi]; fp = rp.z;
-				late = !(vp >= min_sc || rp.w >= 0) && w.t[pi] == i;           // chain.c:93-107: first referencer emits it
+				cand = !(vp >= min_sc || rp.w >= 0) && w.newid[pi] < 0;
 			}
+			const unsigned grp = __match_any_sync(FULL, cand ? pi : -1 - lane);
+			const bool late = cand && (__ffs(grp) - 1 == lane);
 			const int cnt = (E ? 1 : 0) + (late ? 1 : 0);
 			int incl = cnt;
 #pragma unroll
@@ -1254,10 +1252,8 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 
 int launch_compact(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
-	cudaMemsetAsync(w.t, 0x7f, (size_t)w.n_anchors * sizeof(int32_t), s);
-	k_first_ref<<<blocks_for(w.n_anchors, 256 * 4, 148 * 16), 256, 0, s>>>(w);
 	k_compact<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.min_sc);
-	return 2;
+	return 1;
 }
 
 int launch_split_records(const Workspace &w, cudaStream_t s)
