@@ -61,8 +61,10 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 			if (valid) {
 				const int span = (int)((ai.y >> 32) & 0xff);
 				sum += (unsigned)span;
-				w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1);   // singleton defaults: f = span, p = -1
-				w.v[i] = span; w.t[i] = -1;
+				// f = span, p = -1, v = span for every anchor that starts a run (singletons are finished by this; the
+				// fill kernels write all other anchors of a run themselves, so those are not touched here)
+				if (start) { w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1); w.v[i] = span; }
+				w.t[i] = -1;
 				if ((ai.y >> 48) & 0xff) multiseg = 1;
 			}
 			const unsigned smask = __ballot_sync(FULL, start);
