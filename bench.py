@@ -319,6 +319,14 @@ def main():
     int_peak_alu = ctx.int_peak(0)
     int_achieved = pairs_step * INT_OPS_PER_PAIR / (fill_ms_per_step * 1e-3) if fill_ms_per_step > 0 else 0.0
 
+    traffic = None   # dram bytes of one k_fill launch from the committed ncu capture of this exact workload, else null
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_fill_traffic.json")))
+        if tj.get("workload") == spec.name and int(tj.get("reads", 0)) == n_reads:
+            traffic = int(tj["dram_bytes_per_launch"])
+    except Exception:
+        traffic = None
+
     line = None
     if rank == 0:
         line = {
@@ -339,7 +347,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"kernel": "k_fill", "bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": hbm_achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": hbm_achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": n_anchors * BYTES_PER_ANCHOR, "ms_per_launch": fill_ms_per_step,
                          "note": "k_fill is integer-issue bound, not HBM bound (see roofline_issue); 40 B/anchor algorithmic"},
             "roofline_issue": {"kernel": "k_fill", "bound": "int-issue", "achieved": int_achieved / 1e12, "peak": int_peak_mix / 1e12,

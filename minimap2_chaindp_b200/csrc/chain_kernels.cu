@@ -1042,6 +1042,7 @@ __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, i
 }
 
 // exclusive scans over reads: n_u -> u_off, n_v -> b_off, new_i -> rec_off; totals
+#define SCAN_ITEMS 8
 __global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
 {
 	__shared__ long long s_part[3][32];
@@ -1049,12 +1050,19 @@ __global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
 	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	if (tid < 3) s_carry[tid] = 0;
 	__syncthreads();
-	for (int base = 0; base < w.n_reads; base += 1024) {
-		const int r = base + tid;
+	for (int base = 0; base < w.n_reads; base += 1024 * SCAN_ITEMS) {
+		const int r0 = base + tid * SCAN_ITEMS;          // this thread owns SCAN_ITEMS consecutive reads
+		int item[3][SCAN_ITEMS];
 		long long val[3] = {0, 0, 0}, incl[3];
-		if (r < w.n_reads) {
-			if (have_tail) { val[0] = w.n_u[r]; val[1] = w.n_v[r]; }
-			val[2] = w.new_i[r];
+#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; ++k) {
+			const int r = r0 + k;
+			item[0][k] = item[1][k] = item[2][k] = 0;
+			if (r < w.n_reads) {
+				if (have_tail) { item[0][k] = w.n_u[r]; item[1][k] = w.n_v[r]; }
+				item[2][k] = (int)w.new_i[r];
+			}
+			val[0] += item[0][k]; val[1] += item[1][k]; val[2] += item[2][k];
 		}
 #pragma unroll
 		for (int q = 0; q < 3; ++q) {
@@ -1078,7 +1086,12 @@ __global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
 		long long ex[3];
 #pragma unroll
 		for (int q = 0; q < 3; ++q) ex[q] = s_carry[q] + (wid ? s_part[q][wid - 1] : 0) + incl[q] - val[q];
-		if (r < w.n_reads) { w.u_off[r] = ex[0]; w.b_off[r] = ex[1]; w.rec_off[r] = ex[2]; }
+#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; ++k) {
+			const int r = r0 + k;
+			if (r < w.n_reads) { w.u_off[r] = ex[0]; w.b_off[r] = ex[1]; w.rec_off[r] = ex[2]; }
+			ex[0] += item[0][k]; ex[1] += item[1][k]; ex[2] += item[2][k];
+		}
 		__syncthreads();
 		if (tid < 3) s_carry[tid] += s_part[tid][31];
 		__syncthreads();
