@@ -34,7 +34,7 @@ struct Workspace {
 	int4 *wrec;               // [n_anchors] working record {low32(x), qpos, f, p}; p is a batch-wide index (or -1)
 	int32_t *v;               // [n_anchors] peak score along the best chain ending here (chain.c:90)
 	int32_t *f, *p;           // [n_anchors] debug export only (fill_batch with f/p/v requested)
-	int32_t *t;               // [n_anchors] marks during the fill, then "first referencer" during compaction
+	int32_t *t;               // [n_anchors] marks of the fill that land beyond the current 32-lane chunk (tag = i)
 	// compaction (chain.c:93-122)
 	int32_t *newid;           // [n_anchors] old -> new index within the read, -1 = dropped
 	new_seed *rec;            // [n_anchors] records of read r at rec + offs[r]
