@@ -125,7 +125,7 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 		{ (void**)&w.voff, 4 * A }, { (void**)&w.order, 4 * A }, { (void**)&w.ooff, 4 * A }, { (void**)&w.stk, 4 * A },
 		{ (void**)&w.n_u, 4 * R }, { (void**)&w.n_v, 4 * R },
 		{ (void**)&w.u_off, 8 * (R + 1) }, { (void**)&w.b_off, 8 * (R + 1) }, { (void**)&w.rec_off, 8 * (R + 1) },
-		{ (void**)&w.totals, 8 * 8 }, { (void**)&w.u_out, 8 * A }, { (void**)&w.b_out, 16 * A },
+		{ (void**)&w.totals, 8 * 8 }, { (void**)&w.scan_part, 8 * 3 * (R / 1024 + 2) }, { (void**)&w.u_out, 8 * A }, { (void**)&w.b_out, 16 * A },
 	};
 	size_t total = 0;
 	for (auto &it : items) total += align_up(it.bytes, 256);

@@ -56,6 +56,7 @@ struct Workspace {
 	int64_t *u_off, *b_off;   // [n_reads+1]
 	int64_t *totals;          // [8]: sum n_u, sum n_v, n_units, sum new_i, visited pairs
 	int64_t *rec_off;         // [n_reads+1] (fill_batch only)
+	long long *scan_part;     // [3 * (n_reads/1024 + 2)] per-block sums of the read scans
 	uint64_t *u_out;          // [n_anchors]
 	ulonglong2 *b_out;        // [n_anchors]
 	new_seed *rec_out;        // aliases b_out/u_out region? no: own buffer [n_anchors] (fill_batch only, lazily allocated)

@@ -5,7 +5,7 @@
 //   chain.c:52-90  DP fill f/p/v with the max_skip early exit       k_fill<GENERIC>   warp per run, persistent
 //   chain.c:93-122 compaction to new_seed[] + new indices           k_compact         warp per read
 //   chain.c:127-180 chain ends, peaks, ordering, backtrack, filters k_tail            CTA per read
-//   chain.c:186-214 gather + first-anchor-x order                   k_tail (order), k_scan_reads, k_gather
+//   chain.c:186-214 gather + first-anchor-x order                   k_tail* (order), k_scan_*, k_gather
 //
 // Everything is integer work on 16-byte anchors; nothing here is GEMM-shaped, so no tensor cores.  The one
 // floating-point expression, (int)(dd * .01 * avg_qspan) (chain.c:73,78), is evaluated with explicit
@@ -1041,66 +1041,99 @@ __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, i
 	}
 }
 
-// exclusive scans over reads: n_u -> u_off, n_v -> b_off, new_i -> rec_off; totals
-#define SCAN_ITEMS 8
-__global__ void __launch_bounds__(1024) k_scan_reads(Workspace w, int have_tail)
-{
-	__shared__ long long s_part[3][32];
-	__shared__ long long s_carry[3];
-	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-	if (tid < 3) s_carry[tid] = 0;
-	__syncthreads();
-	for (int base = 0; base < w.n_reads; base += 1024 * SCAN_ITEMS) {
-		const int r0 = base + tid * SCAN_ITEMS;          // this thread owns SCAN_ITEMS consecutive reads
-		int item[3][SCAN_ITEMS];
-		long long val[3] = {0, 0, 0}, incl[3];
+// exclusive scans over reads: n_u -> u_off, n_v -> b_off, new_i -> rec_off; totals.  Three small launches (per-block
+// sums, scan of the block sums, per-block scan + offset) so that every access is coalesced and all SMs take part.
+static __device__ __forceinline__ void block_scan3(long long (&x)[3], long long (&total)[3], long long (*s_part)[32])
+{	// inclusive scan of x[] across the 1024 threads of the block; total[] = block sums
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
-		for (int k = 0; k < SCAN_ITEMS; ++k) {
-			const int r = r0 + k;
-			item[0][k] = item[1][k] = item[2][k] = 0;
-			if (r < w.n_reads) {
-				if (have_tail) { item[0][k] = w.n_u[r]; item[1][k] = w.n_v[r]; }
-				item[2][k] = (int)w.new_i[r];
-			}
-			val[0] += item[0][k]; val[1] += item[1][k]; val[2] += item[2][k];
-		}
+	for (int q = 0; q < 3; ++q) {
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, x[q], d); if (lane >= d) x[q] += o; }
+		if (lane == 31) s_part[q][wid] = x[q];
+	}
+	__syncthreads();
+	if (wid == 0) {
 #pragma unroll
 		for (int q = 0; q < 3; ++q) {
-			long long x = val[q];
+			long long y = s_part[q][lane];
 #pragma unroll
-			for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, x, d); if (lane >= d) x += o; }
-			incl[q] = x;
-			if (lane == 31) s_part[q][wid] = x;
+			for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, y, d); if (lane >= d) y += o; }
+			s_part[q][lane] = y;
+		}
+	}
+	__syncthreads();
+#pragma unroll
+	for (int q = 0; q < 3; ++q) { if (wid) x[q] += s_part[q][wid - 1]; total[q] = s_part[q][31]; }
+}
+
+static __device__ __forceinline__ void load_read_counts(const Workspace &w, int r, int have_tail, long long (&val)[3])
+{
+	val[0] = val[1] = val[2] = 0;
+	if (r < w.n_reads) {
+		if (have_tail) { val[0] = w.n_u[r]; val[1] = w.n_v[r]; }
+		val[2] = w.new_i[r];
+	}
+}
+
+__global__ void __launch_bounds__(1024) k_scan_block_sums(Workspace w, int have_tail)
+{
+	__shared__ long long s_part[3][32];
+	long long val[3], tot[3];
+	load_read_counts(w, blockIdx.x * 1024 + threadIdx.x, have_tail, val);
+	block_scan3(val, tot, s_part);
+	if (threadIdx.x == 0) { w.scan_part[3 * blockIdx.x] = tot[0]; w.scan_part[3 * blockIdx.x + 1] = tot[1]; w.scan_part[3 * blockIdx.x + 2] = tot[2]; }
+}
+
+__global__ void __launch_bounds__(1024) k_scan_block_offsets(Workspace w, int n_blocks)
+{	// one CTA: exclusive scan of the block sums in place; totals
+	__shared__ long long s_part[3][32];
+	__shared__ long long s_carry[3];
+	if (threadIdx.x < 3) s_carry[threadIdx.x] = 0;
+	__syncthreads();
+	for (int base = 0; base < n_blocks; base += 1024) {
+		const int c = base + threadIdx.x;
+		long long val[3] = {0, 0, 0}, x[3], tot[3];
+		if (c < n_blocks) { val[0] = w.scan_part[3 * c]; val[1] = w.scan_part[3 * c + 1]; val[2] = w.scan_part[3 * c + 2]; }
+		x[0] = val[0]; x[1] = val[1]; x[2] = val[2];
+		block_scan3(x, tot, s_part);
+		if (c < n_blocks) {
+#pragma unroll
+			for (int q = 0; q < 3; ++q) w.scan_part[3 * c + q] = s_carry[q] + x[q] - val[q];
 		}
 		__syncthreads();
-		if (wid == 0) {
-#pragma unroll
-			for (int q = 0; q < 3; ++q) {
-				long long x = s_part[q][lane];
-#pragma unroll
-				for (int d = 1; d < 32; d <<= 1) { const long long o = __shfl_up_sync(FULL, x, d); if (lane >= d) x += o; }
-				s_part[q][lane] = x;   // inclusive over warps
-			}
-		}
-		__syncthreads();
-		long long ex[3];
-#pragma unroll
-		for (int q = 0; q < 3; ++q) ex[q] = s_carry[q] + (wid ? s_part[q][wid - 1] : 0) + incl[q] - val[q];
-#pragma unroll
-		for (int k = 0; k < SCAN_ITEMS; ++k) {
-			const int r = r0 + k;
-			if (r < w.n_reads) { w.u_off[r] = ex[0]; w.b_off[r] = ex[1]; w.rec_off[r] = ex[2]; }
-			ex[0] += item[0][k]; ex[1] += item[1][k]; ex[2] += item[2][k];
-		}
-		__syncthreads();
-		if (tid < 3) s_carry[tid] += s_part[tid][31];
+		if (threadIdx.x < 3) s_carry[threadIdx.x] += tot[threadIdx.x];
 		__syncthreads();
 	}
-	if (tid == 0) {
+	if (threadIdx.x == 0) {
 		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
 		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS] + w.counters[CNT_LONG_UNITS]; w.totals[3] = s_carry[2];
 		w.totals[4] = (long long)*w.visited;
 	}
+}
+
+__global__ void __launch_bounds__(1024) k_scan_apply(Workspace w, int have_tail)
+{
+	__shared__ long long s_part[3][32];
+	const int r = blockIdx.x * 1024 + threadIdx.x;
+	long long val[3], x[3], tot[3];
+	load_read_counts(w, r, have_tail, val);
+	x[0] = val[0]; x[1] = val[1]; x[2] = val[2];
+	block_scan3(x, tot, s_part);
+	if (r < w.n_reads) {
+		w.u_off[r] = w.scan_part[3 * blockIdx.x] + x[0] - val[0];
+		w.b_off[r] = w.scan_part[3 * blockIdx.x + 1] + x[1] - val[1];
+		w.rec_off[r] = w.scan_part[3 * blockIdx.x + 2] + x[2] - val[2];
+	}
+}
+
+static int launch_scan_reads(const Workspace &w, int have_tail, cudaStream_t s)
+{
+	const int nb = (w.n_reads + 1023) / 1024 > 0 ? (w.n_reads + 1023) / 1024 : 1;
+	k_scan_block_sums<<<nb, 1024, 0, s>>>(w, have_tail);
+	k_scan_block_offsets<<<1, 1024, 0, s>>>(w, nb);
+	k_scan_apply<<<nb, 1024, 0, s>>>(w, have_tail);
+	return 3;
 }
 
 // chain.c:187-192,205-213: write the final packed u[] and b[]
@@ -1281,8 +1314,7 @@ int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
 	k_tail_warp<<<blocks_for(w.n_reads, TW_WARPS, 148 * 16), TW_WARPS * 32, 0, s>>>(w, prm.min_cnt, prm.min_sc);
 	k_tail<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w, prm.min_cnt, prm.min_sc, TW_CAP);
-	k_scan_reads<<<1, 1024, 0, s>>>(w, 1);
-	return 3;
+	return 2 + launch_scan_reads(w, 1, s);
 }
 
 int launch_gather(const Workspace &w, cudaStream_t s)
@@ -1293,9 +1325,9 @@ int launch_gather(const Workspace &w, cudaStream_t s)
 
 int launch_pack_records(const Workspace &w, cudaStream_t s)
 {
-	k_scan_reads<<<1, 1024, 0, s>>>(w, 0);
+	const int n = launch_scan_reads(w, 0, s);
 	k_pack_records<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w);
-	return 2;
+	return n + 1;
 }
 
 int launch_export_fp(const Workspace &w, cudaStream_t s)
