@@ -182,3 +182,33 @@ def test_concurrent_callers_are_batched(ctx):
     for r in range(64):
         wu, wb = oracle.chain_dp(oprm, a[offs[r]:offs[r + 1]])
         assert np.array_equal(out[r][0], wu) and np.array_equal(out[r][1], wb), f"read {r}"
+
+
+def test_argument_errors(ctx):
+    """Bad arguments come back as error codes (never abort, never compute)."""
+    a = np.zeros((10, 2), np.uint64)
+    with pytest.raises(api.ChainError) as ei:
+        ctx.chain_batch(api.params("map-ont"), np.array([0, 7, 5, 10], np.int64), a)        # offs not non-decreasing
+    assert ei.value.code == api.ERR_ARG
+    with pytest.raises(api.ChainError) as ei:
+        ctx.chain_batch(api.params("map-ont", max_dist_x=-1), np.array([0, 10], np.int64), a)
+    assert ei.value.code == api.ERR_ARG
+    with pytest.raises(api.ChainError) as ei:
+        ctx.chain_batch(api.params("map-ont", max_iter=-5), np.array([0, 10], np.int64), a)
+    assert ei.value.code == api.ERR_ARG
+    with pytest.raises(api.ChainError) as ei:
+        api.ChainContext(device=99)
+    assert ei.value.code == api.ERR_CUDA
+    # the context is still usable after an error
+    got = ctx.chain_batch(api.params("map-ont"), np.array([0, 10], np.int64), a)
+    assert got.n_u.tolist() == [0]
+
+
+def test_wide_window_variant(ctx):
+    """max_dist_x >= 2^27 switches to the prefix-of-lanes window test (WIDE)."""
+    rng = np.random.default_rng(21)
+    reads = [random_colinear(rng, int(n), noise=0.3, step=5) for n in rng.integers(2, 800, 25)]
+    offs, a = concat_reads(reads)
+    for over in (dict(max_dist_x=1 << 27, max_dist_y=1 << 27), dict(max_dist_x=(1 << 31) - 1, max_dist_y=5000, bw=700)):
+        got, want = _both(ctx, "map-ont", offs, a, **over)
+        assert_same(got, want, f"wide {over}")
