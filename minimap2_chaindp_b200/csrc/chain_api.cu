@@ -658,22 +658,22 @@ struct Pending {
 	mm2b200_params_t prm;
 	int64_t n;
 	const mm128_t *a;
-	// filled by the dispatcher; pointers into the context's result arena, valid until `copied` is signalled
+	bool own_malloc;          // results may be handed over as plain malloc()ed arrays (km == NULL)
+	// filled by the dispatcher: malloc()ed copies of this call's slice of the batch result, so the dispatcher never has
+	// to wait for the callers before it starts the next batch
 	int rc = 0; std::string err;
-	int32_t n_u = 0; const uint64_t *u = nullptr; const mm128_t *b = nullptr; int64_t n_b = 0;
+	int32_t n_u = 0; uint64_t *u = nullptr; mm128_t *b = nullptr; int64_t n_b = 0;
 	bool done = false;
+	std::condition_variable cv;   // one per call: only the owner is woken
 };
 
 struct Batcher {
 	std::mutex mu;
-	std::condition_variable cv_work, cv_done, cv_copied;
+	std::condition_variable cv_work;
 	std::deque<Pending*> q;
-	int outstanding_copies = 0;
-	mm2b200_ctx *ctx = nullptr;
+	mm2b200_ctx *ctx = nullptr;        // the default context (also used by mm_chain_dp_fpga / _bottom)
 	int init_rc = 0; std::string init_err;
 	bool started = false;
-	std::vector<mm128_t> gather; std::vector<int64_t> offs;
-	PinnedBuf stage;
 };
 
 Batcher *g_batcher = nullptr;
@@ -697,8 +697,10 @@ mm2b200_ctx *default_ctx()
 	return g_default_ctx;
 }
 
-void dispatcher_main(Batcher *B)
+void dispatcher_main(Batcher *B, mm2b200_ctx *ctx)
 {
+	std::vector<int64_t> offs;
+	PinnedBuf stage;
 	for (;;) {
 		std::vector<Pending*> batch;
 		{
@@ -712,34 +714,33 @@ void dispatcher_main(Batcher *B)
 			}
 		}
 		int64_t total = 0;
-		B->offs.assign(1, 0);
-		for (auto *p : batch) { total += p->n; B->offs.push_back(total); }
-		int rc = B->stage.reserve((size_t)(total > 0 ? total : 1) * sizeof(mm128_t));
+		offs.assign(1, 0);
+		for (auto *p : batch) { total += p->n; offs.push_back(total); }
+		int rc = stage.reserve((size_t)(total > 0 ? total : 1) * sizeof(mm128_t));
 		mm2b200_result_t res{};
 		if (!rc) {
-			mm128_t *dst = B->stage.as<mm128_t>();
+			mm128_t *dst = stage.as<mm128_t>();
 			for (size_t k = 0; k < batch.size(); ++k)
-				if (batch[k]->n > 0) memcpy(dst + B->offs[k], batch[k]->a, (size_t)batch[k]->n * sizeof(mm128_t));
-			rc = mm2b200_chain_batch(B->ctx, &batch[0]->prm, (int64_t)batch.size(), B->offs.data(), dst, &res);
+				if (batch[k]->n > 0) memcpy(dst + offs[k], batch[k]->a, (size_t)batch[k]->n * sizeof(mm128_t));
+			rc = mm2b200_chain_batch(ctx, &batch[0]->prm, (int64_t)batch.size(), offs.data(), dst, &res);
+		}
+		// hand every caller a private copy of its slice (outside the lock), then wake exactly that caller
+		for (size_t k = 0; k < batch.size(); ++k) {
+			Pending *p = batch[k];
+			p->rc = rc;
+			if (rc) p->err = g_err;
+			else if (res.n_u[k] > 0) {
+				p->n_u = res.n_u[k];
+				p->n_b = res.b_off[k + 1] - res.b_off[k];
+				p->u = (uint64_t*)malloc((size_t)p->n_u * 8);
+				p->b = (mm128_t*)malloc((size_t)(p->n_b > 0 ? p->n_b : 1) * sizeof(mm128_t));
+				memcpy(p->u, res.u + res.u_off[k], (size_t)p->n_u * 8);
+				memcpy(p->b, res.b + res.b_off[k], (size_t)p->n_b * sizeof(mm128_t));
+			}
 		}
 		{
-			std::unique_lock<std::mutex> lk(B->mu);
-			for (size_t k = 0; k < batch.size(); ++k) {
-				Pending *p = batch[k];
-				p->rc = rc;
-				if (rc) p->err = g_err;
-				else {
-					p->n_u = res.n_u[k];
-					p->u = res.u + res.u_off[k];
-					p->b = res.b + res.b_off[k];
-					p->n_b = res.b_off[k + 1] - res.b_off[k];
-				}
-				p->done = true;
-			}
-			B->outstanding_copies = (int)batch.size();
-			B->cv_done.notify_all();
-			// the result arena is reused by the next batch: wait until every caller has copied its slice out
-			B->cv_copied.wait(lk, [&] { return B->outstanding_copies == 0; });
+			std::lock_guard<std::mutex> lk(B->mu);
+			for (auto *p : batch) { p->done = true; p->cv.notify_one(); }
 		}
 	}
 }
@@ -750,7 +751,7 @@ Batcher *batcher()
 		Batcher *B = new Batcher();
 		B->ctx = default_ctx();
 		if (!B->ctx) { B->init_rc = MM2B200_ERR_CUDA; B->init_err = g_err; }
-		else { std::thread(dispatcher_main, B).detach(); B->started = true; }
+		else { std::thread(dispatcher_main, B, B->ctx).detach(); B->started = true; }
 		g_batcher = B;
 	});
 	return g_batcher;
@@ -783,24 +784,26 @@ extern "C" mm128_t *mm_chain_dp(int max_dist_x, int max_dist_y, int bw, int max_
 		Pending pd;
 		pd.prm = mm2b200_params_t{max_dist_x, max_dist_y, bw, max_skip, min_cnt, min_sc, is_cdna, n_segs, 0};
 		pd.n = n; pd.a = a;
+		pd.own_malloc = (km == nullptr);     // kmalloc(NULL, n) is malloc(n) (kalloc.c:127), so malloc()ed results are compatible
 		{
 			std::unique_lock<std::mutex> lk(B->mu);
 			B->q.push_back(&pd);
 			B->cv_work.notify_one();
-			B->cv_done.wait(lk, [&] { return pd.done; });
+			pd.cv.wait(lk, [&] { return pd.done; });
 		}
 		if (pd.rc == MM2B200_OK && pd.n_u > 0) {
-			uint64_t *u = (uint64_t*)host_alloc(km, (size_t)pd.n_u * 8);
-			ret = (mm128_t*)host_alloc(km, (size_t)pd.n_b * sizeof(mm128_t));
-			memcpy(u, pd.u, (size_t)pd.n_u * 8);
-			memcpy(ret, pd.b, (size_t)pd.n_b * sizeof(mm128_t));
+			uint64_t *u = pd.u;
+			ret = pd.b;
+			if (!pd.own_malloc) {            // results must live in the caller's kalloc arena: copy on the caller's thread
+				u = (uint64_t*)host_alloc(km, (size_t)pd.n_u * 8);
+				ret = (mm128_t*)host_alloc(km, (size_t)pd.n_b * sizeof(mm128_t));
+				memcpy(u, pd.u, (size_t)pd.n_u * 8);
+				memcpy(ret, pd.b, (size_t)pd.n_b * sizeof(mm128_t));
+				free(pd.u); free(pd.b);
+			}
 			if (_u) *_u = u; else host_free(km, u);
 			if (n_u_) *n_u_ = pd.n_u;
 		} else if (pd.rc != MM2B200_OK) g_err = pd.err;
-		{
-			std::lock_guard<std::mutex> lk(B->mu);
-			if (--B->outstanding_copies == 0) B->cv_copied.notify_all();
-		}
 	}
 	host_free(km, a);   // chain.c:137,214: the input array is consumed
 	return ret;
