@@ -26,6 +26,12 @@ extern "C" void kfree(void *km, void *ptr) __attribute__((weak));
 
 static thread_local std::string g_err;
 
+// Long-read batches keep up to 32 sub-batches in flight on separate streams; with the default 8 hardware queues
+// streams share queues and serialise behind each other's long fill kernels (measured: 1021 -> 540 ms on the 6000-read
+// map-pb slice).  The variable is read when the CUDA context is created, so it is set when the library is loaded and
+// never overrides a value the user chose.
+__attribute__((constructor)) static void mm2b200_on_load() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+
 static int fail(int code, const char *fmt, ...)
 {
 	char buf[512];
@@ -90,6 +96,7 @@ struct mm2b200_ctx {
 	int device = 0;
 	int profile = 0;
 	int64_t slot_anchors = 0;
+	bool adaptive_slots = true;
 	LaunchCfg lc{};
 	std::vector<Slot> slots;
 	std::mutex mu;
@@ -248,6 +255,17 @@ extern "C" void *mm2b200_pinned_alloc(size_t bytes)
 }
 extern "C" void mm2b200_pinned_free(void *p) { if (p) cudaFreeHost(p); }
 
+static int add_slot(mm2b200_ctx *ctx)
+{
+	ctx->slots.emplace_back();
+	Slot &s = ctx->slots.back();
+	if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&s.ev_totals, cudaEventDisableTiming) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming) != cudaSuccess)
+		return fail(MM2B200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+	return MM2B200_OK;
+}
+
 extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 {
 	if (!out) return fail(MM2B200_ERR_ARG, "ctx out pointer is NULL");
@@ -263,15 +281,10 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 	ctx->profile = c.profile;
 	ctx->slot_anchors = c.slot_anchors > 0 ? c.slot_anchors : ((int64_t)8 << 20);
 	const int ns = c.n_slots > 0 ? c.n_slots : 3;
-	ctx->slots.resize(ns);
-	for (auto &s : ctx->slots) {
-		if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
-		    cudaEventCreateWithFlags(&s.ev_totals, cudaEventDisableTiming) != cudaSuccess ||
-		    cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming) != cudaSuccess) {
-			int rc = fail(MM2B200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
-			mm2b200_destroy(ctx);
-			return rc;
-		}
+	ctx->adaptive_slots = c.n_slots <= 0;      // default: long-read batches may add slots (see run_batch)
+	for (int k = 0; k < ns; ++k) {
+		int rc = add_slot(ctx);
+		if (rc) { mm2b200_destroy(ctx); return rc; }
 	}
 	query_launch_cfg(&ctx->lc);
 	ctx->lc.count_visited = c.count_visited;
@@ -431,16 +444,32 @@ static int run_batch(BatchJob &job)
 		if ((rc = ctx->r_b.reserve((size_t)(N + 1) * 16))) return rc;
 	}
 	job.src_pinned = job.src ? is_pinned(job.src) : true;
+	// Long reads mean few runs per sub-batch (a 55 k-anchor read is one run): the fill kernel needs thousands of runs in
+	// flight, so such batches keep more sub-batches on the device at once (their kernels overlap on separate streams).
+	if (ctx->adaptive_slots && R > 0) {
+		const int64_t avg = N / R > 0 ? N / R : 1;
+		const int64_t reads_per_chunk = ctx->slot_anchors / avg > 0 ? ctx->slot_anchors / avg : 1;
+		int64_t want = (4096 + reads_per_chunk - 1) / reads_per_chunk;
+		const int64_t n_chunks_est = N / ctx->slot_anchors + 1;
+		size_t free_b = 0, total_b = 0;
+		cudaMemGetInfo(&free_b, &total_b);
+		const int64_t mem_cap = (int64_t)(total_b / 2 / ((size_t)ctx->slot_anchors * 176 + 1));
+		if (want > n_chunks_est) want = n_chunks_est;
+		if (want > mem_cap) want = mem_cap;
+		if (want > 32) want = 32;
+		while ((int64_t)ctx->slots.size() < want) if ((rc = add_slot(ctx))) return rc;
+	}
 	const int S = (int)ctx->slots.size();
-	int64_t r0 = 0, chunk = 0;
-	int prev_slot = -1;
+	int64_t r0 = 0, chunk = 0, next_a = 0;   // next_a: oldest chunk whose totals have not been collected yet
 	while (r0 < R) {
 		// greedy chunk: consecutive reads up to slot_anchors anchors (at least one read)
 		int64_t r1 = r0 + 1;
 		while (r1 < R && job.offs[r1 + 1] - job.offs[r0] <= ctx->slot_anchors && r1 - r0 < ((int64_t)1 << 24)) ++r1;
 		const int64_t na = job.offs[r1] - job.offs[r0], nr = r1 - r0;
 		Slot &s = ctx->slots[chunk % S];
-		if (s.state == 1 && (rc = finish_a(job, s))) return rc;
+		if (s.state == 1) {     // reuse: collect (in chunk order) everything up to the chunk that still owns this slot
+			while (next_a <= chunk - S) { if ((rc = finish_a(job, ctx->slots[next_a % S]))) return rc; ++next_a; }
+		}
 		if (s.state == 2 && (rc = finish_b(job, s))) return rc;
 		if ((rc = ensure_slot(ctx, s, (size_t)na, (size_t)nr))) return rc;
 		if (job.mode == MODE_FILL && (rc = ensure_rec_out(s))) return rc;
@@ -481,17 +510,18 @@ static int run_batch(BatchJob &job)
 		CUDA_TRY(cudaEventRecord(s.ev_totals, s.stream));
 		CUDA_TRY(cudaGetLastError());
 		s.state = 1;
-		// while this chunk runs, move the previous one along
-		if (prev_slot >= 0 && ctx->slots[prev_slot].state == 1 && (rc = finish_a(job, ctx->slots[prev_slot]))) return rc;
-		prev_slot = (int)(chunk % S);
 		++chunk;
 		r0 = r1;
+		// move older chunks along without blocking: as soon as a chunk's totals are on the host, start its output copies.
+		// With the default three slots the previous chunk is waited for (its D2H then overlaps this chunk's kernels).
+		while (next_a < chunk - 1) {
+			Slot &o = ctx->slots[next_a % S];
+			if (S <= 3 || cudaEventQuery(o.ev_totals) == cudaSuccess) { if ((rc = finish_a(job, o))) return rc; ++next_a; }
+			else break;
+		}
 	}
 	// drain in chunk order
-	for (int64_t c = chunk > S ? chunk - S : 0; c < chunk; ++c) {
-		Slot &s = ctx->slots[c % S];
-		if (s.state == 1 && (rc = finish_a(job, s))) return rc;
-	}
+	while (next_a < chunk) { if ((rc = finish_a(job, ctx->slots[next_a % S]))) return rc; ++next_a; }
 	for (int64_t c = chunk > S ? chunk - S : 0; c < chunk; ++c) {
 		Slot &s = ctx->slots[c % S];
 		if (s.state == 2 && (rc = finish_b(job, s))) return rc;
