@@ -869,15 +869,14 @@ __global__ void __launch_bounds__(TW_WARPS * 32) k_tail_warp(Workspace w, int32_
 			const int peak_sc = (int)(c >> 32);
 			int j = (int)(uint32_t)c;
 			const int n0 = n_v;
-			bool first = true;                                   // do { } while: the peak is taken even if claimed
 			for (;;) {
 				const int cl = j - lane;
 				const int wl = cl >= 0 ? s_rp[cl] : -4;
 				const bool claimed_l = cl >= 0 ? (s_flag[cl] != 0) : true;
 				const int wprev = __shfl_up_sync(FULL, wl, 1);
+				// lane 0 is always taken: j is unclaimed by construction, except the peak, which the reference takes anyway (do-while)
 				const bool ok = lane == 0 ? true : ((wprev >> 2) == cl && cl >= 0 && !claimed_l);
-				(void)first;
-				const int run = __ffs(~__ballot_sync(FULL, ok)) - 1;   // >= 1 (lane 0 is always ok); 32 if all lanes link
+				const int run = __ffs(~__ballot_sync(FULL, ok)) - 1;   // >= 1; -1 means all 32 lanes link
 				const int take = run < 0 ? 32 : run;
 				if (lane < take) {
 					if (n_v + lane < cap) members[n_v + lane] = cl;
@@ -886,7 +885,6 @@ __global__ void __launch_bounds__(TW_WARPS * 32) k_tail_warp(Workspace w, int32_
 				n_v += take;
 				const int jn = __shfl_sync(FULL, wl, take - 1) >> 2;   // predecessor of the last record taken
 				__syncwarp();
-				first = false;
 				j = jn;
 				if (jn < 0 || s_flag[jn]) break;
 			}
@@ -937,7 +935,7 @@ __global__ void __launch_bounds__(TW_WARPS * 32) k_tail_warp(Workspace w, int32_
 
 __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, int32_t min_sc, int32_t min_m)
 {
-	__shared__ int s_cnt, s_nu, s_nv;
+	__shared__ int s_cnt, s_nu;
 	__shared__ int s_head[256], s_tail[256];
 	const int tid = threadIdx.x;
 	for (int r = blockIdx.x; r < w.n_reads; r += gridDim.x) {
@@ -977,20 +975,34 @@ __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, i
 		// chain.c:156-160: descending (peak score, peak index) == ascending sort read backwards
 		cta_sort_u64(cand, n_end);
 
-		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains
-		if (tid == 0) {
+		// chain.c:163-179: backtrack in that order; claims persist even for rejected chains.  Warp 0 walks run-wise like
+		// k_tail_warp (a stretch of consecutively linked, unclaimed records per iteration), here on global memory.
+		if (tid < 32) {
+			const int lane = tid;
 			int n_v = 0, k = 0;
 			for (int ii = n_end - 1; ii >= 0; --ii) {
 				const uint64_t c = cand[ii];
 				const int peak_sc = (int)(c >> 32);
 				int j = (int)(uint32_t)c;
 				const int n0 = n_v;
-				do {
-					if (n_v < cap) members[n_v] = j;
-					++n_v;
-					claimed[j] = 1;
-					j = rp[j] >> 2;
-				} while (j >= 0 && !claimed[j]);
+				for (;;) {
+					const int cl = j - lane;
+					const int wl = cl >= 0 ? rp[cl] : -4;
+					const bool claimed_l = cl >= 0 ? (claimed[cl] != 0) : true;
+					const int wprev = __shfl_up_sync(FULL, wl, 1);
+					const bool ok = lane == 0 ? true : ((wprev >> 2) == cl && cl >= 0 && !claimed_l);
+					const int run = __ffs(~__ballot_sync(FULL, ok)) - 1;
+					const int take = run < 0 ? 32 : run;
+					if (lane < take) {
+						if (n_v + lane < cap) members[n_v + lane] = cl;
+						claimed[cl] = 1;
+					}
+					n_v += take;
+					const int jn = __shfl_sync(FULL, wl, take - 1) >> 2;
+					__syncwarp();
+					j = jn;
+					if (jn < 0 || claimed[jn]) break;
+				}
 				const int cnt = n_v - n0;
 				bool keep = false;
 				uint64_t val = 0;
@@ -1001,11 +1013,10 @@ __global__ void __launch_bounds__(TAIL_T) k_tail(Workspace w, int32_t min_cnt, i
 					const int d = peak_sc - rec[j].f;
 					if (d >= min_sc && cnt >= min_cnt) { keep = true; val = ((uint64_t)(uint32_t)d << 32) | (uint32_t)cnt; }
 				}
-				if (keep) { chain_u[k] = val; voff[k] = n0; ++k; }
+				if (keep) { if (lane == 0) { chain_u[k] = val; voff[k] = n0; } ++k; }
 				else n_v = n0;
 			}
-			s_nu = k; s_nv = n_v;
-			w.n_u[r] = k; w.n_v[r] = n_v;
+			if (lane == 0) { s_nu = k; w.n_u[r] = k; w.n_v[r] = n_v; }
 		}
 		__syncthreads();
 		const int n_u = s_nu;
