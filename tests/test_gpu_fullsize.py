@@ -100,3 +100,17 @@ def test_other_configs_large_slice(name, n_reads, n_check):
         wu, wb = oracle.chain_dp(oprm, a[offs[r]:offs[r + 1]])
         u, b = res.read(int(r))
         assert np.array_equal(u, wu) and np.array_equal(b, wb), f"{name} read {r}"
+
+
+def test_asm5_contig_scale():
+    """configs[4]: one serial run of ~4 M anchors per contig (two contigs here); full oracle comparison."""
+    spec = workload.CONFIGS["asm5-50mb"]
+    offs, a = workload.generate(spec, 0, 2)
+    assert int(np.diff(offs).min()) > 3_000_000
+    prm = api.params(spec.preset)
+    with api.ChainContext(device=0, count_visited=True) as c:
+        res = c.chain_batch(prm, offs, a)
+    want = oracle.chain_batch(oracle.params(spec.preset), offs, a)
+    for name in ("n_u", "u_off", "b_off", "u", "b"):
+        assert np.array_equal(getattr(res, name), getattr(want, name)), name
+    assert res.n_visited == want.visited
