@@ -271,6 +271,7 @@ def main():
     with api.ChainContext(device=local, count_visited=True) as cctx:
         cres = cctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
         pairs_step = int(cres.n_visited)
+        lanes_step = int(cres.n_lanes)
     chains_step = int(np.frombuffer((C.c_char * 8).from_address(res.u_off + 8 * n_reads), dtype=np.int64)[0])
     canch_step = int(np.frombuffer((C.c_char * 8).from_address(res.b_off + 8 * n_reads), dtype=np.int64)[0])
     n_units = int(res.n_units)
@@ -355,6 +356,7 @@ def main():
             "roofline_issue": {"kernel": "k_fill", "bound": "int-issue", "achieved": int_achieved / 1e12, "peak": int_peak_mix / 1e12,
                                "unit": "T lane-op/s", "frac": int_achieved / int_peak_mix if int_peak_mix else None,
                                "peak_alu_pipe_only": int_peak_alu / 1e12, "ops_per_pair": INT_OPS_PER_PAIR,
+                               "lane_efficiency": pairs_step / lanes_step if lanes_step else None,
                                "peak_source": "measured live (mm2b200_int_peak: add/xor/mad.lo streams on all SMs)"},
             "stage_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in stage.items()},
         }

@@ -108,6 +108,7 @@ typedef struct {
 	int64_t n_units;         /* independent anchor runs (len >= 2) the fill kernel processed */
 	int64_t n_sub_batches;
 	int64_t n_visited;       /* (i,j) pairs the reference loop visits (bodies of chain.c:59-88); needs cfg.count_visited */
+	int64_t n_lanes;         /* predecessor lanes the fill kernel evaluated (32 per chunk); n_visited / n_lanes = lane efficiency */
 } mm2b200_result_t;
 
 /* mm_chain_dp over n_reads reads: read r owns a[offs[r] .. offs[r+1]) (each sorted by x, map.c:233).
@@ -154,7 +155,7 @@ typedef struct {
 	const int64_t  *d_b_off;  /* [n_reads+1] */
 	const uint64_t *d_u;
 	const mm128_t  *d_b;
-	const int64_t  *d_totals; /* [8]: [0..2] as above, [3] = sum new_i, [4] = visited (i,j) pairs */
+	const int64_t  *d_totals; /* [8]: [0..2] as above, [3] = sum new_i, [4] = visited (i,j) pairs, [5] = 32-lane chunks evaluated */
 } mm2b200_dev_result_t;
 
 /* Whole path on anchors already resident in HBM: d_a[n_anchors] and d_offs[n_reads+1] are device pointers.

@@ -78,7 +78,7 @@ class _Config(C.Structure):
 class _Result(C.Structure):
     _fields_ = [("n_reads", C.c_int64), ("n_u", C.c_void_p), ("u_off", C.c_void_p), ("b_off", C.c_void_p),
                 ("u", C.c_void_p), ("b", C.c_void_p), ("n_units", C.c_int64), ("n_sub_batches", C.c_int64),
-                ("n_visited", C.c_int64)]
+                ("n_visited", C.c_int64), ("n_lanes", C.c_int64)]
 
 
 class _Records(C.Structure):
@@ -173,6 +173,7 @@ class BatchResult:
     n_units: int = 0
     n_sub_batches: int = 0
     n_visited: int = 0
+    n_lanes: int = 0
 
     def read(self, r: int):
         return self.u[self.u_off[r]:self.u_off[r + 1]], self.b[self.b_off[r]:self.b_off[r + 1]]
@@ -256,7 +257,7 @@ class ChainContext:
             u_off, b_off = np.zeros(1, np.int64), np.zeros(1, np.int64)
         return BatchResult(_view(res.n_u, nr, np.int32), u_off, b_off,
                            _view(res.u, int(u_off[-1]), np.uint64), _view(res.b, int(b_off[-1]), np.uint64, (2,)),
-                           int(res.n_units), int(res.n_sub_batches), int(res.n_visited))
+                           int(res.n_units), int(res.n_sub_batches), int(res.n_visited), int(res.n_lanes))
 
     def fill_batch(self, prm: Params, offs, a, want_fpv: bool = False):
         """mm_chain_dp_fpga (chain.c:218) over a batch -> (rec_off, records[, f, p, v])."""

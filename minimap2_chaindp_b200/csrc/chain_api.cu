@@ -124,7 +124,7 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 	void *pa = nullptr, *poffs = nullptr;
 	Item items[] = {
 		{ &pa, 16 * A }, { &poffs, 8 * (R + 1) },
-		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N }, { (void**)&w.visited, 8 },
+		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N }, { (void**)&w.visited, 16 },
 		{ (void**)&w.wrec, 16 * A }, { (void**)&w.f, 4 * A }, { (void**)&w.p, 4 * A }, { (void**)&w.v, 4 * A }, { (void**)&w.t, 4 * A },
 		{ (void**)&w.newid, 4 * A }, { (void**)&w.rec, 24 * A }, { (void**)&w.recp, 4 * A }, { (void**)&w.new_i, 4 * R },
 		{ (void**)&w.succ, A }, { (void**)&w.claimed, A }, { (void**)&w.members, 4 * A },
@@ -354,7 +354,7 @@ struct BatchJob {
 	bool src_pinned;
 	int32_t *dbg_f, *dbg_p, *dbg_v;   // fill mode only
 	int64_t ubase = 0, bbase = 0;     // running output positions
-	int64_t n_units = 0, n_chunks = 0, n_visited = 0;
+	int64_t n_units = 0, n_chunks = 0, n_visited = 0, n_lanes = 0;
 };
 
 static bool is_pinned(const void *p)
@@ -373,6 +373,7 @@ static int finish_a(BatchJob &job, Slot &s)
 	const int64_t tu = tot[0], tb = tot[1];
 	job.n_units += tot[2];
 	job.n_visited += tot[4];
+	job.n_lanes += 32 * tot[5];
 	s.ubase = job.ubase; s.bbase = job.bbase;
 	// (result arenas were reserved to their upper bounds in run_batch, so nothing here can move a buffer that an
 	// earlier chunk's copy is still writing to; per-chunk offset copies cover n_reads entries so chunks never overlap)
@@ -549,7 +550,7 @@ extern "C" int mm2b200_chain_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *p
 	res->n_reads = n_reads;
 	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
 	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
-	res->n_units = job.n_units; res->n_sub_batches = job.n_chunks; res->n_visited = job.n_visited;
+	res->n_units = job.n_units; res->n_sub_batches = job.n_chunks; res->n_visited = job.n_visited; res->n_lanes = job.n_lanes;
 	return MM2B200_OK;
 }
 
@@ -579,7 +580,7 @@ extern "C" int mm2b200_bottom_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	res->n_reads = n_reads;
 	res->n_u = ctx->r_n_u.as<int32_t>(); res->u_off = ctx->r_u_off.as<int64_t>(); res->b_off = ctx->r_b_off.as<int64_t>();
 	res->u = ctx->r_u.as<uint64_t>(); res->b = ctx->r_b.as<mm128_t>();
-	res->n_units = 0; res->n_sub_batches = job.n_chunks; res->n_visited = 0;
+	res->n_units = 0; res->n_sub_batches = job.n_chunks; res->n_visited = 0; res->n_lanes = 0;
 	return MM2B200_OK;
 }
 

@@ -29,7 +29,7 @@ struct Workspace {
 	Unit *units;              // [units_cap]: short runs from the front, long runs from the back
 	int32_t units_cap;
 	int32_t *counters;        // [CNT_N]
-	unsigned long long *visited; // [1] reference-visited (i,j) pairs (chain.c:59-88 loop bodies) of this sub-batch
+	unsigned long long *visited; // [2] reference-visited (i,j) pairs (chain.c:59-88 loop bodies); 32-lane chunks evaluated
 	// fill (chain.c:52-90)
 	int4 *wrec;               // [n_anchors] working record {low32(x), qpos, f, p}; p is a batch-wide index (or -1)
 	int32_t *v;               // [n_anchors] peak score along the best chain ending here (chain.c:90)

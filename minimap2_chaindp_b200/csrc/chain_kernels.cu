@@ -154,6 +154,7 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 		const int s = un.start, e = un.start + un.len;
 		const double avg = (double)w.avg[un.read];
 		long long n_visited = 0;   // loop bodies the reference executes (chain.c:59-88), the metric's numerator
+		long long n_chunks = 0;    // 32-lane chunks evaluated (lane efficiency = visited / (32 * chunks))
 
 		for (int i = s + 1; i < e; ++i) {
 			const ulonglong2 ai = a[i];
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 				int nwin = 32;
 				if (wmask != FULL) { nwin = __ffs(~wmask) - 1; done = true; }
 				if (nwin == 0) break;
-				n_visited += nwin;
+				n_visited += nwin; ++n_chunks;
 				const bool act = lane < nwin;
 
 				// ---- pair score (chain.c:60-79) ----
@@ -233,7 +234,7 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 			}
 			__syncwarp();
 		}
-		if (lane == 0) atomicAdd(w.visited, (unsigned long long)n_visited);
+		if (lane == 0) { atomicAdd(w.visited, (unsigned long long)n_visited); atomicAdd(w.visited + 1, (unsigned long long)n_chunks); }
 	}
 }
 
@@ -532,7 +533,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 		const int s = un.start, e = un.start + un.len;
 		const float avgf = w.avg[un.read];
 		const double avg = (double)avgf;
-		long long visited = 0;
+		long long visited = 0, n_chunks = 0;
 
 		if (TABLE && (!have_tab || __float_as_uint(avgf) != tab_key)) {
 			__syncwarp();
@@ -574,6 +575,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			int vj = lds32<SM_VRING>(ring_w + off0);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 			int cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+			if (FULLV) ++n_chunks;
 			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
 			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 			if (!done && i - 33 >= jlo) {
@@ -586,6 +588,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				const bool mmem = j1 >= jlo && t[j1] == i;
 				dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 				cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+				if (FULLV) ++n_chunks;
 				done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
 				                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
@@ -598,6 +601,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
 					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+					if (FULLV) ++n_chunks;
 					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
 					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
 				}
@@ -620,7 +624,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				}
 			}
 		}
-		if (FULLV && lane == 0) atomicAdd(w.visited, (unsigned long long)visited);
+		if (FULLV && lane == 0) { atomicAdd(w.visited, (unsigned long long)visited); atomicAdd(w.visited + 1, (unsigned long long)n_chunks); }
 	}
 }
 
@@ -1119,7 +1123,7 @@ __global__ void __launch_bounds__(1024) k_scan_block_offsets(Workspace w, int n_
 	if (threadIdx.x == 0) {
 		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
 		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS] + w.counters[CNT_LONG_UNITS]; w.totals[3] = s_carry[2];
-		w.totals[4] = (long long)*w.visited;
+		w.totals[4] = (long long)w.visited[0]; w.totals[5] = (long long)w.visited[1];
 	}
 }
 
@@ -1214,10 +1218,18 @@ __global__ void __launch_bounds__(256) k_int_peak(unsigned *out, int iters, unsi
 #pragma unroll
 		for (int k = 0; k < 8; ++k) {
 			if (MODE == 0) {
-				asm volatile("add.u32 %0, %0, %1;" : "+r"(a0) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a1) : "r"(d));
-				asm volatile("add.u32 %0, %0, %1;" : "+r"(a2) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a3) : "r"(d));
-				asm volatile("add.u32 %0, %0, %1;" : "+r"(a4) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a5) : "r"(d));
-				asm volatile("add.u32 %0, %0, %1;" : "+r"(a6) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a7) : "r"(d));
+				// every chain alternates add / xor so that ptxas cannot fold two steps into one IADD3 / LOP3
+				if (k & 1) {
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(a0) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a1) : "r"(d));
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(a2) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a3) : "r"(d));
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(a4) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a5) : "r"(d));
+					asm volatile("add.u32 %0, %0, %1;" : "+r"(a6) : "r"(c));  asm volatile("xor.b32 %0, %0, %1;" : "+r"(a7) : "r"(d));
+				} else {
+					asm volatile("xor.b32 %0, %0, %1;" : "+r"(a0) : "r"(d));  asm volatile("add.u32 %0, %0, %1;" : "+r"(a1) : "r"(c));
+					asm volatile("xor.b32 %0, %0, %1;" : "+r"(a2) : "r"(d));  asm volatile("add.u32 %0, %0, %1;" : "+r"(a3) : "r"(c));
+					asm volatile("xor.b32 %0, %0, %1;" : "+r"(a4) : "r"(d));  asm volatile("add.u32 %0, %0, %1;" : "+r"(a5) : "r"(c));
+					asm volatile("xor.b32 %0, %0, %1;" : "+r"(a6) : "r"(d));  asm volatile("add.u32 %0, %0, %1;" : "+r"(a7) : "r"(c));
+				}
 			} else {
 				asm volatile("add.u32 %0, %0, %1;" : "+r"(a0) : "r"(c));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a1) : "r"(c), "r"(d));
 				asm volatile("xor.b32 %0, %0, %1;" : "+r"(a2) : "r"(d));  asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a3) : "r"(c), "r"(d));
@@ -1286,7 +1298,7 @@ void query_launch_cfg(LaunchCfg *cfg)
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
 	cudaMemsetAsync(w.counters, 0, CNT_N * sizeof(int32_t), s);
-	cudaMemsetAsync(w.visited, 0, sizeof(unsigned long long), s);
+	cudaMemsetAsync(w.visited, 0, 2 * sizeof(unsigned long long), s);
 	k_prep<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.max_dist_x);
 	return 1;
 }

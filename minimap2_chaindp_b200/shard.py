@@ -32,7 +32,7 @@ def merge_results(parts: List[BatchResult]) -> BatchResult:
     b_off.append(np.array([bb], np.int64))
     return BatchResult(n_u, np.concatenate(u_off), np.concatenate(b_off), u, b,
                        n_units=sum(p.n_units for p in parts), n_sub_batches=sum(p.n_sub_batches for p in parts),
-                       n_visited=sum(p.n_visited for p in parts))
+                       n_visited=sum(p.n_visited for p in parts), n_lanes=sum(p.n_lanes for p in parts))
 
 
 def shard_of(offs, rank: int, world: int):
