@@ -494,6 +494,69 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 	return (brk1 || brk2 || !all_in) ? 1 : 0;
 }
 
+// Chunks beyond the first are mostly dead: on the BASELINE workloads 46-57 % of them have every lane SKIPped
+// (chain.c:63-67) and 93-97 % have at most two scored lanes -- they belong to off-chain anchors that walk through a
+// long window of predecessors on other diagonals.  Such a chunk needs no warp-wide replay: an all-SKIP chunk changes
+// nothing, and a few scored lanes are stepped through the reference's state machine one by one, in visit order, with
+// warp-uniform scalar code (two shuffles per scored lane).  Returns 0 = scan goes on, 1 = anchor finished,
+// 2 = too many scored lanes, nothing was changed: run the dense routine on this chunk.
+#define SPARSE_MAX 4
+template <bool TABLE, bool COUNT>
+static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, int &vbest, int &budget, long long &visited,
+                                                         const int i, const int jb, const int jlo, const int lane,
+                                                         const int4 rj, const bool marked_mem,
+                                                         const unsigned xi, const int qi, const int span,
+                                                         const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
+                                                         const int B0, const unsigned tab_w, const double avg,
+                                                         int32_t *t, const int32_t *vg)
+{
+	const int j = jb - lane;
+	const unsigned dr = xi - (unsigned)rj.x;
+	const int dq = qi - rj.y;
+	const int dd = abs((int)dr - dq);
+	bool inw = (j >= jlo) && (dr <= mdx);
+	const unsigned wb = __ballot_sync(FULL, inw);
+	int done = 0, nwin = 32;
+	if (wb != FULL) {                                     // the window (chain.c:58) ends inside this chunk: lanes past the
+		nwin = __ffs(~wb) - 1;                            // first one outside are dropped (also exact for wide windows)
+		done = 1;
+		inw = lane < nwin;
+	}
+	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
+	unsigned live = __ballot_sync(FULL, !skip);
+	if (COUNT) visited += nwin;
+	if (live == 0u) return done;                          // nothing scored: no IMPROVE, no MISS, no mark
+	if (__popc(live) > SPARSE_MAX) { if (COUNT) visited -= nwin; return 2; }
+
+	int sc = 0;
+	if (!skip) {
+		const int cost = TABLE ? lds_u16(tab_w + (unsigned)dd * 2u) : lin_cost(dd, avg) + ((31 - __clz(dd | 1)) >> 1);
+		sc = min(min(dq, (int)dr), span) - cost + rj.z;   // chain.c:68-79
+	}
+	const unsigned mmem = __ballot_sync(FULL, marked_mem);
+	unsigned lm = 0;                                      // marks set by earlier scored lanes of this chunk
+	do {
+		const int L = __ffs(live) - 1;
+		live &= live - 1u;
+		const int scL = __shfl_sync(FULL, sc, L), pjL = __shfl_sync(FULL, rj.w, L);
+		if (scL > max_f) {                                // chain.c:80-82
+			max_f = scL; max_j = jb - L; vbest = vg[jb - L];
+			budget = min(budget + 1, B0);
+		} else if (((mmem | lm) >> L) & 1u) {             // chain.c:83-85
+			if (--budget <= 0) {
+				if (COUNT) visited -= nwin - (L + 1);
+				return 1;
+			}
+		}
+		if (pjL >= 0) {                                   // chain.c:87
+			const unsigned kt = (unsigned)(jb - pjL);
+			if (kt < 32u) lm |= 1u << kt;
+			else if (lane == 0) t[pjL] = i;
+		}
+	} while (live);
+	return done;
+}
+
 // FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
 template <bool TABLE, bool FULLV, bool WIDE>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
@@ -584,26 +647,37 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				__syncwarp();
 				const int j1 = i - 33 - lane;
 				rj = lds128<0>(ring_w + (off0 ^ 512u));
-				vj = lds32<SM_VRING>(ring_w + (off0 ^ 512u));
 				const bool mmem = j1 >= jlo && t[j1] == i;
-				dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-				cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 				if (FULLV) ++n_chunks;
-				done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
-				                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+				far = false;
+				done = scan_chunk_sparse<TABLE, FULLV>(max_f, max_j, vbest, budget, visited, i, i - 33, jlo, lane, rj, mmem,
+				                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
+				if (done == 2) {                                  // many scored lanes: warp-wide replay
+					vj = lds32<SM_VRING>(ring_w + (off0 ^ 512u));
+					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
+					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+				}
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
 				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
 					if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 					__syncwarp();
 					const int j = jb - lane;
-					rj = make_int4(0, 0, 0, -1); vj = 0;
+					rj = make_int4(0, 0, 0, -1);
 					bool mg = false;
-					if (j >= jlo) { rj = wrec[j]; vj = vg[j]; mg = t[j] == i; }
-					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+					if (j >= jlo) { rj = wrec[j]; mg = t[j] == i; }
 					if (FULLV) ++n_chunks;
-					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
-					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+					far = false;
+					done = scan_chunk_sparse<TABLE, FULLV>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
+					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
+					if (done == 2) {
+						vj = j >= jlo ? vg[j] : 0;
+						dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
+						cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+						done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
+						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+					}
 				}
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
