@@ -4,7 +4,7 @@ import pytest
 
 import oracle
 from minimap2_chaindp_b200 import api, workload
-from util import assert_same, concat_reads, many_chain_reads, random_colinear, random_dense
+from util import assert_same, concat_reads, interleaved_diagonals, many_chain_reads, random_colinear, random_dense
 
 pytestmark = pytest.mark.gpu
 
@@ -64,6 +64,22 @@ def test_deep_windows(ctx, seed):
     for over in (dict(), dict(max_skip=5), dict(max_skip=100), dict(n_segs=5000), dict(max_iter=50), dict(bw=2000)):
         got, want = _both(ctx, "map-ont", offs, a, **over)
         assert_same(got, want, f"deep seed {seed} {over}")
+
+
+@pytest.mark.parametrize("k", [2, 5, 9, 20, 33, 50])
+def test_sparse_chunks(ctx, k):
+    """Chunks with 0-4 scored lanes (scalar path of the fill kernel), marks and breaks that cross chunk boundaries."""
+    rng = np.random.default_rng(4000 + k)
+    reads = [interleaved_diagonals(rng, int(n), k, step=int(rng.integers(1, 4))) for n in rng.integers(2, 4000, 24)]
+    offs, a = concat_reads(reads)
+    with api.ChainContext(device=0, count_visited=True) as c:
+        for over in (dict(), dict(max_skip=3), dict(max_skip=60), dict(bw=100), dict(max_dist_x=20000, max_dist_y=20000), dict(max_iter=300)):
+            want = oracle.chain_batch(oracle.params("map-ont", **over), offs, a)
+            got = ctx.chain_batch(api.params("map-ont", **over), offs, a)
+            assert_same(got, want, f"sparse k={k} {over}")
+            got = c.chain_batch(api.params("map-ont", **over), offs, a)
+            assert_same(got, want, f"sparse counted k={k} {over}")
+            assert got.n_visited == want.visited, (k, over)
 
 
 def test_generic_path_cdna_and_segments(ctx):

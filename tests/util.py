@@ -35,6 +35,18 @@ def random_colinear(rng, n, noise=0.2, step=8, jitter=3, span=15, band=300):
     return sort_by_x(a, rng)
 
 
+def interleaved_diagonals(rng, n, k, step=3, gap=700, span=15, drop=0.1):
+    """k parallel diagonals more than bw apart, visited round-robin along x: for an anchor on one diagonal the
+    predecessors on the other k-1 are SKIPped (dd > bw), so every 32-predecessor chunk holds only a few scored lanes,
+    the marks t[p[j]] land k anchors back (beyond the chunk for k > 32) and the max_skip break comes ~26*k deep."""
+    r = 20000 + np.cumsum(rng.integers(1, step + 1, n))
+    d = np.arange(n) % k
+    q = r - 20000 + d * gap + rng.integers(-2, 3, n)
+    keep = rng.random(n) >= drop
+    a = pack(np.zeros(n, np.uint64), np.zeros(n, np.uint64), r, np.full(n, span), q)[keep]
+    return sort_by_x(a, rng)
+
+
 def many_chain_reads(rng, n_reads=6, n_chains=150):
     """Reads with > 64 short chains, many of which start at the same x: the final x-order hits ksort's unstable path."""
     reads = []
