@@ -565,7 +565,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem4);
+	// 1 KB-aligned base: a warp's ring is then a naturally aligned 1 KB window and ring addresses wrap with one LOP3
+	const unsigned sbase = ((unsigned)__cvta_generic_to_shared(smem4) + 1023u) & ~1023u;
 	unsigned ring_w = sbase + SM_RING + wib * (RING * 16);
 	unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
 	unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
@@ -574,10 +575,12 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 
 	const int n_long = w.counters[CNT_LONG_UNITS];
 	const int n_units = w.counters[CNT_UNITS] + n_long;
-	const unsigned mdx = (unsigned)prm.max_dist_x;
+	unsigned mdx = (unsigned)prm.max_dist_x;
 	const unsigned dq_max = (unsigned)(prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x);   // chain.c:64
 	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
-	const int max_skip = prm.max_skip, bw = prm.bw;
+	const int max_skip = prm.max_skip;
+	int bw = prm.bw;
+	asm volatile("" : "+r"(mdx), "+r"(bw));   // in registers, not re-read from the constant bank for every anchor
 	const int B0 = max(max_skip + 1, 1);
 	const int max_iter = (FULLV && prm.max_iter > 0) ? prm.max_iter : 0x7fffffff;
 	const ulonglong2 *__restrict__ a = w.a;
@@ -624,8 +627,13 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			}
 			__syncwarp();
 			const int i1 = min(blk + 32, e);
-		for (int i = max(blk, s + 1); i < i1; ++i) {
-			const int4 ai = lds128<0>(abuf_w + (unsigned)(i & 31) * 16u);
+			const int i0 = max(blk, s + 1);
+			// running shared addresses: anchor i in the block buffer, this lane's chunk-0 record (anchor i-1-lane), slot of i
+			unsigned aaddr = abuf_w + (unsigned)(i0 & 31) * 16u;
+			unsigned raddr = ring_w + (unsigned)((i0 - 1 - lane) & (RING - 1)) * 16u;
+			unsigned waddr = ring_w + (unsigned)(i0 & (RING - 1)) * 16u;
+		for (int i = i0; i < i1; ++i) {
+			const int4 ai = lds128<0>(aaddr);
 			const unsigned xi = (unsigned)ai.x;
 			const int qi = ai.y, span = ai.z;
 			const int jlo = FULLV ? max(s, i - max_iter) : s;
@@ -633,9 +641,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			bool far;
 
 			// chunk 0: anchors i-1 .. i-32 from the ring; no earlier chunk can have marked them
-			const unsigned off0 = (unsigned)((i - 1 - lane) & (RING - 1)) * 16u;
-			int4 rj = lds128<0>(ring_w + off0);
-			int vj = lds32<SM_VRING>(ring_w + off0);
+			int4 rj = lds128<0>(raddr);
+			int vj = lds32<SM_VRING>(raddr);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 			int cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 			if (FULLV) ++n_chunks;
@@ -646,14 +653,14 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
 				__syncwarp();
 				const int j1 = i - 33 - lane;
-				rj = lds128<0>(ring_w + (off0 ^ 512u));
+				rj = lds128<0>(raddr ^ 512u);
 				const bool mmem = j1 >= jlo && t[j1] == i;
 				if (FULLV) ++n_chunks;
 				far = false;
 				done = scan_chunk_sparse<TABLE, FULLV>(max_f, max_j, vbest, budget, visited, i, i - 33, jlo, lane, rj, mmem,
 				                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
 				if (done == 2) {                                  // many scored lanes: warp-wide replay
-					vj = lds32<SM_VRING>(ring_w + (off0 ^ 512u));
+					vj = lds32<SM_VRING>(raddr ^ 512u);
 					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
@@ -681,11 +688,11 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				}
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
-			{
-				const unsigned slot = ring_w + (unsigned)(i & (RING - 1)) * 16u;
-				sts128<0>(slot, make_int4((int)xi, qi, max_f, max_j));
-				sts32<SM_VRING>(slot, max(vbest, max_f));
-			}
+			sts128<0>(waddr, make_int4((int)xi, qi, max_f, max_j));
+			sts32<SM_VRING>(waddr, max(vbest, max_f));
+			aaddr += 16u;
+			raddr = ring_w | ((raddr + 16u) & (RING * 16u - 1u));
+			waddr = ring_w | ((waddr + 16u) & (RING * 16u - 1u));
 			// (no warp sync needed: every lane stored the same words, so a later load by any lane sees at least its own store)
 		}
 			// flush the block (deep windows and the later kernels read the records from global memory)
@@ -1335,7 +1342,7 @@ static inline int blocks_for(long long items, int per_block, int cap)
 	return (int)b;
 }
 
-static int fill_smem_bytes(int tab_entries) { return SM_TAB + FILL_WARPS * tab_entries * 2; }
+static int fill_smem_bytes(int tab_entries) { return SM_TAB + FILL_WARPS * tab_entries * 2 + 1024; }   // + alignment slack
 static int fill_tab_entries(const mm2b200_params_t &prm)
 {	// 16-bit table of bw+1 gap costs per warp, only while it stays small (<= 2 KB per warp) and the costs fit
 	if (prm.bw < 0 || prm.bw > 1023) return 0;
