@@ -291,6 +291,14 @@ static __device__ __forceinline__ void sts_u16(unsigned addr, int v)
 	asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "h"((unsigned short)v) : "memory");
 }
 
+// 1 << k with PTX shift semantics: 0 for k >= 32 (C++ leaves that undefined and the compiler would emit a wrapping shift)
+static __device__ __forceinline__ unsigned bit_or_zero(unsigned k)
+{
+	unsigned r;
+	asm("shl.b32 %0, 1, %1;" : "=r"(r) : "r"(k));
+	return r;
+}
+
 // One 32-predecessor chunk of anchor i (lane = jb - j).  State carried across the chunks of one anchor:
 //   max_f / max_j / vbest  running best predecessor (chain.c:80-81) and its peak score v[]
 //   budget                 marked misses still allowed before the break: max_skip + 1 - n_skip (chain.c:82-85)
@@ -424,7 +432,7 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 	const int pj = rj.w;
 	const unsigned kt = (unsigned)(jb - pj);
 	const bool mk = !skip && pj >= 0;
-	const unsigned mloc = __reduce_or_sync(FULL, (mk && kt < 32u) ? (1u << (kt & 31u)) : 0u);
+	const unsigned mloc = __reduce_or_sync(FULL, mk ? bit_or_zero(kt) : 0u);
 	const int M = __reduce_max_sync(FULL, scx);
 	const bool all_in = __all_sync(FULL, inw);
 	const unsigned eq = __ballot_sync(FULL, scx == M);
@@ -580,7 +588,8 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
 	const int max_skip = prm.max_skip;
 	int bw = prm.bw;
-	asm volatile("" : "+r"(mdx), "+r"(bw));   // in registers, not re-read from the constant bank for every anchor
+	// per-thread registers instead of a constant-bank re-read per anchor (threadIdx.y is 0; the compiler cannot fold it)
+	mdx += threadIdx.y; bw += (int)threadIdx.y;
 	const int B0 = max(max_skip + 1, 1);
 	const int max_iter = (FULLV && prm.max_iter > 0) ? prm.max_iter : 0x7fffffff;
 	const ulonglong2 *__restrict__ a = w.a;
