@@ -509,7 +509,7 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 // warp-uniform scalar code (two shuffles per scored lane).  Returns 0 = scan goes on, 1 = anchor finished,
 // 2 = too many scored lanes, nothing was changed: run the dense routine on this chunk.
 #define SPARSE_MAX 4
-template <bool TABLE, bool COUNT>
+template <bool TABLE, bool COUNT, bool WIDE>
 static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, int &vbest, int &budget, long long &visited,
                                                          const int i, const int jb, const int jlo, const int lane,
                                                          const int4 rj, const bool marked_mem,
@@ -523,13 +523,15 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 	const int dq = qi - rj.y;
 	const int dd = abs((int)dr - dq);
 	bool inw = (j >= jlo) && (dr <= mdx);
-	const unsigned wb = __ballot_sync(FULL, inw);
-	int done = 0, nwin = 32;
-	if (wb != FULL) {                                     // the window (chain.c:58) ends inside this chunk: lanes past the
-		nwin = __ffs(~wb) - 1;                            // first one outside are dropped (also exact for wide windows)
-		done = 1;
-		inw = lane < nwin;
-	}
+	int done, nwin = 32;
+	if (WIDE || COUNT) {
+		const unsigned wb = __ballot_sync(FULL, inw);
+		done = wb != FULL;
+		if (done) {                                       // the window (chain.c:58) ends inside this chunk: lanes past the
+			nwin = __ffs(~wb) - 1;                        // first one outside are dropped (exact for wide windows too)
+			inw = lane < nwin;
+		}
+	} else done = !__all_sync(FULL, inw);                 // max_dist_x < 2^27: the per-lane test is exact
 	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
 	unsigned live = __ballot_sync(FULL, !skip);
 	if (COUNT) visited += nwin;
@@ -661,12 +663,10 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
 				__syncwarp();
-				const int j1 = i - 33 - lane;
 				rj = lds128<0>(raddr ^ 512u);
-				const bool mmem = j1 >= jlo && t[j1] == i;
+				const bool mmem = t[max(i - 33 - lane, jlo)] == i;        // (lanes below jlo are outside the window anyway)
 				if (FULLV) ++n_chunks;
-				far = false;
-				done = scan_chunk_sparse<TABLE, FULLV>(max_f, max_j, vbest, budget, visited, i, i - 33, jlo, lane, rj, mmem,
+				done = scan_chunk_sparse<TABLE, FULLV, WIDE>(max_f, max_j, vbest, budget, visited, i, i - 33, jlo, lane, rj, mmem,
 				                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
 				if (done == 2) {                                  // many scored lanes: warp-wide replay
 					vj = lds32<SM_VRING>(raddr ^ 512u);
@@ -674,25 +674,24 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
 					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+					if (!done && far) t[rj.w] = i;                // marks beyond this chunk (the scalar path writes its own)
 				}
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
 				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
-					if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 					__syncwarp();
-					const int j = jb - lane;
-					rj = make_int4(0, 0, 0, -1);
-					bool mg = false;
-					if (j >= jlo) { rj = wrec[j]; mg = t[j] == i; }
+					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo re-read anchor jlo and are masked
+					rj = wrec[jc];
+					const bool mg = t[jc] == i;
 					if (FULLV) ++n_chunks;
-					far = false;
-					done = scan_chunk_sparse<TABLE, FULLV>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
+					done = scan_chunk_sparse<TABLE, FULLV, WIDE>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
 					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
 					if (done == 2) {
-						vj = j >= jlo ? vg[j] : 0;
+						vj = vg[jc];
 						dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 						cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 						done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
 						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+						if (!done && far) t[rj.w] = i;
 					}
 				}
 			}
