@@ -194,6 +194,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--slot-anchors", type=int, default=0)
     ap.add_argument("--slots", type=int, default=0)
+    ap.add_argument("--wire", action="store_true", help="e2e: upload through the host batcher's 8-byte wire format (default: raw mm128_t)")
+    ap.add_argument("--wire-threads", type=int, default=0, help="e2e: host encoder threads (0 = library default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -249,6 +251,8 @@ def main():
     prm = api.params(spec.preset)
 
     ctx = api.ChainContext(device=local, n_slots=args.slots, slot_anchors=args.slot_anchors, profile=True)
+    if args.wire:
+        ctx.set_upload(True, args.wire_threads)
     stream = torch.cuda.current_stream()
     d_a = torch.from_numpy(pin.array.view(np.int64)).to(dev)
     d_offs = torch.from_numpy(offs).to(dev)
@@ -310,7 +314,7 @@ def main():
     total_anchors = reduce_sum(float(n_anchors))
     value = total_pairs * args.steps / (dev_ms * 1e-3)
     e2e_value = total_pairs * args.steps / e2e_s
-    h2d = n_anchors * 16 + (n_reads + n_sub) * 8
+    h2d, wire_sub = ctx.upload_stats()      # bytes the last e2e step copied host -> device (counted by the library)
     d2h = n_reads * (4 + 8 + 8) + chains_step * 8 + canch_step * 16 + n_sub * 64
 
     # ---- rooflines of the dominant kernel (k_fill): per-launch averages from the events around it
@@ -346,7 +350,9 @@ def main():
             "anchors_per_s": total_anchors * args.steps / (dev_ms * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "reads_per_s": total_reads * args.steps / e2e_s, "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "api": "mm2b200_chain_batch (pinned host anchors in, pinned host chains out)"},
+                    "api": "mm2b200_chain_batch (pinned host anchors in, pinned host chains out)",
+                    "upload": (f"host batcher wire format ({wire_sub}/{n_sub} sub-batches, {h2d / max(n_anchors, 1):.2f} B/anchor, "
+                               f"encoded by host threads inside the timed region)") if wire_sub else "raw mm128_t (16 B/anchor)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"kernel": "k_fill", "bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",

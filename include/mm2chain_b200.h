@@ -176,6 +176,21 @@ void mm2b200_stage_reset(mm2b200_ctx_t *ctx);
  * mode 0 = ALU-pipe only (add/xor), mode 1 = ALU + FMA-pipe integer ops interleaved (the issue-port ceiling). */
 int mm2b200_int_peak(mm2b200_ctx_t *ctx, int mode, double *lane_ops_per_s);
 
+/* Host batcher (north_star subsystem 1; the reference's counterpart is the packet builder fpga_chaindp.c:send_task).
+ * With wire != 0 (opt-in; the default is the raw 16-byte upload) every sub-batch of anchors is encoded by `threads` host
+ * threads (0 = all cores, at most 16 by default) into a lossless wire format of 8 bytes per anchor plus small per-block dictionaries before it crosses
+ * PCIe, and is restored to mm128_t on the device.  Per block of 256 consecutive anchors the high half of x (strand|rid)
+ * and the high half of y (flags|seg|qspan) are replaced by dictionary indices; a sub-batch holding a block whose qpos
+ * values do not fit the 24 bits left (minus the bits of the block's y index) is uploaded raw.  Results are identical
+ * either way.  It pays only where the host can stream anchors through its cores faster than PCIe moves them (not on the
+ * measured 16-vCPU box, see profiles/).  Environment at context creation: MM2B200_WIRE=1, MM2B200_WIRE_THREADS=n. */
+int mm2b200_set_upload(mm2b200_ctx_t *ctx, int32_t wire, int32_t threads);
+/* The encoder alone (host only, no CUDA): writes [packed u64 x n][block descriptors u64 x blocks][dict u32 x entries]
+ * into buf and reports the layout.  Returns 1 when the anchors do not fit the format.  For tests and tools. */
+int mm2b200_wire_encode(const mm128_t *a, int64_t n, void *buf, size_t cap, size_t *bytes, size_t *tab_pos, size_t *dict_pos);
+/* bytes copied host -> device by the last batch call on this context, and how many of its sub-batches used the wire format */
+int mm2b200_upload_stats(const mm2b200_ctx_t *ctx, int64_t *h2d_bytes, int64_t *wire_sub_batches);
+
 const char *mm2b200_version(void);
 
 #ifdef __cplusplus

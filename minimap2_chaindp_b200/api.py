@@ -35,7 +35,7 @@ EXPORTED_SYMBOLS = (
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
     "mm2b200_partition_reads", "mm2b200_chain_batch_multi",
     "mm2b200_chain_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
-    "mm2b200_version",
+    "mm2b200_set_upload", "mm2b200_upload_stats", "mm2b200_wire_encode", "mm2b200_version",
 )
 
 
@@ -125,6 +125,9 @@ def lib() -> C.CDLL:
         L.mm2b200_stage_reset.argtypes = [vp]
         L.mm2b200_stage_reset.restype = None
         L.mm2b200_int_peak.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
+        L.mm2b200_set_upload.argtypes = [vp, i32, i32]
+        L.mm2b200_upload_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+        L.mm2b200_wire_encode.argtypes = [vp, i64, vp, C.c_size_t] + [C.POINTER(C.c_size_t)] * 3
         # reference entry points
         L.mm_chain_dp.restype = vp
         L.mm_chain_dp.argtypes = [C.c_int] * 8 + [i64, vp, C.POINTER(C.c_int), C.POINTER(vp), vp]
@@ -308,11 +311,61 @@ class ChainContext:
     def stage_reset(self):
         lib().mm2b200_stage_reset(self._h)
 
+    def set_upload(self, wire: bool = True, threads: int = 0):
+        """Host batcher: 8-byte wire format for the anchor upload (default on) and its encoder thread count (0 = all cores)."""
+        _check(lib().mm2b200_set_upload(self._h, 1 if wire else 0, threads))
+
+    def upload_stats(self):
+        """(bytes copied host->device, sub-batches sent in the wire format) of the last batch call."""
+        b, n = C.c_int64(), C.c_int64()
+        _check(lib().mm2b200_upload_stats(self._h, C.byref(b), C.byref(n)))
+        return b.value, n.value
+
     def int_peak(self, mode: int = 1) -> float:
         """Measured integer lane-ops/s of the device (mode 0: ALU pipe only; 1: ALU+FMA-pipe mix)."""
         v = C.c_double()
         _check(lib().mm2b200_int_peak(self._h, mode, C.byref(v)))
         return v.value
+
+
+WIRE_BLOCK = 256
+
+
+def wire_encode(a: np.ndarray):
+    """mm2b200_wire_encode (host only): returns (packed u64[n], descriptors u64[blocks], dict u32[entries]) or None
+    when the anchors do not fit the wire format."""
+    a = _anchors(a)
+    n = len(a)
+    nblk = (n + WIRE_BLOCK - 1) // WIRE_BLOCK
+    cap = n * 8 + nblk * 8 + nblk * 2 * WIRE_BLOCK * 4 + 8
+    buf = np.zeros(cap, dtype=np.uint8)
+    nb, pt, pd = C.c_size_t(), C.c_size_t(), C.c_size_t()
+    rc = lib().mm2b200_wire_encode(a.ctypes.data, n, buf.ctypes.data, cap, C.byref(nb), C.byref(pt), C.byref(pd))
+    if rc == 1:
+        return None
+    _check(rc)
+    packed = buf[:n * 8].view("<u8").copy()
+    tab = buf[pt.value:pt.value + nblk * 8].view("<u8").copy()
+    d = buf[pd.value:nb.value].view("<u4").copy()
+    return packed, tab, d
+
+
+def wire_decode(packed: np.ndarray, tab: np.ndarray, d: np.ndarray) -> np.ndarray:
+    """numpy restatement of k_unpack_wire (tests)."""
+    n = len(packed)
+    out = np.zeros((n, 2), dtype=np.uint64)
+    if n == 0:
+        return out
+    t = tab[np.arange(n) // WIRE_BLOCK]
+    pos = (t & np.uint64(0xffffffff)).astype(np.int64)
+    nhx = ((t >> np.uint64(32)) & np.uint64(0xffff)).astype(np.int64)
+    qbits = np.uint64(24) - (t >> np.uint64(48))
+    mid = (packed >> np.uint64(32)) & np.uint64(0xffffff)
+    hx = d[pos + (packed >> np.uint64(56)).astype(np.int64)].astype(np.uint64)
+    hy = d[pos + nhx + (mid >> qbits).astype(np.int64)].astype(np.uint64)
+    out[:, 0] = (hx << np.uint64(32)) | (packed & np.uint64(0xffffffff))
+    out[:, 1] = (hy << np.uint64(32)) | (mid & ((np.uint64(1) << qbits) - np.uint64(1)))
+    return out
 
 
 def partition_reads(offs, n_parts: int) -> np.ndarray:

@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -76,6 +77,120 @@ static const char *const STAGE_NAMES[] = { "prep", "fill", "compact", "tail", "g
 enum { ST_PREP = 0, ST_FILL, ST_COMPACT, ST_TAIL, ST_GATHER, ST_N };
 
 // ---------------------------------------------------------------------------------------------------------
+// host batcher: worker threads that encode a sub-batch of anchors into the 8-byte wire format while the previous
+// sub-batch is on the PCIe bus (the upload is the end-to-end bottleneck: 16 B/anchor at ~55 GB/s)
+// ---------------------------------------------------------------------------------------------------------
+struct WorkerPool {
+	std::vector<std::thread> th;
+	std::mutex mu;
+	std::condition_variable cv_go, cv_done;
+	uint64_t gen = 0;
+	int pending = 0;
+	bool stop = false;
+	const std::function<void(int)> *fn = nullptr;
+	int size() const { return (int)th.size() + 1; }       // the caller is worker 0
+	void start(int n)
+	{
+		uint64_t g0;
+		{ std::lock_guard<std::mutex> lk(mu); g0 = gen; }
+		for (int k = 1; k < n; ++k) th.emplace_back([this, k, g0] { loop(k, g0); });
+	}
+	void loop(int k, uint64_t seen)
+	{
+		for (;;) {
+			std::unique_lock<std::mutex> lk(mu);
+			cv_go.wait(lk, [&] { return stop || gen != seen; });
+			if (stop) return;
+			seen = gen;
+			const std::function<void(int)> *f = fn;
+			lk.unlock();
+			(*f)(k);
+			lk.lock();
+			if (--pending == 0) cv_done.notify_one();
+		}
+	}
+	void run(const std::function<void(int)> &f)
+	{
+		if (!th.empty()) {
+			{ std::lock_guard<std::mutex> lk(mu); fn = &f; pending = (int)th.size(); ++gen; }
+			cv_go.notify_all();
+		}
+		f(0);
+		if (!th.empty()) {
+			std::unique_lock<std::mutex> lk(mu);
+			cv_done.wait(lk, [&] { return pending == 0; });
+		}
+	}
+	void shutdown()
+	{
+		{ std::lock_guard<std::mutex> lk(mu); stop = true; }
+		cv_go.notify_all();
+		for (auto &t : th) t.join();
+		th.clear();
+		stop = false;
+	}
+};
+
+struct WirePart {                 // what one worker produced for its range of blocks
+	std::vector<uint32_t> dict;   // dictionaries of its blocks, back to back
+	bool ok = true;
+};
+
+// Encode blocks [b0, b1) of a sub-batch (format: chain_kernels.cu, k_unpack_wire).  tab[b] receives the block's
+// descriptor with a dictionary position local to this part; the caller rebases it.  Returns false when a block does
+// not fit the format (its qpos values need more bits than the block's flags|qspan dictionary leaves free).
+static bool wire_encode(const mm128_t *src, int64_t n, int64_t b0, int64_t b1, uint64_t *out, uint64_t *tab, std::vector<uint32_t> &dict)
+{
+	dict.clear();
+	for (int64_t b = b0; b < b1; ++b) {
+		const int64_t k0 = b << WIRE_BLOCK_SHIFT, k1 = k0 + WIRE_BLOCK < n ? k0 + WIRE_BLOCK : n;
+		uint32_t hx[WIRE_BLOCK + 1], hy[WIRE_BLOCK], lastx, qor = 0, ydiff = 0;
+		int nhx = 0, nhy = 1, ybits = 0;
+		// Common case in one pass: flags|seg|qspan is the same for the whole block (no y index bits).  The x dictionary gets
+		// one entry per change of strand|rid -- x is sorted inside a read, so a change is almost always a new value and
+		// looking for an earlier copy is not worth it; 256 anchors can never need more than 256 entries.
+		hy[0] = (uint32_t)(src[k0].y >> 32);
+		lastx = ~(uint32_t)(src[k0].x >> 32);
+		for (int64_t k = k0; k < k1; ++k) {
+			const uint64_t x = src[k].x, y = src[k].y;
+			const uint32_t vx = (uint32_t)(x >> 32);
+			hx[nhx] = vx;                                 // branch-free: the slot is claimed only when the value changed
+			nhx += vx != lastx;
+			lastx = vx;
+			ydiff |= (uint32_t)(y >> 32) ^ hy[0];
+			qor |= (uint32_t)y;
+			out[k] = (x & 0xffffffffull) | (y << 32) | ((uint64_t)(nhx - 1) << 56);
+		}
+		if (ydiff) {                                      // several flags|seg|qspan values: second pass with a y index per anchor
+			uint8_t iy[WIRE_BLOCK], slot[256];
+			memset(slot, 0, sizeof(slot));
+			uint32_t lasty = hy[0];
+			int cy = 0;
+			for (int64_t k = k0; k < k1; ++k) {
+				const uint32_t vy = (uint32_t)(src[k].y >> 32);
+				if (vy != lasty) {
+					cy = slot[vy & 0xff];                     // direct-mapped on qspan, the part that varies (HPC minimizers)
+					if (hy[cy] != vy) {
+						for (cy = 0; cy < nhy && hy[cy] != vy; ++cy) {}
+						if (cy == nhy) hy[nhy++] = vy;
+						slot[vy & 0xff] = (uint8_t)cy;
+					}
+					lasty = vy;
+				}
+				iy[k - k0] = (uint8_t)cy;
+			}
+			while ((1 << ybits) < nhy) ++ybits;
+			if (qor >> (24 - ybits)) return false;
+			for (int64_t k = k0; k < k1; ++k) out[k] |= (uint64_t)iy[k - k0] << (32 + 24 - ybits);
+		} else if (qor >> 24) return false;               // a qpos of 2^24 or more
+		tab[b] = (uint64_t)dict.size() | ((uint64_t)nhx << 32) | ((uint64_t)ybits << 48);
+		dict.insert(dict.end(), hx, hx + nhx);
+		dict.insert(dict.end(), hy, hy + nhy);
+	}
+	return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // one in-flight sub-batch
 // ---------------------------------------------------------------------------------------------------------
 struct Slot {
@@ -101,6 +216,11 @@ struct mm2b200_ctx {
 	std::vector<Slot> slots;
 	std::mutex mu;
 	std::atomic<int64_t> launches{0};
+	// upload wire format (host batcher)
+	bool wire = false;
+	WorkerPool pool;
+	std::vector<WirePart> parts;
+	int64_t h2d_bytes = 0, wire_sub_batches = 0;   // of the last batch call
 	// results (pinned)
 	PinnedBuf r_n_u, r_u_off, r_b_off, r_u, r_b, r_rec_off, r_rec;
 	// profiling
@@ -288,6 +408,16 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 	}
 	query_launch_cfg(&ctx->lc);
 	ctx->lc.count_visited = c.count_visited;
+	{	// host batcher threads: opt-in (MM2B200_WIRE=1 or mm2b200_set_upload; MM2B200_WIRE_THREADS overrides the thread count).
+		// Off by default: on the measured GPU box (16 vCPUs) encoding 77 M anchors costs more host memory time than the
+		// 0.55 GB it keeps off the PCIe bus (e2e 41 ms vs 27 ms raw, profiles/r01j_wire_upload.md).
+		const char *ew = getenv("MM2B200_WIRE"), *et = getenv("MM2B200_WIRE_THREADS");
+		ctx->wire = ew && atoi(ew) != 0;
+		int nt = et ? atoi(et) : (int)std::thread::hardware_concurrency();
+		if (nt > 16) nt = 16;
+		if (nt < 1) nt = 1;
+		if (ctx->wire) ctx->pool.start(nt);
+	}
 	*out = ctx;
 	return MM2B200_OK;
 }
@@ -295,6 +425,7 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 {
 	if (!ctx) return;
+	ctx->pool.shutdown();
 	cudaSetDevice(ctx->device);
 	for (auto &s : ctx->slots) {
 		if (s.stream) cudaStreamSynchronize(s.stream);
@@ -313,6 +444,41 @@ extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 }
 
 extern "C" int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx) { return ctx ? ctx->launches.load() : 0; }
+
+extern "C" int mm2b200_set_upload(mm2b200_ctx_t *ctx, int32_t wire, int32_t threads)
+{
+	if (!ctx || threads < 0) return fail(MM2B200_ERR_ARG, "bad upload settings");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	ctx->pool.shutdown();
+	ctx->wire = wire != 0;
+	int nt = threads ? threads : (int)std::thread::hardware_concurrency();
+	if (nt > 64) nt = 64;
+	if (nt < 1) nt = 1;
+	if (ctx->wire) ctx->pool.start(nt);
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_wire_encode(const mm128_t *a, int64_t n, void *buf, size_t cap, size_t *bytes, size_t *tab_pos, size_t *dict_pos)
+{
+	if (n < 0 || (n > 0 && !a) || !buf || !bytes || !tab_pos || !dict_pos) return fail(MM2B200_ERR_ARG, "bad wire_encode arguments");
+	const int64_t nblk = (n + WIRE_BLOCK - 1) >> WIRE_BLOCK_SHIFT;
+	const size_t pos_tab = (size_t)n * 8, pos_dict = pos_tab + (size_t)nblk * 8;
+	if (cap < pos_dict) return fail(MM2B200_ERR_ARG, "wire buffer too small (%zu < %zu)", cap, pos_dict);
+	std::vector<uint32_t> dict;
+	if (!wire_encode(a, n, 0, nblk, (uint64_t*)buf, (uint64_t*)((char*)buf + pos_tab), dict)) return 1;
+	if (cap < pos_dict + dict.size() * 4) return fail(MM2B200_ERR_ARG, "wire buffer too small for the dictionaries");
+	if (!dict.empty()) memcpy((char*)buf + pos_dict, dict.data(), dict.size() * 4);
+	*bytes = pos_dict + dict.size() * 4; *tab_pos = pos_tab; *dict_pos = pos_dict;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_upload_stats(const mm2b200_ctx_t *ctx, int64_t *h2d_bytes, int64_t *wire_sub_batches)
+{
+	if (!ctx) return fail(MM2B200_ERR_ARG, "NULL ctx");
+	if (h2d_bytes) *h2d_bytes = ctx->h2d_bytes;
+	if (wire_sub_batches) *wire_sub_batches = ctx->wire_sub_batches;
+	return MM2B200_OK;
+}
 
 extern "C" int mm2b200_stage_ms(mm2b200_ctx_t *ctx, const char *stage, double *ms, int64_t *launches)
 {
@@ -415,6 +581,51 @@ static int finish_b(BatchJob &job, Slot &s)
 	return MM2B200_OK;
 }
 
+// Encode one sub-batch into the slot's pinned staging buffer with the worker pool, upload it in one copy and restore
+// a[] on the device.  *sent stays false when the anchors do not fit the wire format (the caller uploads them raw).
+static int upload_wire(mm2b200_ctx *ctx, Slot &s, const mm128_t *src, int64_t na, bool *sent)
+{
+	int rc;
+	const int64_t nblk = (na + WIRE_BLOCK - 1) >> WIRE_BLOCK_SHIFT;
+	const size_t dict_cap = (size_t)na + 2 * WIRE_BLOCK;                       // beyond 4 B/anchor the format no longer pays
+	const size_t pos_tab = (size_t)na * 8, pos_dict = pos_tab + (size_t)nblk * 8;
+	if ((rc = s.h_a.reserve(pos_dict + dict_cap * 4))) return rc;
+	char *h = s.h_a.as<char>();
+	uint64_t *out = (uint64_t*)h, *tab = (uint64_t*)(h + pos_tab);
+	uint32_t *dict = (uint32_t*)(h + pos_dict);
+	int parts = (int)(nblk / 256);                                              // >= 64 Ki anchors per worker
+	if (parts > ctx->pool.size()) parts = ctx->pool.size();
+	if (parts < 1) parts = 1;
+	if ((int)ctx->parts.size() < parts) ctx->parts.resize(parts);
+	std::vector<WirePart> &pp = ctx->parts;
+	const std::function<void(int)> work = [&](int k) {
+		if (k >= parts) return;
+		const int64_t b0 = nblk * k / parts, b1 = nblk * (k + 1) / parts;
+		pp[k].ok = wire_encode(src, na, b0, b1, out, tab, pp[k].dict);
+	};
+	if (parts == 1) work(0); else ctx->pool.run(work);
+	size_t total = 0;
+	for (int k = 0; k < parts; ++k) {
+		if (!pp[k].ok) return MM2B200_OK;
+		total += pp[k].dict.size();
+	}
+	if (total > dict_cap) return MM2B200_OK;
+	size_t base = 0;
+	for (int k = 0; k < parts; ++k) {                                           // rebase the part-local dictionary positions
+		const int64_t b0 = nblk * k / parts, b1 = nblk * (k + 1) / parts;
+		if (base) for (int64_t b = b0; b < b1; ++b) tab[b] += base;
+		if (!pp[k].dict.empty()) memcpy(dict + base, pp[k].dict.data(), pp[k].dict.size() * 4);
+		base += pp[k].dict.size();
+	}
+	const size_t bytes = pos_dict + total * 4;
+	// device staging: the compaction records (24 B/anchor) are dead until k_compact, long after the unpack
+	CUDA_TRY(cudaMemcpyAsync((void*)s.w.rec, h, bytes, cudaMemcpyHostToDevice, s.stream));
+	{ StageTimer t(ctx, s.stream, ST_PREP); t.done(launch_unpack_wire(s.w, (const void*)s.w.rec, pos_tab, pos_dict, s.stream)); }
+	ctx->h2d_bytes += (int64_t)bytes;
+	*sent = true;
+	return MM2B200_OK;
+}
+
 static int run_batch(BatchJob &job)
 {
 	mm2b200_ctx *ctx = job.ctx;
@@ -430,6 +641,7 @@ static int run_batch(BatchJob &job)
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	CUDA_TRY(cudaSetDevice(ctx->device));
 	const int64_t R = job.n_reads;
+	ctx->h2d_bytes = 0; ctx->wire_sub_batches = 0;
 	// reserve the pinned result arenas to their upper bounds up front (sum n_v <= N, n_u <= n / max(min_cnt,1),
 	// new_i <= n): a buffer must never move while an earlier chunk's D2H copy is still landing in it
 	const int64_t N = R > 0 ? job.offs[R] - job.offs[0] : 0;
@@ -485,12 +697,21 @@ static int run_batch(BatchJob &job)
 		CUDA_TRY(cudaMemcpyAsync((void*)w.offs, ho, (size_t)(nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
 		void *dst = job.mode == MODE_BOTTOM ? (void*)w.rec : (void*)w.a;
 		const char *src = job.src + (size_t)job.offs[r0] * job.elem;
+		ctx->h2d_bytes += (nr + 1) * 8;
 		if (na) {
-			if (job.src_pinned) CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+			bool sent = false;
+			if (ctx->wire && job.mode != MODE_BOTTOM) {
+				if ((rc = upload_wire(ctx, s, (const mm128_t*)src, na, &sent))) return rc;
+			}
+			if (sent) ++ctx->wire_sub_batches;
 			else {
-				if ((rc = s.h_a.reserve((size_t)na * job.elem))) return rc;
-				memcpy(s.h_a.ptr, src, (size_t)na * job.elem);
-				CUDA_TRY(cudaMemcpyAsync(dst, s.h_a.ptr, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+				if (job.src_pinned) CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+				else {
+					if ((rc = s.h_a.reserve((size_t)na * job.elem))) return rc;
+					memcpy(s.h_a.ptr, src, (size_t)na * job.elem);
+					CUDA_TRY(cudaMemcpyAsync(dst, s.h_a.ptr, (size_t)na * job.elem, cudaMemcpyHostToDevice, s.stream));
+				}
+				ctx->h2d_bytes += na * (int64_t)job.elem;
 			}
 		}
 		if (job.mode == MODE_BOTTOM) {

@@ -77,6 +77,10 @@ int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 int launch_gather(const Workspace &w, cudaStream_t s);
 int launch_pack_records(const Workspace &w, cudaStream_t s);
 int launch_export_fp(const Workspace &w, cudaStream_t s);       // debug: wrec -> f[], p[] (per-read indices)
+// wire format of the upload: [packed u64 x n][block descriptors u64 x blocks][dict u32 x entries]; restores w.a
+#define WIRE_BLOCK_SHIFT 8
+#define WIRE_BLOCK (1 << WIRE_BLOCK_SHIFT)
+int launch_unpack_wire(const Workspace &w, const void *d_wire, size_t tab_pos, size_t dict_pos, cudaStream_t s);
 void query_launch_cfg(LaunchCfg *cfg);
 long long launch_int_peak(int mode, int grid, int iters, unsigned *d_out, cudaStream_t s);
 

@@ -1442,6 +1442,40 @@ int launch_pack_records(const Workspace &w, cudaStream_t s)
 	return n + 1;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// wire format of the upload (host batcher -> device): 8 bytes per anchor plus small dictionaries instead of 16.
+// Inside a block of WIRE_BLOCK consecutive anchors the high half of x (strand|rid) and the high half of y
+// (flags|seg|qspan, minimap.h:48-55) take few distinct values, so each block carries one dictionary for each and an
+// anchor travels as  low32(x) | (qpos | iy << qbits) << 32 | ix << 56  with qbits = 24 - ybits, ybits = bits needed for
+// the block's y dictionary.  Block descriptor: dictionary position (32) | x entries (16) | ybits (16); the y entries
+// follow the x entries.  Lossless; a sub-batch with a block whose qpos values do not fit qbits is uploaded raw.
+// This kernel restores a[] in HBM.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_unpack_wire(ulonglong2 *__restrict__ a, const uint64_t *__restrict__ packed,
+                                                     const uint64_t *__restrict__ tab, const uint32_t *__restrict__ dict, int n)
+{
+	for (int k = blockIdx.x * 256 + threadIdx.x; k < n; k += gridDim.x * 256) {
+		const uint64_t pk = packed[k];
+		const uint64_t d = tab[k >> WIRE_BLOCK_SHIFT];
+		const unsigned pos = (unsigned)d, nhx = (unsigned)(d >> 32) & 0xffffu, qbits = 24u - (unsigned)(d >> 48);
+		const unsigned mid = (unsigned)(pk >> 32) & 0xffffffu;
+		const unsigned hx = dict[pos + (unsigned)(pk >> 56)];
+		const unsigned hy = dict[pos + nhx + (mid >> qbits)];
+		ulonglong2 o;
+		o.x = ((uint64_t)hx << 32) | (pk & 0xffffffffull);
+		o.y = ((uint64_t)hy << 32) | (mid & ((1u << qbits) - 1u));
+		a[k] = o;
+	}
+}
+
+int launch_unpack_wire(const Workspace &w, const void *d_wire, size_t tab_pos, size_t dict_pos, cudaStream_t s)
+{
+	const char *base = (const char*)d_wire;
+	k_unpack_wire<<<blocks_for(w.n_anchors, 256 * 4, 148 * 32), 256, 0, s>>>((ulonglong2*)w.a, (const uint64_t*)base,
+		(const uint64_t*)(base + tab_pos), (const uint32_t*)(base + dict_pos), w.n_anchors);
+	return 1;
+}
+
 int launch_export_fp(const Workspace &w, cudaStream_t s)
 {
 	k_export_fp<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w);
