@@ -50,29 +50,42 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
 		unsigned long long sum = 0, prev_last_x = 0;
 		int carry_start = b, multiseg = 0;
-		for (int base = b; base < e; base += 32) {
-			const int i = base + lane;
-			const bool valid = i < e;
-			ulonglong2 ai = valid ? w.a[i] : make_ulonglong2(0ull, 0ull);
-			unsigned long long xp = __shfl_up_sync(FULL, ai.x, 1);
-			if (lane == 0) xp = prev_last_x;
-			const bool start = valid && (i == b || ai.x - xp > mdx);
-			prev_last_x = __shfl_sync(FULL, ai.x, 31);
-			if (valid) {
-				const int span = (int)((ai.y >> 32) & 0xff);
-				sum += (unsigned)span;
-				// f = span, p = -1, v = span for every anchor that starts a run (singletons are finished by this; the
-				// fill kernels write all other anchors of a run themselves, so those are not touched here)
-				if (start) { w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1); w.v[i] = span; }
-				w.t[i] = -1;
-				if ((ai.y >> 48) & 0xff) multiseg = 1;
+		// four 512-byte tiles are requested before the first is consumed (one tile in flight per warp left the kernel at
+		// 44 % of the copy bandwidth); the tiles are then walked in order because run boundaries carry across them
+		for (int base0 = b; base0 < e; base0 += 128) {
+			ulonglong2 tile[4];
+#pragma unroll
+			for (int k = 0; k < 4; ++k) {
+				const int i = base0 + 32 * k + lane;
+				tile[k] = i < e ? __ldcs(&w.a[i]) : make_ulonglong2(0ull, 0ull);
 			}
-			const unsigned smask = __ballot_sync(FULL, start);
-			const unsigned below = smask & lanemask_lt(lane);
-			const int prev_start = below ? base + (31 - __clz(below)) : carry_start;
-			const bool emit = start && i != b && (i - prev_start) >= 2;   // this start closes the run [prev_start, i)
-			if (emit) emit_unit(w, prev_start, i - prev_start, r);
-			if (smask) carry_start = base + (31 - __clz(smask));
+#pragma unroll
+			for (int k = 0; k < 4; ++k) {
+				const int base = base0 + 32 * k;
+				if (base >= e) break;
+				const int i = base + lane;
+				const bool valid = i < e;
+				const ulonglong2 ai = tile[k];
+				unsigned long long xp = __shfl_up_sync(FULL, ai.x, 1);
+				if (lane == 0) xp = prev_last_x;
+				const bool start = valid && (i == b || ai.x - xp > mdx);
+				prev_last_x = __shfl_sync(FULL, ai.x, 31);
+				if (valid) {
+					const int span = (int)((ai.y >> 32) & 0xff);
+					sum += (unsigned)span;
+					// f = span, p = -1, v = span for every anchor that starts a run (singletons are finished by this; the
+					// fill kernels write all other anchors of a run themselves, so those are not touched here)
+					if (start) { w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1); w.v[i] = span; }
+					w.t[i] = -1;
+					if ((ai.y >> 48) & 0xff) multiseg = 1;
+				}
+				const unsigned smask = __ballot_sync(FULL, start);
+				const unsigned below = smask & lanemask_lt(lane);
+				const int prev_start = below ? base + (31 - __clz(below)) : carry_start;
+				const bool emit = start && i != b && (i - prev_start) >= 2;   // this start closes the run [prev_start, i)
+				if (emit) emit_unit(w, prev_start, i - prev_start, r);
+				if (smask) carry_start = base + (31 - __clz(smask));
+			}
 		}
 		for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync(FULL, sum, d);
 		multiseg = __any_sync(FULL, multiseg);
@@ -291,6 +304,28 @@ static __device__ __forceinline__ void sts_u16(unsigned addr, int v)
 	asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "h"((unsigned short)v) : "memory");
 }
 
+// a + IMM issued on the FMA pipe (IMAD a, one, IMM) instead of the ALU pipe (VIADD): in the fill kernel the ALU pipe
+// (compares, logic, selects, min/max: one warp instruction every two cycles) is the busier of the two integer pipes
+// (ncu capture k: ALU 80 %, FMA 20 %), so plain add-immediates are moved over.  `one` is a register holding 1 that is
+// opaque to the optimiser.
+template <int IMM> static __device__ __forceinline__ int addi_fma(int a, int one)
+{
+	int d;
+	asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "n"(IMM));
+	return d;
+}
+// 2 * a + b as one IMAD (table address)
+static __device__ __forceinline__ unsigned mad2_fma(unsigned a, unsigned b)
+{
+	unsigned d;
+	asm("mad.lo.u32 %0, %1, 2, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+template <int IMM> static __device__ __forceinline__ unsigned addi_fma(unsigned a, int one)
+{
+	return (unsigned)addi_fma<IMM>((int)a, one);
+}
+
 // 1 << k with PTX shift semantics: 0 for k >= 32 (C++ leaves that undefined and the compiler would emit a wrapping shift)
 static __device__ __forceinline__ unsigned bit_or_zero(unsigned k)
 {
@@ -420,13 +455,13 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
                                                        const int4 rj, const int vj, const bool marked_mem,
                                                        const unsigned xi, const int qi, const int span,
                                                        const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
-                                                       const int dd, const int cost, const int B0, const int max_skip)
+                                                       const int dd, const int cost, const int B0, const int max_skip, const int one)
 {
 	const int j = jb - lane;
 	const unsigned dr = xi - (unsigned)rj.x;
 	const int dq = qi - rj.y;
 	const bool inw = (j >= jlo) && (dr <= mdx);
-	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
+	const bool skip = !inw || addi_fma<-1>(dr, one) >= dr_max || addi_fma<-1>((unsigned)dq, one) >= dq_max || dd > bw;
 	const int sc = min(min(dq, (int)dr), span) - cost + rj.z;
 	const int scx = skip ? (int)0x80000000 : sc;
 	const int pj = rj.w;
@@ -443,7 +478,7 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 		                         xi, qi, span, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
 	far = mk && kt >= 32u;
 	const bool marked = ((mloc >> lane) & 1u) || marked_mem;
-	if ((gt & (low - 1u)) != 0u) {
+	if ((gt & addi_fma<-1>(low, one)) != 0u) {
 		// several lanes before the chunk maximum beat the running maximum => at least two IMPROVE lanes:
 		// exclusive prefix-max scan for the exact set, then the general segment-by-segment replay
 		int pm = scx;
@@ -474,7 +509,7 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 		return (brk >= 0 || !all_in) ? 1 : 0;
 	}
 	const unsigned imp = M > max_f ? low : 0u;            // the only IMPROVE lane, if any
-	const unsigned below = imp - 1u;                      // lanes visited before it (all lanes when there is none)
+	const unsigned below = addi_fma<-1>(imp, one);        // lanes visited before it (all lanes when there is none)
 	const unsigned mm = __ballot_sync(FULL, marked && !skip) & ~imp;
 	const unsigned seg1 = mm & below, seg2 = mm & ~(imp | below);
 	const int c1 = __popc(seg1), c2 = __popc(seg2);
@@ -582,6 +617,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
 	// opaque to the optimiser: keep the three per-warp base addresses in registers instead of re-deriving them per access
 	asm volatile("" : "+r"(ring_w), "+r"(abuf_w), "+r"(tab_w));
+	const int one = 1 + (int)threadIdx.y;         // see addi_fma (threadIdx.y is 0, which ptxas cannot know)
 
 	const int n_long = w.counters[CNT_LONG_UNITS];
 	const int n_units = w.counters[CNT_UNITS] + n_long;
@@ -655,11 +691,11 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			int4 rj = lds128<0>(raddr);
 			int vj = lds32<SM_VRING>(raddr);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-			int cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
+			int cost = TABLE ? lds_u16(mad2_fma(min((unsigned)dd0, (unsigned)bw), tab_w)) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 			if (FULLV) ++n_chunks;
-			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 1, jlo, lane, rj, vj, false,
-			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
-			if (!done && i - 33 >= jlo) {
+			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, addi_fma<-1>(i, one), jlo, lane, rj, vj, false,
+			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
+			if (!done && addi_fma<-33>(i, one) >= jlo) {
 				if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
 				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
 				__syncwarp();
@@ -673,7 +709,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
-					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
 					if (!done && far) t[rj.w] = i;                // marks beyond this chunk (the scalar path writes its own)
 				}
 				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
@@ -690,7 +726,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 						dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 						cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 						done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
-						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip);
+						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
 						if (!done && far) t[rj.w] = i;
 					}
 				}
@@ -698,9 +734,9 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
 			sts128<0>(waddr, make_int4((int)xi, qi, max_f, max_j));
 			sts32<SM_VRING>(waddr, max(vbest, max_f));
-			aaddr += 16u;
-			raddr = ring_w | ((raddr + 16u) & (RING * 16u - 1u));
-			waddr = ring_w | ((waddr + 16u) & (RING * 16u - 1u));
+			aaddr = addi_fma<16>(aaddr, one);
+			raddr = ring_w | (addi_fma<16>(raddr, one) & (RING * 16u - 1u));
+			waddr = ring_w | (addi_fma<16>(waddr, one) & (RING * 16u - 1u));
 			// (no warp sync needed: every lane stored the same words, so a later load by any lane sees at least its own store)
 		}
 			// flush the block (deep windows and the later kernels read the records from global memory)
