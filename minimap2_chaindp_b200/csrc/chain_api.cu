@@ -212,7 +212,6 @@ struct mm2b200_ctx {
 	int profile = 0;
 	int64_t slot_anchors = 0;
 	bool adaptive_slots = true;
-	bool taper = true;                // smaller sub-batches at the end of a batch (MM2B200_TAPER=0 turns it off)
 	LaunchCfg lc{};
 	std::vector<Slot> slots;
 	std::mutex mu;
@@ -403,7 +402,6 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 	ctx->slot_anchors = c.slot_anchors > 0 ? c.slot_anchors : ((int64_t)8 << 20);
 	const int ns = c.n_slots > 0 ? c.n_slots : 3;
 	ctx->adaptive_slots = c.n_slots <= 0;      // default: long-read batches may add slots (see run_batch)
-	{ const char *et = getenv("MM2B200_TAPER"); ctx->taper = !(et && atoi(et) == 0); }
 	for (int k = 0; k < ns; ++k) {
 		int rc = add_slot(ctx);
 		if (rc) { mm2b200_destroy(ctx); return rc; }
@@ -677,17 +675,9 @@ static int run_batch(BatchJob &job)
 	const int S = (int)ctx->slots.size();
 	int64_t r0 = 0, chunk = 0, next_a = 0;   // next_a: oldest chunk whose totals have not been collected yet
 	while (r0 < R) {
-		// greedy chunk: consecutive reads up to slot_anchors anchors (at least one read).  Towards the end of the batch the
-		// chunks are halved (down to 512 Ki anchors): nothing overlaps the kernels and the download of the LAST chunk, so it
-		// should be small (the upload, the bottleneck, is unaffected by where the cuts are).
-		int64_t limit = ctx->slot_anchors;
-		if (ctx->taper) {
-			const int64_t rest = (job.offs[R] - job.offs[r0]) / 2, floor_ = (int64_t)512 << 10;
-			if (rest < limit) limit = rest > floor_ ? rest : floor_;
-			if (limit > ctx->slot_anchors) limit = ctx->slot_anchors;
-		}
+		// greedy chunk: consecutive reads up to slot_anchors anchors (at least one read)
 		int64_t r1 = r0 + 1;
-		while (r1 < R && job.offs[r1 + 1] - job.offs[r0] <= limit && r1 - r0 < ((int64_t)1 << 24)) ++r1;
+		while (r1 < R && job.offs[r1 + 1] - job.offs[r0] <= ctx->slot_anchors && r1 - r0 < ((int64_t)1 << 24)) ++r1;
 		const int64_t na = job.offs[r1] - job.offs[r0], nr = r1 - r0;
 		Slot &s = ctx->slots[chunk % S];
 		if (s.state == 1) {     // reuse: collect (in chunk order) everything up to the chunk that still owns this slot
