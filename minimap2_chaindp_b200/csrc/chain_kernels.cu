@@ -1394,6 +1394,7 @@ static int fill_tab_entries(const mm2b200_params_t &prm)
 	return (prm.bw + 1 + 7) & ~7;
 }
 
+static int g_fill_ctas_cap = 0;   // MM2B200_FILL_CTAS: cap on resident fill CTAs per SM (0 = occupancy), see tools/overlap_probe.py
 template <bool TABLE, bool FULLV, bool WIDE>
 static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
@@ -1407,7 +1408,8 @@ static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, in
 		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, FILL_WARPS * 32, smem);
 		oc[0] = occ < 1 ? 1 : occ; oc[1] = smem;
 	}
-	kern<<<sms * oc[0], FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries);
+	const int per_sm = (g_fill_ctas_cap > 0 && g_fill_ctas_cap < oc[0]) ? g_fill_ctas_cap : oc[0];
+	kern<<<sms * per_sm, FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries);
 }
 
 void query_launch_cfg(LaunchCfg *cfg)
@@ -1419,6 +1421,8 @@ void query_launch_cfg(LaunchCfg *cfg)
 	if (occ < 1) occ = 1;
 	cfg->sm_count = sms;
 	cfg->fill_blocks_per_sm = occ;
+	const char *ec = getenv("MM2B200_FILL_CTAS");
+	g_fill_ctas_cap = ec ? atoi(ec) : 0;
 }
 
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
