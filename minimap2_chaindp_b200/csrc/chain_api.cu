@@ -724,7 +724,7 @@ static int run_batch(BatchJob &job)
 			else {
 				StageTimer t(ctx, s.stream, ST_GATHER);
 				int nl = launch_pack_records(w, s.stream);
-				if (job.dbg_p || job.dbg_f) nl += launch_export_fp(w, s.stream);
+				if (job.dbg_p || job.dbg_f || job.dbg_v) nl += launch_export_fp(w, s.stream);
 				t.done(nl);
 			}
 		}

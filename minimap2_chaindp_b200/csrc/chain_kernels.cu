@@ -73,13 +73,20 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 				if (valid) {
 					const int span = (int)((ai.y >> 32) & 0xff);
 					sum += (unsigned)span;
-					// f = span, p = -1, v = span for every anchor that starts a run (singletons are finished by this; the
-					// fill kernels write all other anchors of a run themselves, so those are not touched here)
-					if (start) { w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1); w.v[i] = span; }
-					w.t[i] = -1;
 					if ((ai.y >> 48) & 0xff) multiseg = 1;
 				}
 				const unsigned smask = __ballot_sync(FULL, start);
+				if (valid) {
+					// A run start gets f = span, p = -1, v = span (the fill kernels write all other anchors of a run).  A singleton
+					// (a start whose successor starts the next run, or the last anchor of the read) needs no record at all: its
+					// span travels in the mark word, t[i] = -2 - span (decoded in k_compact and k_export_fp), which saves the 20 scattered
+					// bytes here and the 20 bytes the compaction would read back.  Lane 31 cannot see its successor and writes
+					// the full record instead (equally valid).
+					const int span = (int)((ai.y >> 32) & 0xff);
+					const bool single = start && (i + 1 >= e || (lane < 31 && ((smask >> (lane + 1)) & 1u)));
+					if (start && !single) { w.wrec[i] = make_int4((int)(unsigned)ai.x, (int)(unsigned)ai.y, span, -1); w.v[i] = span; }
+					w.t[i] = single ? -2 - span : -1;
+				}
 				const unsigned below = smask & lanemask_lt(lane);
 				const int prev_start = below ? base + (31 - __clz(below)) : carry_start;
 				const bool emit = start && i != b && (i - prev_start) >= 2;   // this start closes the run [prev_start, i)
@@ -774,11 +781,17 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 		new_seed *rec = w.rec + b;
 		int32_t *recp = w.recp + b;
 		int n_new = 0;
+		int t_next = b + lane < e ? w.t[b + lane] : -1;                          // mark word of the tile ahead (decides which loads follow)
 		for (int base = b; base < e; base += 32) {
 			const int i = base + lane;
 			const bool valid = i < e;
 			int pi = -1, vi = 0, fi = 0;
-			if (valid) { const int4 ri = w.wrec[i]; pi = ri.w; fi = ri.z; vi = w.v[i]; }
+			const int ti = t_next;
+			t_next = i + 32 < e ? w.t[i + 32] : -1;
+			if (valid) {
+				if (ti <= -2) fi = vi = -2 - ti;                                  // singleton: k_prep left only its span
+				else { const int4 ri = w.wrec[i]; pi = ri.w; fi = ri.z; vi = w.v[i]; }
+			}
 			const bool E = valid && (vi >= min_sc || pi >= 0);                  // chain.c:109
 			// chain.c:93-107: a predecessor that was not emitted on its own is emitted by its FIRST referencer.  Anchors are
 			// visited in increasing i, so "first" = no earlier tile emitted it (newid still -1) and the lowest lane of this
@@ -1322,6 +1335,8 @@ __global__ void __launch_bounds__(256) k_export_fp(Workspace w)
 	for (int r = gw; r < w.n_reads; r += nw) {
 		const int b = (int)w.offs[r], e = (int)w.offs[r + 1];
 		for (int i = b + lane; i < e; i += 32) {
+			const int ti = w.t[i];
+			if (ti <= -2) { w.f[i] = -2 - ti; w.p[i] = -1; w.v[i] = -2 - ti; continue; }   // singleton (see k_prep)
 			const int4 ri = w.wrec[i];
 			w.f[i] = ri.z;
 			w.p[i] = ri.w >= 0 ? ri.w - b : -1;
