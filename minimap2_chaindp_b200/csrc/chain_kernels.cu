@@ -805,16 +805,15 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 				vp = w.v[pi]; fp = rp.z;
 				cand = !(vp >= min_sc || rp.w >= 0) && w.newid[pi] < 0;
 			}
-			const unsigned grp = __match_any_sync(FULL, cand ? pi : -1 - lane);
+			// (most tiles have no candidate at all -- only a chain's first anchor is one -- and skip the vote; lanes without a
+			// candidate share one group, MATCH.ANY gets slower with the number of distinct values)
+			unsigned grp = 0;
+			if (__any_sync(FULL, cand)) grp = __match_any_sync(FULL, cand ? pi : -1);
 			const bool late = cand && (__ffs(grp) - 1 == lane);
-			const int cnt = (E ? 1 : 0) + (late ? 1 : 0);
-			int incl = cnt;
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				const int o = __shfl_up_sync(FULL, incl, d);
-				if (lane >= d) incl += o;
-			}
-			const int slot = n_new + incl - cnt;          // first record this lane emits
+			// records emitted by the lanes below this one: two ballots instead of a shuffle scan (a lane emits 0, 1 or 2)
+			const unsigned em = __ballot_sync(FULL, E), lm = __ballot_sync(FULL, late);
+			const unsigned lt = lanemask_lt(lane);
+			const int slot = n_new + __popc(em & lt) + __popc(lm & lt);          // first record this lane emits
 			const int my_new = slot + (late ? 1 : 0);
 			if (valid) w.newid[i] = E ? my_new : -1;
 			__syncwarp();
@@ -831,7 +830,7 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 				store_rec(&rec[my_new], w.a[i], pw, fi);
 				recp[my_new] = pw;
 			}
-			n_new += __shfl_sync(FULL, incl, 31);
+			n_new += __popc(em) + __popc(lm);
 		}
 		if (lane == 0) w.new_i[r] = (uint32_t)n_new;
 	}
