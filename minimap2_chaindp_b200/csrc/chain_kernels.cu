@@ -794,42 +794,47 @@ __global__ void __launch_bounds__(256) k_compact(Workspace w, int32_t min_sc)
 			}
 			const bool E = valid && (vi >= min_sc || pi >= 0);                  // chain.c:109
 			// chain.c:93-107: a predecessor that was not emitted on its own is emitted by its FIRST referencer.  Anchors are
-			// visited in increasing i, so "first" = no earlier tile emitted it (newid still -1) and the lowest lane of this
+			// visited in increasing i, so "first" = no earlier tile emitted it (newid still -1; a predecessor inside this tile
+			// cannot have been emitted earlier, its referencers all sit in this tile or later) and the lowest lane of this
 			// tile among those that name it.
-			if (valid) w.newid[i] = -1;
-			__syncwarp();
 			bool cand = false;
-			int vp = 0, fp = 0;
+			int vp = 0, fp = 0, nid_p = -1;
 			if (pi >= 0) {
 				const int4 rp = w.wrec[pi];
 				vp = w.v[pi]; fp = rp.z;
-				cand = !(vp >= min_sc || rp.w >= 0) && w.newid[pi] < 0;
+				if (pi < base) nid_p = w.newid[pi];
+				cand = !(vp >= min_sc || rp.w >= 0) && nid_p < 0;
 			}
 			// (most tiles have no candidate at all -- only a chain's first anchor is one -- and skip the vote; lanes without a
 			// candidate share one group, MATCH.ANY gets slower with the number of distinct values)
 			unsigned grp = 0;
 			if (__any_sync(FULL, cand)) grp = __match_any_sync(FULL, cand ? pi : -1);
-			const bool late = cand && (__ffs(grp) - 1 == lane);
+			const int first = __ffs(grp) - 1;                                   // first referencer of this lane's candidate
+			const bool late = cand && first == lane;
 			// records emitted by the lanes below this one: two ballots instead of a shuffle scan (a lane emits 0, 1 or 2)
 			const unsigned em = __ballot_sync(FULL, E), lm = __ballot_sync(FULL, late);
 			const unsigned lt = lanemask_lt(lane);
 			const int slot = n_new + __popc(em & lt) + __popc(lm & lt);          // first record this lane emits
 			const int my_new = slot + (late ? 1 : 0);
+			// new index of the predecessor without a trip through memory: emitted by this tile's first referencer (its slot),
+			// emitted on its own inside this tile (that lane's my_new), or known from an earlier tile (nid_p)
+			const int pn_late = __shfl_sync(FULL, slot, first & 31);
+			const int pn_tile = __shfl_sync(FULL, my_new, (pi - base) & 31);
+			const int pn = pi < 0 ? -1 : (cand ? pn_late : (pi >= base ? pn_tile : nid_p));
 			if (valid) w.newid[i] = E ? my_new : -1;
 			__syncwarp();
-			if (late) w.newid[pi] = slot;
-			__syncwarp();
 			if (late) {
+				w.newid[pi] = slot;
 				const int32_t pw = (int32_t)(0xfffffffcu | (vp >= min_sc ? 1u : 0u) | (fp < vp ? 2u : 0u));
 				store_rec(&rec[slot], w.a[pi], pw, fp);
 				recp[slot] = pw;
 			}
 			if (E) {
-				const int pn = pi >= 0 ? w.newid[pi] : -1;
 				const int32_t pw = (int32_t)(((unsigned)pn << 2) | (vi >= min_sc ? 1u : 0u) | (fi < vi ? 2u : 0u));
 				store_rec(&rec[my_new], w.a[i], pw, fi);
 				recp[my_new] = pw;
 			}
+			__syncwarp();                                                       // newid[] of this tile is visible to the next one
 			n_new += __popc(em) + __popc(lm);
 		}
 		if (lane == 0) w.new_i[r] = (uint32_t)n_new;
