@@ -15,9 +15,7 @@ struct Unit {
 	int32_t pad;
 };
 
-// CNT_AVG_KEY: bit pattern (sign flipped, so never 0) of the avg_qspan shared by every non-empty read of the sub-batch;
-// CNT_AVG_MIXED: set when two reads disagree (then the tile kernel, which keeps ONE gap-cost table per CTA, stands down)
-enum Counter { CNT_UNITS = 0, CNT_QUEUE = 1, CNT_MULTISEG = 2, CNT_LONG_UNITS = 3, CNT_QUEUE_LONG = 4, CNT_AVG_KEY = 5, CNT_AVG_MIXED = 6, CNT_N = 8 };
+enum Counter { CNT_UNITS = 0, CNT_QUEUE = 1, CNT_MULTISEG = 2, CNT_LONG_UNITS = 3, CNT_QUEUE_LONG = 4, CNT_N = 8 };
 
 // Device workspace of one sub-batch ("slot").  All per-anchor arrays are indexed by the batch-wide anchor index;
 // per-read scratch of the tail lives at the read's own offset offs[r] (every per-read count is <= n_r).
@@ -68,10 +66,6 @@ struct LaunchCfg {
 	int sm_count;
 	int fill_blocks_per_sm;      // generic kernel
 	int count_visited;           // instrumented fast kernel (metric numerator) instead of the plain one
-	int tile_runs;               // runs per warp of the tile kernel (0 = tile kernel off, warp-per-run kernel only)
-	int tile_warps;              // warps per tile CTA
-	int tile_group;              // chunk-0 scoring passes per straight-line block
-	int tile_ctas_per_sm;        // cap on resident tile CTAs per SM (0 = occupancy)
 };
 
 // launchers (chain_kernels.cu); every launcher returns the number of kernels it enqueued

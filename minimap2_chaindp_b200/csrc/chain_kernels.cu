@@ -99,15 +99,8 @@ __global__ void __launch_bounds__(256) k_prep(Workspace w, int32_t max_dist_x)
 		if (lane == 0) {
 			if (e - carry_start >= 2) emit_unit(w, carry_start, e - carry_start, r);
 			// (float)sum_qspan / n  (chain.c:47): u64->float, int64->float, IEEE float divide
-			const float avg = e > b ? __fdiv_rn(__ull2float_rn(sum), __ll2float_rn((long long)(e - b))) : 0.0f;
-			w.avg[r] = avg;
+			w.avg[r] = e > b ? __fdiv_rn(__ull2float_rn(sum), __ll2float_rn((long long)(e - b))) : 0.0f;
 			if (multiseg) atomicOr(&w.counters[CNT_MULTISEG], 1);
-			if (e > b) {   // do all reads share one avg_qspan (one gap-cost table)?  Every non-HPC preset: all spans == k
-				const int key = (int)(__float_as_uint(avg) ^ 0x80000000u);
-				int cur = *(volatile int*)&w.counters[CNT_AVG_KEY];
-				if (cur == 0) { cur = atomicCAS(&w.counters[CNT_AVG_KEY], 0, key); if (cur == 0) cur = key; }
-				if (cur != key) w.counters[CNT_AVG_MIXED] = 1;
-			}
 		}
 	}
 }
@@ -280,7 +273,6 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 //    lane beats the running maximum, L is the only IMPROVE lane (the common case) and no prefix scan is needed.
 #define FILL_WARPS 4
 #define RING 64
-#define XLONG_RUN 4096   // runs at least this long stay with the warp-per-run kernel when the tile kernel is on
 // dynamic shared memory of k_fill_fast, byte offsets from the CTA's base (per warp: 1 KB ring + 1 KB v + 512 B anchors)
 #define SM_RING   0                               // int4 {x, q, f, p} of the last RING anchors, 16 B each
 #define SM_VRING  (FILL_WARPS * RING * 16)        // v[] of the same anchors, 16-byte stride so one register addresses both
@@ -462,7 +454,7 @@ static __device__ __noinline__ int scan_chunk(int &max_f, int &max_j, int &vbest
 }
 
 // The common case of a chunk as straight-line code: at most one IMPROVE lane and a window that is exact per lane
-// (max_dist_x < 2^27, so 32 lanes can never wrap the low 32 bits of x).  Everything is computed with selects; the only
+// (max_dist_x < 2^26, so the 33 gaps down to a chunk's last lane can never wrap the low 32 bits of x).  Everything is computed with selects; the only
 // branch leaves for the general routine above when several lanes before the chunk maximum beat the running maximum.
 template <bool COUNT, bool WIDE>
 static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, int &vbest, int &budget, long long &visited, bool &far,
@@ -581,7 +573,7 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 			nwin = __ffs(~wb) - 1;                        // first one outside are dropped (exact for wide windows too)
 			inw = lane < nwin;
 		}
-	} else done = !__all_sync(FULL, inw);                 // max_dist_x < 2^27: the per-lane test is exact
+	} else done = !__all_sync(FULL, inw);                 // max_dist_x < 2^26: the per-lane test is exact
 	const bool skip = !inw || (dr - 1u) >= dr_max || ((unsigned)dq - 1u) >= dq_max || dd > bw;
 	unsigned live = __ballot_sync(FULL, !skip);
 	if (COUNT) visited += nwin;
@@ -620,13 +612,10 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 // FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
 // (register caps were tried: 40 registers / 12 CTAs per SM 5.70 ms, 32 / 16 CTAs 6.09 ms, 67 / 7 CTAs 5.07 ms, default 48 / 10 CTAs 4.89 ms)
 template <bool TABLE, bool FULLV, bool WIDE>
-__global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries, int tile_on)
+__global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
 	extern __shared__ int4 smem4[];
 	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
-	// with the tile kernel launched beside it (and able to run: one avg_qspan for the whole sub-batch) this kernel
-	// only takes the very long runs, which it walks off the long list with its own cursor
-	const bool xl = tile_on && w.counters[CNT_AVG_MIXED] == 0;
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	// 1 KB-aligned base: a warp's ring is then a naturally aligned 1 KB window and ring addresses wrap with one LOP3
@@ -658,11 +647,10 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	for (;;) {
 		// next run from the device-side queue; the redux makes the index provably warp-uniform for the compiler
 		int u = 0;
-		if (lane == 0) u = atomicAdd(&w.counters[xl ? CNT_QUEUE_LONG : CNT_QUEUE], 1);
+		if (lane == 0) u = atomicAdd(&w.counters[CNT_QUEUE], 1);
 		u = __reduce_max_sync(FULL, u);
-		if (u >= (xl ? n_long : n_units)) break;
+		if (u >= n_units) break;
 		const Unit un = fetch_unit(w, u, n_long);
-		if (xl && un.len < XLONG_RUN) continue;
 		const int s = un.start, e = un.start + un.len;
 		const float avgf = w.avg[un.read];
 		const double avg = (double)avgf;
@@ -770,311 +758,6 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			}
 		}
 		if (FULLV && lane == 0) { atomicAdd(w.visited, (unsigned long long)visited); atomicAdd(w.visited + 1, (unsigned long long)n_chunks); }
-	}
-}
-
-// ---- tile variant: a warp owns R runs; warp-wide scoring, lane-per-run replay ---------------------------------
-//
-// k_fill_fast pays the replay of chain.c:80-87 (IMPROVE lane, marked misses before / after it, skip budget, break,
-// winner) once per anchor as ~45 warp-uniform instructions that all 32 lanes execute.  Here a warp works on R
-// independent runs at once ("tile"), in rounds:
-//   1. SIMT: lane r owns run r.  It publishes the run's next chunk request -- anchor (x, q, span), running maximum,
-//      chunk position, marks that earlier chunks sent into this one, ring address -- as 32 bytes of shared memory.
-//      Requests are compacted: requests served from the run's 64-anchor ring (chunks 0 and 1: > 95 % of all) fill
-//      the slot array from the front, deeper ones from the back.
-//   2. SCORING PASSES, warp-wide as in k_fill_fast: lane l scores predecessor jb - l (chain.c:60-79), the marks
-//      inside the chunk and those that land in the next chunk go through two redux.or, the chunk maximum through one
-//      redux.max, and three ballots (score == maximum, score > running maximum, marked && scored) turn the per-lane
-//      outcomes into masks; one lane stores the five words as the slot's result.  Ring passes run G slots at a time
-//      as one straight-line block (loads first), so G independent dependency chains are in flight per warp.
-//   3. SIMT REPLAY for all R runs at once: lane r replays chain.c:80-87 on its run's masks (same algebra as
-//      scan_chunk_fast), decides break / window end / continue, and -- when the anchor is finished -- writes f, p, v
-//      (chain.c:89-90) to the run's ring and to global memory and moves on to the run's next anchor (or pops the
-//      next run from the queue).  This section is paid once per R anchor-chunks instead of once per chunk.
-//   4. Chunks with two or more IMPROVE lanes (1.3 %) are redone for that run alone by the general warp-wide routine.
-// Ring records hold the distance to the predecessor (i - p[i], or TILE_NOPRED) instead of p[i]: the lane that scores
-// anchor j then marks lane `lane + distance` without knowing j.  Ring slots that the run has not filled yet hold a
-// record no anchor can chain to (q = INT_MAX, so dq <= 0: chain.c:63), which replaces the j >= st test.
-// Marks that land beyond the ring chunks are published to t[] unconditionally (marks past the eventual
-// break are never consulted for this i and are invisible to every other i because they carry the tag i).
-// The next anchor of every run is fetched one step ahead with cp.async into a 2 x 16-byte landing zone per run.
-// One gap-cost table per CTA: the kernel requires one avg_qspan for the whole sub-batch (CNT_AVG_MIXED == 0; every
-// preset without HPC spans), else it stands down and k_fill_fast takes everything.  Runs >= XLONG_RUN anchors are
-// left to k_fill_fast as well (a single serial run gains nothing from a tile).
-#define TILE_NOPRED ((int)0x80000000)
-static __device__ __forceinline__ int lds_u16_ro(unsigned addr)   // read-only table: free to be scheduled anywhere
-{
-	unsigned short v;
-	asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
-	return (int)v;
-}
-static __device__ __forceinline__ void cp_async16(unsigned dst, const void *src)
-{
-	asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
-}
-static __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-// per-thread constants of the tile passes
-struct TileConst {
-	unsigned dr_lim, dq_max, tab, lane16, lanebit, lane;
-	int bw;
-	int32_t *t;
-};
-
-// G ring passes (slots k0 .. k0+G-1 of the request array) as one straight-line block.
-//   request:  S0 = {x, q, span, running maximum}   S1 = {jb, i, marks sent into this chunk, ring address of anchor jb}
-//   result:   {chunk maximum, lanes == maximum, lanes > running maximum, marked && scored lanes} {marks for the next chunk}
-template <int G>
-static __device__ __forceinline__ void tile_pass(const unsigned stp, const unsigned resp, const TileConst &c, const bool leader)
-{
-	const int IMIN = (int)0x80000000;
-	int4 S0[G], S1[G], rj[G];
-#pragma unroll
-	for (int g = 0; g < G; ++g) { S0[g] = lds128<0>(stp + g * 32); S1[g] = lds128<16>(stp + g * 32); }
-#pragma unroll
-	for (int g = 0; g < G; ++g) {   // the ring is a naturally aligned 1 KB window: slot of anchor jb - lane
-		const unsigned ta = (unsigned)S1[g].w - c.lane16;
-		rj[g] = lds128<0>((ta & 0x3f0u) | ((unsigned)S1[g].w & ~0x3f0u));
-	}
-	bool skip[G];
-	int cost[G], dq[G];
-	unsigned dr[G];
-#pragma unroll
-	for (int g = 0; g < G; ++g) {   // chain.c:60-67
-		dr[g] = (unsigned)S0[g].x - (unsigned)rj[g].x;
-		dq[g] = S0[g].y - rj[g].y;
-		const int dd = abs((int)dr[g] - dq[g]);
-		skip[g] = (dr[g] - 1u) >= c.dr_lim || ((unsigned)dq[g] - 1u) >= c.dq_max || dd > c.bw;
-		asm("" : "=r"(cost[g]));    // left undefined for skipped lanes (their score is replaced below)
-		if (!skip[g]) cost[g] = lds_u16_ro(c.tab + (unsigned)dd * 2u);
-	}
-#pragma unroll
-	for (int g = 0; g < G; ++g) {
-		const int sc = min(min(dq[g], (int)dr[g]), S0[g].z) - cost[g] + rj[g].z;   // chain.c:68-79
-		const int scx = skip[g] ? IMIN : sc;
-		// marks (chain.c:87): lane + distance is the lane that scores this anchor's predecessor
-		const unsigned kt = c.lane + (unsigned)rj[g].w;
-		const unsigned mloc = __reduce_or_sync(FULL, skip[g] ? 0u : bit_or_zero(kt));
-		const unsigned mhi = __reduce_or_sync(FULL, skip[g] ? 0u : bit_or_zero(kt - 32u));
-		if (!skip[g] && (int)kt >= 32) c.t[S1[g].x - (int)kt] = S1[g].y;
-		const int M = __reduce_max_sync(FULL, scx);
-		const unsigned eq = __ballot_sync(FULL, scx == M);
-		const unsigned gt = __ballot_sync(FULL, scx > S0[g].w);
-		const unsigned mm = __ballot_sync(FULL, !skip[g] && ((mloc | (unsigned)S1[g].z) & c.lanebit) != 0u);
-		if (leader) { sts128<0>(resp + g * 32, make_int4(M, (int)eq, (int)gt, (int)mm)); sts32<16>(resp + g * 32, (int)mhi); }
-	}
-}
-
-template <int R, int NW, int G>
-__global__ void __launch_bounds__(NW * 32) k_fill_tile(Workspace w, mm2b200_params_t prm, int tab_entries)
-{
-	extern __shared__ int4 smem4[];
-	if (prm.is_cdna || w.counters[CNT_MULTISEG] != 0 || w.counters[CNT_AVG_MIXED] != 0) return;
-
-	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	const int IMIN = (int)0x80000000;
-	// layout from a 1 KB-aligned base:
-	//   [rings NW*R KB][blank ring 1 KB][v rings NW*R*256][requests NW*R*32][results NW*R*32][landing zones NW*R*32][table]
-	const unsigned sbase = ((unsigned)__cvta_generic_to_shared(smem4) + 1023u) & ~1023u;
-	const unsigned ring_w = sbase + (unsigned)wib * (R * 1024u);
-	const unsigned blank = sbase + NW * R * 1024u;
-	const unsigned vring_w = blank + 1024u + (unsigned)wib * (R * 256u);
-	const unsigned st_w = blank + 1024u + NW * R * 256u + (unsigned)wib * (R * 32u);
-	const unsigned res_w = blank + 1024u + NW * R * 288u + (unsigned)wib * (R * 32u);
-	const unsigned land_w = blank + 1024u + NW * R * 320u + (unsigned)wib * (R * 32u);
-	const unsigned tab = blank + 1024u + NW * R * 352u;
-
-	const int n_long = w.counters[CNT_LONG_UNITS];
-	const int n_units = w.counters[CNT_UNITS] + n_long;
-	const unsigned mdx = (unsigned)prm.max_dist_x;
-	const unsigned dq_max = (unsigned)(prm.max_dist_y < prm.max_dist_x ? prm.max_dist_y : prm.max_dist_x);   // chain.c:64
-	const unsigned dr_max = prm.n_segs > 1 ? (unsigned)prm.max_dist_y : 0xffffffffu;                             // chain.c:67
-	const int bw = prm.bw, max_skip = prm.max_skip;
-	const int B0 = max_skip + 1 > 1 ? max_skip + 1 : 1;
-	const ulonglong2 *__restrict__ a = w.a;
-	int4 *wrec = w.wrec;
-	int32_t *vg = w.v, *t = w.t;
-	TileConst c;
-	c.dr_lim = dr_max < mdx ? dr_max : mdx;          // scored pairs have 1 <= dr <= dr_lim (chain.c:58,63,67)
-	c.dq_max = dq_max; c.tab = tab; c.lane16 = (unsigned)lane * 16u; c.lanebit = 1u << lane; c.lane = (unsigned)lane; c.bw = bw; c.t = t;
-	const bool leader = lane == 0;
-	const unsigned lt = lanemask_lt(lane);
-	const int4 blank_rec = make_int4(0, 0x7fffffff, 0, TILE_NOPRED);   // q = INT_MAX: dq <= 0 for every anchor (chain.c:63)
-
-	{	// the CTA's gap-cost table (chain.c:73,78 in the reference's double arithmetic), one avg_qspan per sub-batch
-		const double avg = (double)__uint_as_float((unsigned)w.counters[CNT_AVG_KEY] ^ 0x80000000u);
-		for (int dd = threadIdx.x; dd <= bw; dd += NW * 32)
-			sts_u16(tab + dd * 2, lin_cost(dd, avg) + ((31 - __clz(dd | 1)) >> 1));
-		for (int k = threadIdx.x; k < 64; k += NW * 32) sts128<0>(blank + (unsigned)k * 16u, blank_rec);
-		__syncthreads();
-	}
-
-	// ---- lane-private state of run `lane` (lanes >= R never own a run) ----
-	const unsigned my_ring = ring_w + (unsigned)lane * 1024u, my_vring = vring_w + (unsigned)lane * 256u, my_land = land_w + (unsigned)lane * 32u;
-	int i = 0, e = 0, s = 0, jb = 0;                 // current anchor, run end, run start, first predecessor of the chunk
-	int xi = 0, qi = 0, span = 0;
-	int max_f = 0, max_j = -1, vbest = IMIN, budget = B0;
-	unsigned min_marks = 0;                          // marks the previous chunk of this anchor sent into the next one
-	bool active = false, fin = true, qdone = lane >= R;
-
-	for (;;) {
-		// ---- SIMT: next anchor / next run ----
-		if (fin) {
-			fin = false;
-			++i;
-			int4 ai = make_int4(0, 0, 0, 0);
-			if (i >= e) {                                // run finished (or none yet): pop the next one
-				active = false;
-				while (!qdone) {
-					const int q = atomicAdd(&w.counters[CNT_QUEUE], 1);
-					if (q >= n_units) { qdone = true; break; }
-					const Unit un = fetch_unit(w, q, n_long);
-					if (un.len >= XLONG_RUN) continue;        // k_fill_fast's
-					s = un.start; e = s + un.len; i = s + 1;
-					const ulonglong2 a0 = a[s], a1 = a[i];
-					// blank ring, then the run's first anchor (f = span, p = -1, v = span: chain.c:56,89-90)
-					for (int k = 0; k < 64; ++k) sts128<0>(my_ring + (unsigned)k * 16u, blank_rec);
-					const int sp = (int)((a0.y >> 32) & 0xff);
-					const unsigned slot = (unsigned)(s & 63);
-					sts128<0>(my_ring + slot * 16u, make_int4((int)(unsigned)a0.x, (int)(unsigned)a0.y, sp, TILE_NOPRED));
-					sts32<0>(my_vring + slot * 4u, sp);
-					ai = make_int4((int)(unsigned)a1.x, (int)(a1.x >> 32), (int)(unsigned)a1.y, (int)(a1.y >> 32));
-					active = true;
-					break;
-				}
-			} else {
-				cp_async_wait_all();
-				ai = lds128<0>(my_land + (unsigned)(i & 1) * 16u);
-			}
-			if (active) {
-				if (i + 1 < e) cp_async16(my_land + (unsigned)((i + 1) & 1) * 16u, &a[i + 1]);
-				xi = ai.x; qi = ai.z; span = ai.w & 0xff;
-				max_f = span; max_j = -1; vbest = IMIN; budget = B0; jb = i - 1; min_marks = 0u;
-			}
-		}
-		// ---- SIMT: publish the chunk requests, compacted: ring chunks from the front, deep chunks from the back ----
-		const bool reqA = active && i - jb <= 33;
-		const unsigned actA = __ballot_sync(FULL, reqA), actB = __ballot_sync(FULL, active && !reqA);
-		if ((actA | actB) == 0u) break;
-		const int nA = __popc(actA), nB = __popc(actB);
-		const int slot = reqA ? __popc(actA & lt) : R - 1 - __popc(actB & lt);
-		if (active) {
-			const unsigned sp = st_w + (unsigned)slot * 32u;
-			sts128<0>(sp, make_int4(xi, qi, span, max_f));
-			// (a deep request shows the blank ring to a ring block that happens to cover its slot: every lane skipped)
-			sts128<16>(sp, make_int4(jb, i, reqA ? (int)min_marks : jb - s, reqA ? (int)(my_ring + (((unsigned)jb & 63u) << 4)) : (int)blank));
-		}
-		if (lane >= nA && lane < ((nA + G - 1) & ~(G - 1)) && lane < R - nB) {
-			// a slot the last ring block touches but nobody filled: q = 0 against the blank ring, every lane is skipped
-			const unsigned sp = st_w + (unsigned)lane * 32u;
-			sts128<0>(sp, make_int4(0, 0, 0, 0));
-			sts128<16>(sp, make_int4(0, 0, 0, (int)blank));
-		}
-		__syncwarp();
-
-		// ---- scoring passes ----
-		for (int k0 = 0; k0 < nA; k0 += G) tile_pass<G>(st_w + (unsigned)k0 * 32u, res_w + (unsigned)k0 * 32u, c, leader);
-		for (int k = R - 1; k >= R - nB; --k) {          // chunks beyond the ring: records and marks from global memory
-			const unsigned stp = st_w + (unsigned)k * 32u;
-			const int4 S0 = lds128<0>(stp), S1 = lds128<16>(stp);
-			const int jbr = S1.x, ir = S1.y, jrel = S1.z;
-			const int jc = max(jbr - lane, jbr - jrel);
-			const int4 rj = wrec[jc];
-			const bool mmem = t[jc] == ir;               // marks that earlier chunks of this anchor sent here
-			const unsigned dr = (unsigned)S0.x - (unsigned)rj.x;
-			const int dq = S0.y - rj.y;
-			const int dd = abs((int)dr - dq);
-			const bool skip = lane > jrel || (dr - 1u) >= c.dr_lim || ((unsigned)dq - 1u) >= dq_max || dd > bw;
-			int cost = 0;
-			if (!skip) cost = lds_u16_ro(tab + (unsigned)dd * 2u);
-			const int sc = min(min(dq, (int)dr), S0.z) - cost + rj.z;
-			const int scx = skip ? IMIN : sc;
-			const int pj = rj.w;
-			const unsigned kt = (unsigned)(jbr - pj);
-			const bool mk = !skip && pj >= 0;
-			const unsigned mloc = __reduce_or_sync(FULL, mk ? bit_or_zero(kt) : 0u);
-			if (mk && kt >= 32u) t[pj] = ir;
-			const int M = __reduce_max_sync(FULL, scx);
-			const unsigned eq = __ballot_sync(FULL, scx == M);
-			const unsigned gt = __ballot_sync(FULL, scx > S0.w);
-			const unsigned mm = __ballot_sync(FULL, !skip && ((mloc & c.lanebit) != 0u || mmem));
-			if (leader) sts128<0>(res_w + (unsigned)k * 32u, make_int4(M, (int)eq, (int)gt, (int)mm));
-		}
-		__syncwarp();
-
-		// ---- SIMT replay of chain.c:80-87 on the masks: lane r for run r ----
-		bool slow = false, done = false;
-		if (active) {
-			const unsigned rp = res_w + (unsigned)slot * 32u;
-			const int4 res = lds128<0>(rp);
-			const unsigned rhi = (unsigned)lds32<16>(rp);
-			const int cM = res.x;
-			const unsigned ceq = (unsigned)res.y, cgt = (unsigned)res.z, cmm = (unsigned)res.w;
-			const unsigned low = ceq & (0u - ceq);                // first lane that attains the chunk maximum
-			slow = (cgt & (low - 1u)) != 0u;                      // an earlier lane beats the running maximum: >= 2 IMPROVE lanes
-			const unsigned imp = cM > max_f ? low : 0u;           // the only IMPROVE lane, if any
-			const unsigned below = imp - 1u;                      // lanes visited before it (all lanes when there is none)
-			const unsigned mm = cmm & ~imp;                       // MARKED-MISS lanes
-			const unsigned seg1 = mm & below, seg2 = mm & ~(imp | below);
-			const int c1 = __popc(seg1), c2 = __popc(seg2);
-			const bool brk1 = c1 >= budget;                       // break before the IMPROVE lane (chain.c:84-85)
-			const bool take = imp != 0u && !brk1;
-			const int L = __popc(below) & 31;
-			const int b1 = budget - c1, b2 = min(b1 + 1, B0);     // chain.c:82: if (n_skip > 0) --n_skip
-			const bool brk2 = take && c2 >= b2;
-			// the scan goes on iff the chunk's last lane (anchor jb-31) is inside the window (chain.c:58; x is sorted, and
-			// with max_dist_x < 2^26 the low 32 bits of x decide it) and something is left below it
-			const int jl = jb - 31;
-			bool cont = jl > s;
-			if (cont) {
-				const int xl = reqA ? lds32<0>(my_ring + (((unsigned)jl & 63u) << 4)) : wrec[jl].x;
-				cont = ((unsigned)xi - (unsigned)xl) <= mdx;
-			}
-			if (!slow) {
-				if (take) {
-					max_f = cM; max_j = jb - L;
-					vbest = reqA ? lds32<0>(my_vring + (((unsigned)max_j & 63u) << 2)) : vg[max_j];
-				}
-				budget = take ? b2 - c2 : b1;
-				done = brk1 || brk2 || !cont;
-			}
-			if (i - jb == 1) min_marks = rhi;                     // what chunk 0 sends into chunk 1 (beyond that: t[])
-		}
-		// ---- rare: several IMPROVE lanes in a chunk; redo that run's chunk with the general warp-wide routine ----
-		for (unsigned sm = __ballot_sync(FULL, slow); sm; sm &= sm - 1u) {
-			const int r = __ffs(sm) - 1;
-			int mf = __shfl_sync(FULL, max_f, r), mj = __shfl_sync(FULL, max_j, r), vb = __shfl_sync(FULL, vbest, r), bud = __shfl_sync(FULL, budget, r);
-			const int jbr = __shfl_sync(FULL, jb, r), ir = __shfl_sync(FULL, i, r), sr = __shfl_sync(FULL, s, r);
-			const int xr = __shfl_sync(FULL, xi, r), qr = __shfl_sync(FULL, qi, r), spr = __shfl_sync(FULL, span, r);
-			const unsigned slot_r = (unsigned)__shfl_sync(FULL, slot, r);
-			const int j = jbr - lane, jc = max(j, sr);
-			const int depth = ir - jbr;
-			int4 rj; int vj; bool mmem;
-			if (depth <= 33) {
-				rj = lds128<0>((ring_w + (unsigned)r * 1024u) | (((unsigned)j & 63u) << 4));
-				rj.w = rj.w < 0 ? -1 : j - rj.w;              // distance -> index
-				vj = lds32<0>((vring_w + (unsigned)r * 256u) | (((unsigned)j & 63u) << 2));
-				mmem = (((unsigned)lds32<24>(st_w + slot_r * 32u) >> lane) & 1u) != 0u;   // the request's marks word
-			} else { rj = wrec[jc]; vj = vg[jc]; mmem = t[jc] == ir; }
-			const int dd0 = abs((int)((unsigned)xr - (unsigned)rj.x) - (qr - rj.y));
-			const int cost = lds_u16_ro(tab + min((unsigned)dd0, (unsigned)bw) * 2u);
-			long long vis = 0; bool far;
-			const int dn = scan_chunk<false>(mf, mj, vb, bud, vis, far, jbr, sr, lane, rj, vj, mmem,
-			                                 (unsigned)xr, qr, spr, mdx, dr_max, dq_max, bw, cost, B0, max_skip);
-			if (lane == r) { max_f = mf; max_j = mj; vbest = vb; budget = bud; done = dn != 0 || jb - 31 <= s; }
-		}
-		// ---- SIMT: finish the anchor (chain.c:89-90) or step to the next chunk ----
-		if (active) {
-			if (done) {
-				const int vi = max(vbest, max_f);
-				const unsigned sl = (unsigned)(i & 63);
-				sts128<0>(my_ring + sl * 16u, make_int4(xi, qi, max_f, max_j >= 0 ? i - max_j : TILE_NOPRED));
-				sts32<0>(my_vring + sl * 4u, vi);
-				wrec[i] = make_int4(xi, qi, max_f, max_j);
-				vg[i] = vi;
-				fin = true;
-			} else jb -= 32;
-		}
 	}
 }
 
@@ -1748,25 +1431,14 @@ static int cached_occupancy(OccCache &oc, K kern, int threads, int smem)
 }
 
 template <bool TABLE, bool FULLV, bool WIDE>
-static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, int tile_on, cudaStream_t s)
+static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
 	const int smem = fill_smem_bytes(tab_entries);
 	auto kern = k_fill_fast<TABLE, FULLV, WIDE>;
 	static thread_local OccCache oc;   // one cache per template instance
 	const int occ = cached_occupancy(oc, kern, FILL_WARPS * 32, smem);
 	const int per_sm = (g_fill_ctas_cap > 0 && g_fill_ctas_cap < occ) ? g_fill_ctas_cap : occ;
-	kern<<<sms * per_sm, FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries, tile_on);
-}
-
-template <int R, int NW, int G>
-static void launch_fill_tile(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg &cfg, int tab_entries, cudaStream_t s)
-{
-	const int smem = NW * R * 1376 + 1024 + tab_entries * 2 + 1024;   // rings, v rings, requests, results, landing zones; blank ring; table; alignment slack
-	auto kern = k_fill_tile<R, NW, G>;
-	static thread_local OccCache oc;
-	const int occ = cached_occupancy(oc, kern, NW * 32, smem);
-	const int per_sm = (cfg.tile_ctas_per_sm > 0 && cfg.tile_ctas_per_sm < occ) ? cfg.tile_ctas_per_sm : occ;
-	kern<<<cfg.sm_count * per_sm, NW * 32, smem, s>>>(w, prm, tab_entries);
+	kern<<<sms * per_sm, FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries);
 }
 
 void query_launch_cfg(LaunchCfg *cfg)
@@ -1780,14 +1452,6 @@ void query_launch_cfg(LaunchCfg *cfg)
 	cfg->fill_blocks_per_sm = occ;
 	const char *ec = getenv("MM2B200_FILL_CTAS");
 	g_fill_ctas_cap = ec ? atoi(ec) : 0;
-	const char *et = getenv("MM2B200_TILE");          // runs per warp of the tile kernel: 0 (off), 4, 8, 16, 32
-	cfg->tile_runs = et ? atoi(et) : 16;
-	const char *ew = getenv("MM2B200_TILE_WARPS");    // warps per tile CTA
-	cfg->tile_warps = ew ? atoi(ew) : 2;
-	const char *eg = getenv("MM2B200_TILE_GROUP");    // chunk-0 passes per straight-line block
-	cfg->tile_group = eg ? atoi(eg) : 4;
-	const char *ex = getenv("MM2B200_TILE_CTAS");
-	cfg->tile_ctas_per_sm = ex ? atoi(ex) : 0;
 }
 
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
@@ -1801,35 +1465,16 @@ int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg &cfg, bool host_generic, cudaStream_t s)
 {
 	int n = 0;
-	// Every variant that could apply is enqueued unless the host already knows the generic one is needed; the ones that
-	// do not match the device-side flags (multi-segment anchors, mixed avg_qspan) return immediately.
+	// Both variants are enqueued unless the host already knows the generic one is needed; the one that does not
+	// match the device-side segment flag returns immediately.
 	if (!host_generic) {
 		const int te = fill_tab_entries(prm);
 		const bool full = cfg.count_visited || prm.max_iter > 0;   // instrumented / max_iter-aware variant
-		const bool wide = prm.max_dist_x >= (1 << 26);             // per-lane window test not exact (33 gaps could wrap 2^32)
-		const int tile = (te && !full && !wide) ? cfg.tile_runs : 0;
-		if (wide) {                                                // general chunk routine only
-			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, 0, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, 0, s);
-		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, 0, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, tile != 0, s); }
-		else { if (full) launch_fill_fast<false, true, false>(w, prm, cfg.sm_count, 0, 0, s); else launch_fill_fast<false, false, false>(w, prm, cfg.sm_count, 0, 0, s); }
+		if (prm.max_dist_x >= (1 << 26)) {                         // per-lane window test not exact (33 gaps could wrap 2^32): general chunk routine only
+			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, s);
+		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, s); }
+		else { if (full) launch_fill_fast<false, true, false>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false, false>(w, prm, cfg.sm_count, 0, s); }
 		++n;
-		if (tile) {
-			const int key = tile * 100 + cfg.tile_warps * 10 + cfg.tile_group;   // runs per warp, warps per CTA, passes per block
-			switch (key) {
-			case 842:  launch_fill_tile<8, 4, 2>(w, prm, cfg, te, s); break;
-			case 844:  launch_fill_tile<8, 4, 4>(w, prm, cfg, te, s); break;
-			case 848:  launch_fill_tile<8, 4, 8>(w, prm, cfg, te, s); break;
-			case 1622: launch_fill_tile<16, 2, 2>(w, prm, cfg, te, s); break;
-			case 1624: launch_fill_tile<16, 2, 4>(w, prm, cfg, te, s); break;
-			case 1628: launch_fill_tile<16, 2, 8>(w, prm, cfg, te, s); break;
-			case 1644: launch_fill_tile<16, 4, 4>(w, prm, cfg, te, s); break;
-			case 1648: launch_fill_tile<16, 4, 8>(w, prm, cfg, te, s); break;
-			case 3224: launch_fill_tile<32, 2, 4>(w, prm, cfg, te, s); break;
-			case 3228: launch_fill_tile<32, 2, 8>(w, prm, cfg, te, s); break;
-			default:   launch_fill_tile<16, 2, 4>(w, prm, cfg, te, s); break;
-			}
-			++n;
-		}
 	}
 	k_fill_generic<<<cfg.sm_count * cfg.fill_blocks_per_sm, 128, 0, s>>>(w, prm); ++n;
 	return n;

@@ -221,10 +221,10 @@ def test_argument_errors(ctx):
 
 
 def test_wide_window_variant(ctx):
-    """max_dist_x >= 2^27 switches to the prefix-of-lanes window test (WIDE)."""
+    """max_dist_x >= 2^26 switches to the prefix-of-lanes window test (WIDE)."""
     rng = np.random.default_rng(21)
     reads = [random_colinear(rng, int(n), noise=0.3, step=5) for n in rng.integers(2, 800, 25)]
     offs, a = concat_reads(reads)
-    for over in (dict(max_dist_x=1 << 27, max_dist_y=1 << 27), dict(max_dist_x=(1 << 31) - 1, max_dist_y=5000, bw=700)):
+    for over in (dict(max_dist_x=1 << 26, max_dist_y=1 << 26), dict(max_dist_x=1 << 27, max_dist_y=1 << 27), dict(max_dist_x=(1 << 31) - 1, max_dist_y=5000, bw=700)):
         got, want = _both(ctx, "map-ont", offs, a, **over)
         assert_same(got, want, f"wide {over}")
