@@ -56,18 +56,26 @@ typedef struct {
  * when there is no chain.  Thread-safe: concurrent callers are combined into one device batch by the
  * library's batcher (default context on device $MM2B200_DEVICE, default 0).  kmalloc/kfree are taken from the
  * host program when it exports them (kalloc.c:120,72); otherwise km must be NULL and malloc/free are used.
- * On an internal error it returns NULL with *n_u_ = 0 and mm2b200_last_error() set (a is still consumed). */
+ * Errors (no CUDA device, out of memory, n >= 2^29, ...): the reference has no error channel and "NULL, 0" also means
+ * "no chain", so a failing drop-in symbol prints the reason to stderr and abort()s (default).  With the environment
+ * variable MM2B200_ON_ERROR=null it returns NULL with *n_u_ = 0 instead and mm2b200_last_error() is non-empty (a is
+ * still consumed).  A failing batch is retried call by call, so one bad read cannot fail its neighbours. */
 mm128_t *mm_chain_dp(int max_dist_x, int max_dist_y, int bw, int max_skip, int min_cnt, int min_sc, int is_cdna,
                      int n_segs, int64_t n, mm128_t *a, int *n_u_, uint64_t **_u, void *km);
 
-/* chain.c:218 (mmpriv.h:69): the fork's device half.  free()s a; returns a malloc()ed new_seed[*_new_i]. */
+/* chain.c:218 (mmpriv.h:69): the fork's device half.  free()s a; returns a malloc()ed new_seed[*_new_i].
+ * Thread-safe and batched like mm_chain_dp (the fork's live call sites are map.c:525,941). */
 struct new_seed *mm_chain_dp_fpga(int max_dist_x, int max_dist_y, int bw, int max_skip, int min_sc, int is_cdna,
                                   int n_segs, int64_t n, mm128_t *a, uint32_t *_new_i);
 
 /* chain.c:329 (mmpriv.h:70): the fork's host half (here also on the device).  Does not free fpga_a.
- * Returns malloc()ed b and *_u (the reference ignores km here, chain.c:341-358,400). */
+ * Returns malloc()ed b and *_u (the reference ignores km here, chain.c:341-358,400).  Thread-safe and batched like
+ * mm_chain_dp (the fork's live call site is map.c:837). */
 mm128_t *mm_chain_dp_bottom(int min_cnt, int min_sc, int n_segs, int *n_u_, uint64_t **_u, void *km,
                             struct new_seed *fpga_a, uint32_t new_i);
+
+/* how many device batches the three entry points above were combined into, and how many calls they served */
+int mm2b200_entry_stats(int64_t *n_batches, int64_t *n_calls);
 
 /* ---- Section 2: context ------------------------------------------------------------------------------------ */
 
@@ -160,7 +168,9 @@ typedef struct {
 
 /* Whole path on anchors already resident in HBM: d_a[n_anchors] and d_offs[n_reads+1] are device pointers.
  * Everything is enqueued on `stream` (a cudaStream_t passed as void*; NULL = the legacy default stream) and the
- * call returns without waiting. */
+ * call returns without waiting.  The device result pointers stay valid until the next call on the context; the library
+ * records an event behind the work, and a later call on another stream (or one that has to grow the workspace) waits
+ * for it before it touches the slot. */
 int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
                          const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_result_t *out);
 

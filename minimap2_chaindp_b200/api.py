@@ -29,7 +29,7 @@ OK, ERR_CUDA, ERR_ARG, ERR_NOMEM, ERR_STATE = 0, -1, -2, -3, -4
 
 # every symbol include/mm2chain_b200.h declares (tests check the library exports all of them)
 EXPORTED_SYMBOLS = (
-    "mm_chain_dp", "mm_chain_dp_fpga", "mm_chain_dp_bottom",
+    "mm_chain_dp", "mm_chain_dp_fpga", "mm_chain_dp_bottom", "mm2b200_entry_stats",
     "mm2b200_create", "mm2b200_destroy", "mm2b200_last_error", "mm2b200_device_count",
     "mm2b200_pinned_alloc", "mm2b200_pinned_free",
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
@@ -101,8 +101,12 @@ def lib() -> C.CDLL:
             raise FileNotFoundError(
                 f"{LIB_PATH} is missing: build it with `python -m minimap2_chaindp_b200.build` "
                 "(nvcc, sm_100a).  There is no CPU fallback for the chaining path.")
+        # a failing drop-in symbol aborts the process by default (the reference has no error channel); under Python the
+        # wrappers below raise ChainError from mm2b200_last_error() instead
+        os.environ.setdefault("MM2B200_ON_ERROR", "null")
         L = C.CDLL(LIB_PATH)
         vp, i64, i32 = C.c_void_p, C.c_int64, C.c_int32
+        L.mm2b200_entry_stats.argtypes = [C.POINTER(i64), C.POINTER(i64)]
         L.mm2b200_create.argtypes = [C.POINTER(_Config), C.POINTER(vp)]
         L.mm2b200_destroy.argtypes = [vp]
         L.mm2b200_destroy.restype = None
@@ -406,6 +410,13 @@ def _malloc_copy(arr: np.ndarray) -> int:
     if arr.nbytes:
         C.memmove(p, arr.ctypes.data, arr.nbytes)
     return p
+
+
+def entry_stats():
+    """(device batches, calls) served so far by the combining dispatcher behind the three drop-in symbols."""
+    nb, nc = C.c_int64(0), C.c_int64(0)
+    lib().mm2b200_entry_stats(C.byref(nb), C.byref(nc))
+    return int(nb.value), int(nc.value)
 
 
 def mm_chain_dp(prm: Params, a):

@@ -4,6 +4,7 @@
 // There is deliberately no CPU implementation of any stage in this file: if CUDA is unavailable every compute
 // entry point fails with MM2B200_ERR_CUDA.
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
@@ -196,6 +197,11 @@ static bool wire_encode(const mm128_t *src, int64_t n, int64_t b0, int64_t b1, u
 struct Slot {
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev_totals = nullptr, ev_done = nullptr;
+	// mm2b200_chain_device enqueues on the CALLER's stream and returns: the workspace (and the device result pointers
+	// handed out) stay in use until ev_user fires.  Anything that reuses or frees the slot from another stream waits for it.
+	cudaEvent_t ev_user = nullptr;
+	cudaStream_t user_stream = nullptr;
+	bool user_pending = false;
 	Workspace w{};
 	void *d_block = nullptr;          // one allocation carved into the workspace arrays
 	void *d_rec_out = nullptr;        // lazily allocated (fill_batch only)
@@ -238,6 +244,7 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 	if (R < 64) R = 64;
 	if (A >= ((size_t)1 << 31) - 64) return fail(MM2B200_ERR_ARG, "sub-batch of %zu anchors exceeds the 2^31 index space", A);
 	CUDA_TRY(cudaStreamSynchronize(s.stream));
+	if (s.user_pending) { CUDA_TRY(cudaEventSynchronize(s.ev_user)); s.user_pending = false; }
 	if (s.d_block) { cudaFree(s.d_block); s.d_block = nullptr; }
 	struct Item { void **pp; size_t bytes; };
 	Workspace &w = s.w;
@@ -334,11 +341,20 @@ static int check_params(const mm2b200_params_t *p)
 	return MM2B200_OK;
 }
 
+// what the kernels get: max_skip beyond 2^30 behaves like 2^30 (a read has fewer than 2^29 anchors, so the budget can
+// never run out) and keeps max_skip + 1 inside int32
+static mm2b200_params_t kernel_params(const mm2b200_params_t &p)
+{
+	mm2b200_params_t q = p;
+	if (q.max_skip > (1 << 30)) q.max_skip = 1 << 30;
+	return q;
+}
+
 // prep + fill + compaction (the mm_chain_dp_fpga half, chain.c:218-327)
 static int enqueue_fill(mm2b200_ctx *ctx, const Workspace &w, const mm2b200_params_t &prm, cudaStream_t st)
 {
 	{ StageTimer t(ctx, st, ST_PREP); t.done(launch_prep(w, prm, st)); }
-	{ StageTimer t(ctx, st, ST_FILL); t.done(launch_fill(w, prm, ctx->lc, prm.is_cdna != 0, st)); }
+	{ StageTimer t(ctx, st, ST_FILL); t.done(launch_fill(w, kernel_params(prm), ctx->lc, prm.is_cdna != 0, st)); }
 	return MM2B200_OK;
 }
 static int enqueue_compact(mm2b200_ctx *ctx, const Workspace &w, const mm2b200_params_t &prm, cudaStream_t st)
@@ -381,7 +397,8 @@ static int add_slot(mm2b200_ctx *ctx)
 	Slot &s = ctx->slots.back();
 	if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaEventCreateWithFlags(&s.ev_totals, cudaEventDisableTiming) != cudaSuccess ||
-	    cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming) != cudaSuccess)
+	    cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&s.ev_user, cudaEventDisableTiming) != cudaSuccess)
 		return fail(MM2B200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
 	return MM2B200_OK;
 }
@@ -434,6 +451,7 @@ extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 		s.h_a.release(); s.h_offs.release(); s.h_totals.release();
 		if (s.ev_totals) cudaEventDestroy(s.ev_totals);
 		if (s.ev_done) cudaEventDestroy(s.ev_done);
+		if (s.ev_user) cudaEventDestroy(s.ev_user);
 		if (s.stream) cudaStreamDestroy(s.stream);
 	}
 	drain_spans(ctx);
@@ -642,6 +660,8 @@ static int run_batch(BatchJob &job)
 	CUDA_TRY(cudaSetDevice(ctx->device));
 	const int64_t R = job.n_reads;
 	ctx->h2d_bytes = 0; ctx->wire_sub_batches = 0;
+	for (auto &s : ctx->slots)      // work that mm2b200_chain_device left running on a caller's stream still owns its slot
+		if (s.user_pending) { CUDA_TRY(cudaEventSynchronize(s.ev_user)); s.user_pending = false; }
 	// reserve the pinned result arenas to their upper bounds up front (sum n_v <= N, n_u <= n / max(min_cnt,1),
 	// new_i <= n): a buffer must never move while an earlier chunk's D2H copy is still landing in it
 	const int64_t N = R > 0 ? job.offs[R] - job.offs[0] : 0;
@@ -856,15 +876,19 @@ extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	CUDA_TRY(cudaSetDevice(ctx->device));
 	Slot &s = ctx->slots[0];
 	if (s.state) return fail(MM2B200_ERR_STATE, "slot 0 busy");
+	cudaStream_t st = (cudaStream_t)stream;
+	// back-to-back calls on one stream are ordered by the stream itself; a different stream must wait for the previous call
+	if (s.user_pending && s.user_stream != st) { CUDA_TRY(cudaEventSynchronize(s.ev_user)); s.user_pending = false; }
 	if ((rc = ensure_slot(ctx, s, (size_t)n_anchors, (size_t)n_reads))) return rc;
 	Workspace w = s.w;              // private copy pointing at the caller's inputs
 	w.a = (const ulonglong2*)d_a; w.offs = d_offs;
 	w.n_reads = (int32_t)n_reads; w.n_anchors = (int32_t)n_anchors;
-	cudaStream_t st = (cudaStream_t)stream;
 	enqueue_fill(ctx, w, *prm, st);
 	enqueue_compact(ctx, w, *prm, st);
 	enqueue_bottom(ctx, w, *prm, st);
 	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaEventRecord(s.ev_user, st));
+	s.user_stream = st; s.user_pending = true;
 	out->d_n_u = w.n_u; out->d_u_off = w.u_off; out->d_b_off = w.b_off;
 	out->d_u = w.u_out; out->d_b = (const mm128_t*)w.b_out; out->d_totals = w.totals;
 	return MM2B200_OK;
@@ -900,21 +924,32 @@ extern "C" int mm2b200_int_peak(mm2b200_ctx_t *ctx, int mode, double *lane_ops_p
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Section 1: reference entry points.  Concurrent mm_chain_dp callers (kt_for workers, map.c:598-604) are
-// combined by a dispatcher thread into one device batch per parameter set: while the GPU works on one batch the
-// next callers queue up, so the batch size adapts to the number of host threads without any timer.
+// Section 1: reference entry points.  Concurrent callers of mm_chain_dp (kt_for workers, map.c:598-604), of
+// mm_chain_dp_fpga (map.c:525,941) and of mm_chain_dp_bottom (map.c:837) are combined by one dispatcher thread into
+// device batches, one per (entry point, parameter set): while the GPU works on one batch the next callers queue up,
+// so the batch size adapts to the number of host threads without any timer.  The dispatcher owns a private context:
+// nothing else ever touches its result arenas, and every caller's slice is copied out before the next batch starts.
+//
+// Errors.  The reference reports none and "NULL, n_u = 0" is also the legitimate "no chain" answer, so a
+// failure must not look like an unmapped read: it is printed to stderr, and unless MM2B200_ON_ERROR=null the process
+// aborts (default; wrong PAF is never produced silently).  With MM2B200_ON_ERROR=null the call returns NULL / 0 and
+// mm2b200_last_error() tells the two apart.  A batch that fails is retried one call at a time, so one bad read (or a
+// transient allocation failure on a big batch) cannot fail its neighbours.
 // ---------------------------------------------------------------------------------------------------------
 namespace {
 
+enum EntryMode { ENTRY_CHAIN = 0, ENTRY_FPGA = 1, ENTRY_BOTTOM = 2 };
+
 struct Pending {
+	int mode = ENTRY_CHAIN;
 	mm2b200_params_t prm;
-	int64_t n;
-	const mm128_t *a;
-	bool own_malloc;          // results may be handed over as plain malloc()ed arrays (km == NULL)
+	int64_t n = 0;
+	const void *in = nullptr;     // mm128_t[n] (ENTRY_CHAIN, ENTRY_FPGA) or new_seed[n] (ENTRY_BOTTOM)
 	// filled by the dispatcher: malloc()ed copies of this call's slice of the batch result, so the dispatcher never has
 	// to wait for the callers before it starts the next batch
 	int rc = 0; std::string err;
 	int32_t n_u = 0; uint64_t *u = nullptr; mm128_t *b = nullptr; int64_t n_b = 0;
+	struct new_seed *rec = nullptr; int64_t n_rec = 0;
 	bool done = false;
 	std::condition_variable cv;   // one per call: only the owner is woken
 };
@@ -923,90 +958,178 @@ struct Batcher {
 	std::mutex mu;
 	std::condition_variable cv_work;
 	std::deque<Pending*> q;
-	mm2b200_ctx *ctx = nullptr;        // the default context (also used by mm_chain_dp_fpga / _bottom)
+	// Two dispatchers, each with a private context: while one batch is on the device the other dispatcher assembles and
+	// launches the next (the fork's worker threads sit in mm_chain_dp_fpga while its result threads sit in mm_chain_dp_bottom).
+	static const int N_DISPATCH = 2;
+	mm2b200_ctx *ctx[N_DISPATCH] = {nullptr, nullptr};
+	std::thread th[N_DISPATCH];
 	int init_rc = 0; std::string init_err;
-	bool started = false;
+	bool started = false, stop = false;
+	std::atomic<int64_t> n_batches{0}, n_calls{0};
 };
 
 Batcher *g_batcher = nullptr;
 std::once_flag g_batcher_once;
-std::mutex g_default_mu;
-mm2b200_ctx *g_default_ctx = nullptr;
-std::string g_default_err;
 
-mm2b200_ctx *default_ctx()
+bool abort_on_error()
 {
-	std::lock_guard<std::mutex> lk(g_default_mu);
-	if (!g_default_ctx && g_default_err.empty()) {
-		mm2b200_config_t cfg{};
-		const char *dev = getenv("MM2B200_DEVICE");
-		cfg.device = dev ? atoi(dev) : 0;
-		cfg.n_slots = 2;
-		cfg.slot_anchors = (int64_t)4 << 20;
-		if (mm2b200_create(&cfg, &g_default_ctx) != MM2B200_OK) g_default_err = g_err.empty() ? "mm2b200_create failed" : g_err;
-	}
-	if (!g_default_ctx) g_err = g_default_err;
-	return g_default_ctx;
+	static const bool v = [] { const char *e = getenv("MM2B200_ON_ERROR"); return !(e && !strcmp(e, "null")); }();
+	return v;
 }
 
-void dispatcher_main(Batcher *B, mm2b200_ctx *ctx)
+// a drop-in symbol failed: never silently (see the section comment)
+void entry_failed(const char *sym, const std::string &msg)
 {
+	g_err = msg;
+	fprintf(stderr, "[mm2chain-b200] %s failed: %s%s\n", sym, msg.c_str(),
+	        abort_on_error() ? " -- aborting (MM2B200_ON_ERROR=null returns NULL and keeps mm2b200_last_error() instead)" : "");
+	if (abort_on_error()) abort();
+}
+
+// one device batch over calls[0..m): all share mode and parameters.  Returns the batch's rc; on success every call has
+// its private result copy.
+int run_entry_batch(mm2b200_ctx *ctx, PinnedBuf &stage, std::vector<int64_t> &offs, Pending *const *calls, size_t m)
+{
+	const int mode = calls[0]->mode;
+	const size_t elem = mode == ENTRY_BOTTOM ? sizeof(struct new_seed) : sizeof(mm128_t);
+	int64_t total = 0;
+	offs.assign(1, 0);
+	for (size_t k = 0; k < m; ++k) { total += calls[k]->n; offs.push_back(total); }
+	int rc = stage.reserve((size_t)(total > 0 ? total : 1) * elem);
+	if (rc) return rc;
+	char *dst = stage.as<char>();
+	for (size_t k = 0; k < m; ++k)
+		if (calls[k]->n > 0) memcpy(dst + (size_t)offs[k] * elem, calls[k]->in, (size_t)calls[k]->n * elem);
+	if (mode == ENTRY_FPGA) {
+		mm2b200_records_t out{};
+		if ((rc = mm2b200_fill_batch(ctx, &calls[0]->prm, (int64_t)m, offs.data(), (const mm128_t*)dst, &out, nullptr, nullptr, nullptr))) return rc;
+		for (size_t k = 0; k < m; ++k) {
+			Pending *p = calls[k];
+			p->n_rec = out.rec_off[k + 1] - out.rec_off[k];
+			p->rec = (struct new_seed*)malloc((size_t)(p->n_rec > 0 ? p->n_rec : 1) * sizeof(struct new_seed));   // chain.c:233: libc malloc
+			if (!p->rec) return fail(MM2B200_ERR_NOMEM, "malloc of %lld records failed", (long long)p->n_rec);
+			if (p->n_rec > 0) memcpy(p->rec, out.rec + out.rec_off[k], (size_t)p->n_rec * sizeof(struct new_seed));
+		}
+		return MM2B200_OK;
+	}
+	mm2b200_result_t res{};
+	if (mode == ENTRY_BOTTOM) rc = mm2b200_bottom_batch(ctx, &calls[0]->prm, (int64_t)m, offs.data(), (const struct new_seed*)dst, &res);
+	else rc = mm2b200_chain_batch(ctx, &calls[0]->prm, (int64_t)m, offs.data(), (const mm128_t*)dst, &res);
+	if (rc) return rc;
+	for (size_t k = 0; k < m; ++k) {
+		Pending *p = calls[k];
+		if (res.n_u[k] <= 0) continue;
+		p->n_u = res.n_u[k];
+		p->n_b = res.b_off[k + 1] - res.b_off[k];
+		p->u = (uint64_t*)malloc((size_t)p->n_u * 8);
+		p->b = (mm128_t*)malloc((size_t)(p->n_b > 0 ? p->n_b : 1) * sizeof(mm128_t));
+		if (!p->u || !p->b) return fail(MM2B200_ERR_NOMEM, "malloc of a chain result (%d chains, %lld anchors) failed", p->n_u, (long long)p->n_b);
+		memcpy(p->u, res.u + res.u_off[k], (size_t)p->n_u * 8);
+		memcpy(p->b, res.b + res.b_off[k], (size_t)p->n_b * sizeof(mm128_t));
+	}
+	return MM2B200_OK;
+}
+
+void drop_results(Pending *p)
+{
+	free(p->u); free(p->b); free(p->rec);
+	p->u = nullptr; p->b = nullptr; p->rec = nullptr; p->n_u = 0; p->n_b = 0; p->n_rec = 0;
+}
+
+void dispatcher_main(Batcher *B, int which)
+{
+	mm2b200_ctx *ctx = B->ctx[which];
 	std::vector<int64_t> offs;
 	PinnedBuf stage;
+	size_t recent = 0;                  // calls in this dispatcher's previous batch
 	for (;;) {
 		std::vector<Pending*> batch;
 		{
 			std::unique_lock<std::mutex> lk(B->mu);
-			B->cv_work.wait(lk, [&] { return !B->q.empty(); });
-			// take every queued call that shares the first one's parameters
-			const mm2b200_params_t key = B->q.front()->prm;
+			B->cv_work.wait(lk, [&] { return B->stop || !B->q.empty(); });
+			if (B->q.empty()) break;     // stop requested and nothing left to serve
+			// The callers of the previous batch are on their way back (they were woken a few microseconds ago): when only a
+			// fraction of them has queued again, wait briefly instead of spending a device round trip on a handful of reads.
+			if (B->q.size() * 2 < recent)
+				B->cv_work.wait_for(lk, std::chrono::microseconds(150), [&] { return B->stop || B->q.size() * 2 >= recent; });
+			if (B->q.empty()) continue;  // the other dispatcher took them
+			// the entry point with the most queued calls; of those, every call that shares the first one's parameters
+			size_t cnt[3] = {0, 0, 0};
+			for (auto *p : B->q) ++cnt[p->mode];
+			const int mode = cnt[1] > cnt[0] ? (cnt[2] > cnt[1] ? 2 : 1) : (cnt[2] > cnt[0] ? 2 : 0);
+			const Pending *key = nullptr;
 			for (auto it = B->q.begin(); it != B->q.end();) {
-				if (!memcmp(&(*it)->prm, &key, sizeof(key))) { batch.push_back(*it); it = B->q.erase(it); }
-				else ++it;
+				if ((*it)->mode == mode && (!key || !memcmp(&(*it)->prm, &key->prm, sizeof(key->prm)))) {
+					if (!key) key = *it;
+					batch.push_back(*it); it = B->q.erase(it);
+				} else ++it;
 			}
+			if (!B->q.empty()) B->cv_work.notify_one();   // something else is left for the other dispatcher
 		}
-		int64_t total = 0;
-		offs.assign(1, 0);
-		for (auto *p : batch) { total += p->n; offs.push_back(total); }
-		int rc = stage.reserve((size_t)(total > 0 ? total : 1) * sizeof(mm128_t));
-		mm2b200_result_t res{};
-		if (!rc) {
-			mm128_t *dst = stage.as<mm128_t>();
-			for (size_t k = 0; k < batch.size(); ++k)
-				if (batch[k]->n > 0) memcpy(dst + offs[k], batch[k]->a, (size_t)batch[k]->n * sizeof(mm128_t));
-			rc = mm2b200_chain_batch(ctx, &batch[0]->prm, (int64_t)batch.size(), offs.data(), dst, &res);
-		}
-		// hand every caller a private copy of its slice (outside the lock), then wake exactly that caller
-		for (size_t k = 0; k < batch.size(); ++k) {
-			Pending *p = batch[k];
-			p->rc = rc;
-			if (rc) p->err = g_err;
-			else if (res.n_u[k] > 0) {
-				p->n_u = res.n_u[k];
-				p->n_b = res.b_off[k + 1] - res.b_off[k];
-				p->u = (uint64_t*)malloc((size_t)p->n_u * 8);
-				p->b = (mm128_t*)malloc((size_t)(p->n_b > 0 ? p->n_b : 1) * sizeof(mm128_t));
-				memcpy(p->u, res.u + res.u_off[k], (size_t)p->n_u * 8);
-				memcpy(p->b, res.b + res.b_off[k], (size_t)p->n_b * sizeof(mm128_t));
+		recent = batch.size();
+		++B->n_batches; B->n_calls += (int64_t)batch.size();
+		int rc = run_entry_batch(ctx, stage, offs, batch.data(), batch.size());
+		if (rc && batch.size() > 1) {
+			// retry one call at a time: a single bad read must not fail the reads that happened to share its batch
+			for (auto *p : batch) {
+				drop_results(p);
+				p->rc = run_entry_batch(ctx, stage, offs, &p, 1);
+				if (p->rc) { p->err = g_err; drop_results(p); }
 			}
-		}
+		} else for (auto *p : batch) { p->rc = rc; if (rc) { p->err = g_err; drop_results(p); } }
 		{
 			std::lock_guard<std::mutex> lk(B->mu);
 			for (auto *p : batch) { p->done = true; p->cv.notify_one(); }
 		}
 	}
+	stage.release();
 }
 
 Batcher *batcher()
 {
 	std::call_once(g_batcher_once, [] {
 		Batcher *B = new Batcher();
-		B->ctx = default_ctx();
-		if (!B->ctx) { B->init_rc = MM2B200_ERR_CUDA; B->init_err = g_err; }
-		else { std::thread(dispatcher_main, B, B->ctx).detach(); B->started = true; }
+		mm2b200_config_t cfg{};
+		const char *dev = getenv("MM2B200_DEVICE");
+		cfg.device = dev ? atoi(dev) : 0;
+		cfg.n_slots = 2;
+		cfg.slot_anchors = (int64_t)4 << 20;
+		for (int k = 0; k < Batcher::N_DISPATCH && !B->init_rc; ++k)
+			if (mm2b200_create(&cfg, &B->ctx[k]) != MM2B200_OK) { B->init_rc = MM2B200_ERR_CUDA; B->init_err = g_err.empty() ? "mm2b200_create failed" : g_err; }
+		if (!B->init_rc) {
+			for (int k = 0; k < Batcher::N_DISPATCH; ++k) B->th[k] = std::thread(dispatcher_main, B, k);
+			B->started = true;
+		}
 		g_batcher = B;
 	});
 	return g_batcher;
+}
+
+// library unload / process exit: let the dispatcher finish what is queued, then join it.  (The context itself is left to
+// the CUDA runtime's own teardown: calling into CUDA from a destructor at exit is not safe.)
+__attribute__((destructor)) void mm2b200_on_unload()
+{
+	Batcher *B = g_batcher;
+	if (!B || !B->started) return;
+	{ std::lock_guard<std::mutex> lk(B->mu); B->stop = true; }
+	B->cv_work.notify_all();
+	for (auto &t : B->th) if (t.joinable()) t.join();
+	B->started = false;
+}
+
+// submit one call and wait for it; returns false (after reporting) when the call failed
+bool submit_entry(const char *sym, Pending &pd)
+{
+	Batcher *B = batcher();
+	if (!B->started) { entry_failed(sym, B->init_err.empty() ? "the dispatcher is not running" : B->init_err); return false; }
+	{
+		std::unique_lock<std::mutex> lk(B->mu);
+		B->q.push_back(&pd);
+		B->cv_work.notify_one();
+		pd.cv.wait(lk, [&] { return pd.done; });
+	}
+	if (pd.rc != MM2B200_OK) { entry_failed(sym, pd.err); return false; }
+	return true;
 }
 
 void *host_alloc(void *km, size_t bytes)
@@ -1022,31 +1145,32 @@ void host_free(void *km, void *p)
 
 } // namespace
 
+extern "C" int mm2b200_entry_stats(int64_t *n_batches, int64_t *n_calls)
+{
+	Batcher *B = g_batcher;
+	if (n_batches) *n_batches = B ? B->n_batches.load() : 0;
+	if (n_calls) *n_calls = B ? B->n_calls.load() : 0;
+	return MM2B200_OK;
+}
+
 extern "C" mm128_t *mm_chain_dp(int max_dist_x, int max_dist_y, int bw, int max_skip, int min_cnt, int min_sc, int is_cdna,
                                 int n_segs, int64_t n, mm128_t *a, int *n_u_, uint64_t **_u, void *km)
 {
 	if (_u) *_u = 0;
 	if (n_u_) *n_u_ = 0;
 	g_err.clear();
-	if (km && !kmalloc) { fail(MM2B200_ERR_ARG, "km != NULL but the host program exports no kmalloc/kfree"); return nullptr; }
+	if (km && !kmalloc) { entry_failed("mm_chain_dp", "km != NULL but the host program exports no kmalloc/kfree"); return nullptr; }
 	mm128_t *ret = nullptr;
-	Batcher *B = batcher();
-	if (!B->started) { g_err = B->init_err; host_free(km, a); return nullptr; }
 	if (n > 0) {
 		Pending pd;
+		pd.mode = ENTRY_CHAIN;
 		pd.prm = mm2b200_params_t{max_dist_x, max_dist_y, bw, max_skip, min_cnt, min_sc, is_cdna, n_segs, 0};
-		pd.n = n; pd.a = a;
-		pd.own_malloc = (km == nullptr);     // kmalloc(NULL, n) is malloc(n) (kalloc.c:127), so malloc()ed results are compatible
-		{
-			std::unique_lock<std::mutex> lk(B->mu);
-			B->q.push_back(&pd);
-			B->cv_work.notify_one();
-			pd.cv.wait(lk, [&] { return pd.done; });
-		}
-		if (pd.rc == MM2B200_OK && pd.n_u > 0) {
+		pd.n = n; pd.in = a;
+		if (submit_entry("mm_chain_dp", pd) && pd.n_u > 0) {
 			uint64_t *u = pd.u;
 			ret = pd.b;
-			if (!pd.own_malloc) {            // results must live in the caller's kalloc arena: copy on the caller's thread
+			if (km) {            // results must live in the caller's kalloc arena: copy on the caller's thread
+				// (km == NULL: kmalloc(NULL, n) is malloc(n) (kalloc.c:127), so the malloc()ed copies are handed over as they are)
 				u = (uint64_t*)host_alloc(km, (size_t)pd.n_u * 8);
 				ret = (mm128_t*)host_alloc(km, (size_t)pd.n_b * sizeof(mm128_t));
 				memcpy(u, pd.u, (size_t)pd.n_u * 8);
@@ -1055,7 +1179,7 @@ extern "C" mm128_t *mm_chain_dp(int max_dist_x, int max_dist_y, int bw, int max_
 			}
 			if (_u) *_u = u; else host_free(km, u);
 			if (n_u_) *n_u_ = pd.n_u;
-		} else if (pd.rc != MM2B200_OK) g_err = pd.err;
+		}
 	}
 	host_free(km, a);   // chain.c:137,214: the input array is consumed
 	return ret;
@@ -1066,21 +1190,17 @@ extern "C" struct new_seed *mm_chain_dp_fpga(int max_dist_x, int max_dist_y, int
 {
 	if (_new_i) *_new_i = 0;
 	g_err.clear();
-	mm2b200_ctx *ctx = default_ctx();
 	struct new_seed *ret = nullptr;
-	if (ctx && n > 0) {
-		static std::mutex mu;   // the returned arena slice must be copied before the next call reuses it
-		std::lock_guard<std::mutex> lk(mu);
-		mm2b200_params_t prm{max_dist_x, max_dist_y, bw, max_skip, 0, min_sc, is_cdna, n_segs, 0};
-		const int64_t offs[2] = {0, n};
-		mm2b200_records_t out{};
-		if (mm2b200_fill_batch(ctx, &prm, 1, offs, a, &out, nullptr, nullptr, nullptr) == MM2B200_OK) {
-			const int64_t m = out.rec_off[1] - out.rec_off[0];
-			ret = (struct new_seed*)malloc((size_t)(m > 0 ? m : 1) * sizeof(struct new_seed));   // chain.c:233: libc malloc, n entries
-			if (m > 0) memcpy(ret, out.rec + out.rec_off[0], (size_t)m * sizeof(struct new_seed));
-			if (_new_i) *_new_i = (uint32_t)m;
+	if (n > 0) {
+		Pending pd;
+		pd.mode = ENTRY_FPGA;
+		pd.prm = mm2b200_params_t{max_dist_x, max_dist_y, bw, max_skip, 0, min_sc, is_cdna, n_segs, 0};
+		pd.n = n; pd.in = a;
+		if (submit_entry("mm_chain_dp_fpga", pd)) {
+			ret = pd.rec;
+			if (_new_i) *_new_i = (uint32_t)pd.n_rec;
 		}
-	} else if (n <= 0) ret = (struct new_seed*)malloc(sizeof(struct new_seed));
+	} else ret = (struct new_seed*)malloc(sizeof(struct new_seed));   // chain.c:233 with n == 0
 	free(a);   // chain.c:322
 	return ret;
 }
@@ -1088,25 +1208,17 @@ extern "C" struct new_seed *mm_chain_dp_fpga(int max_dist_x, int max_dist_y, int
 extern "C" mm128_t *mm_chain_dp_bottom(int min_cnt, int min_sc, int n_segs, int *n_u_, uint64_t **_u, void *km,
                                        struct new_seed *fpga_a, uint32_t new_i)
 {
-	(void)km; (void)n_segs;
+	(void)km;   // the reference ignores km here as well (chain.c:341-358,400: malloc / free)
 	if (_u) *_u = 0;
 	if (n_u_) *n_u_ = 0;
 	g_err.clear();
-	mm2b200_ctx *ctx = default_ctx();
-	if (!ctx || new_i == 0) return nullptr;
-	static std::mutex mu;
-	std::lock_guard<std::mutex> lk(mu);
-	mm2b200_params_t prm{0, 0, 0, 0, min_cnt, min_sc, 0, n_segs, 0};
-	const int64_t offs[2] = {0, (int64_t)new_i};
-	mm2b200_result_t res{};
-	if (mm2b200_bottom_batch(ctx, &prm, 1, offs, fpga_a, &res) != MM2B200_OK || res.n_u[0] == 0) return nullptr;
-	const int32_t nu = res.n_u[0];
-	const int64_t nb = res.b_off[1] - res.b_off[0];
-	uint64_t *u = (uint64_t*)malloc((size_t)nu * 8);
-	mm128_t *b = (mm128_t*)malloc((size_t)nb * sizeof(mm128_t));
-	memcpy(u, res.u + res.u_off[0], (size_t)nu * 8);
-	memcpy(b, res.b + res.b_off[0], (size_t)nb * sizeof(mm128_t));
-	if (_u) *_u = u; else free(u);
-	if (n_u_) *n_u_ = nu;
-	return b;
+	if (new_i == 0) return nullptr;
+	Pending pd;
+	pd.mode = ENTRY_BOTTOM;
+	pd.prm = mm2b200_params_t{0, 0, 0, 0, min_cnt, min_sc, 0, n_segs, 0};
+	pd.n = (int64_t)new_i; pd.in = fpga_a;
+	if (!submit_entry("mm_chain_dp_bottom", pd) || pd.n_u <= 0) return nullptr;
+	if (_u) *_u = pd.u; else free(pd.u);
+	if (n_u_) *n_u_ = pd.n_u;
+	return pd.b;
 }

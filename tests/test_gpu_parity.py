@@ -200,6 +200,109 @@ def test_concurrent_callers_are_batched(ctx):
         assert np.array_equal(out[r][0], wu) and np.array_equal(out[r][1], wb), f"read {r}"
 
 
+def test_concurrent_split_entry_points_are_batched(ctx):
+    """The fork's LIVE call sites (map.c:525,941 mm_chain_dp_fpga; map.c:837 mm_chain_dp_bottom) from 128 host threads:
+    every caller gets its own read's records / chains, and the dispatcher combined the calls into fewer device batches."""
+    import threading
+    spec = workload.CONFIGS["map-ont-100k"]
+    n = 128
+    offs, a = workload.generate(spec, 9000, n)
+    prm, oprm = api.params(spec.preset), oracle.params(spec.preset)
+    out = [None] * n
+    b0, c0 = api.entry_stats()
+
+    def work(r):
+        rec = api.mm_chain_dp_fpga(prm, a[offs[r]:offs[r + 1]])
+        out[r] = (rec, api.mm_chain_dp_bottom(prm, rec))
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(n)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    b1, c1 = api.entry_stats()
+    assert c1 - c0 == 2 * n
+    assert b1 - b0 < 2 * n, "no two calls were ever combined"
+    for r in range(n):
+        ar = a[offs[r]:offs[r + 1]]
+        o = oracle.fill(oprm, ar)
+        orec, _ = oracle.compact(oprm.min_sc, ar, o.f, o.p, o.v)
+        wu, wb = oracle.chain_dp(oprm, ar)
+        assert np.array_equal(out[r][0], orec), f"records of read {r}"
+        assert np.array_equal(out[r][1][0], wu) and np.array_equal(out[r][1][1], wb), f"chains of read {r}"
+
+
+def test_mixed_entry_points_hammer(ctx):
+    """mm_chain_dp from "worker" threads while mm_chain_dp_bottom runs from "result" threads (the layout of map.c:837/858
+    with the rechain block enabled) and a third group uses other parameters: the dispatcher serialises the batches on its
+    private context and nobody reads another call's arena."""
+    import threading
+    spec = workload.CONFIGS["map-ont-100k"]
+    n = 48
+    offs, a = workload.generate(spec, 12000, n)
+    prm, oprm = api.params(spec.preset), oracle.params(spec.preset)
+    prm2, oprm2 = api.params(spec.preset, min_cnt=1, min_sc=0), oracle.params(spec.preset, min_cnt=1, min_sc=0)
+    recs = []
+    for r in range(n):
+        ar = a[offs[r]:offs[r + 1]]
+        o = oracle.fill(oprm, ar)
+        recs.append(oracle.compact(oprm.min_sc, ar, o.f, o.p, o.v)[0])
+    want = [oracle.chain_dp(oprm, a[offs[r]:offs[r + 1]]) for r in range(n)]
+    want2 = [oracle.chain_dp(oprm2, a[offs[r]:offs[r + 1]]) for r in range(n)]
+    bad = []
+
+    def chain(r):
+        for _ in range(3):
+            u, b = api.mm_chain_dp(prm, a[offs[r]:offs[r + 1]])
+            if not (np.array_equal(u, want[r][0]) and np.array_equal(b, want[r][1])):
+                bad.append(("mm_chain_dp", r))
+
+    def bottom(r):
+        for _ in range(3):
+            u, b = api.mm_chain_dp_bottom(prm, recs[r])
+            if not (np.array_equal(u, want[r][0]) and np.array_equal(b, want[r][1])):
+                bad.append(("mm_chain_dp_bottom", r))
+
+    def chain2(r):
+        u, b = api.mm_chain_dp(prm2, a[offs[r]:offs[r + 1]])
+        if not (np.array_equal(u, want2[r][0]) and np.array_equal(b, want2[r][1])):
+            bad.append(("mm_chain_dp other params", r))
+
+    th = [threading.Thread(target=f, args=(r,)) for r in range(n) for f in (chain, bottom, chain2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not bad, bad[:5]
+
+
+def test_max_skip_int_max(ctx):
+    """max_skip = INT_MAX never breaks (chain.c:84); the budget arithmetic must not overflow."""
+    rng = np.random.default_rng(5)
+    reads = [random_colinear(rng, int(n), noise=0.3, step=5) for n in rng.integers(2, 400, 12)]
+    offs, a = concat_reads(reads)
+    got, want = _both(ctx, "map-ont", offs, a, max_skip=(1 << 31) - 1)
+    assert_same(got, want, "max_skip INT_MAX")
+
+
+def test_chain_device_then_other_stream(ctx):
+    """mm2b200_chain_device returns before its work is done; a following batch call (other stream, may regrow the slot)
+    must wait for it instead of freeing the workspace under the running kernels."""
+    import torch
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 300, 3000)
+    prm, oprm = api.params(spec.preset), oracle.params(spec.preset)
+    dev = torch.device("cuda", 0)
+    d_a = torch.from_numpy(a.view(np.int64)).to(dev)
+    d_offs = torch.from_numpy(offs).to(dev)
+    side = torch.cuda.Stream()
+    with api.ChainContext(device=0, n_slots=1, slot_anchors=1 << 16) as c2:
+        for _ in range(3):
+            out = c2.chain_device(prm, 3000, int(offs[-1]), d_offs.data_ptr(), d_a.data_ptr(), side.cuda_stream)
+            got = c2.chain_batch(prm, offs[:201], a[:offs[200]])      # different stream, smaller sub-batches
+            want = oracle.chain_batch(oprm, offs[:201], a[:offs[200]])
+            assert_same(got, want, "batch after chain_device")
+        side.synchronize()
+        got = c2.chain_batch(prm, offs, a)
+        assert_same(got, oracle.chain_batch(oprm, offs, a), "full batch after chain_device")
+
+
 def test_argument_errors(ctx):
     """Bad arguments come back as error codes (never abort, never compute)."""
     a = np.zeros((10, 2), np.uint64)

@@ -10,7 +10,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from minimap2_chaindp_b200 import api, workload  # noqa: E402
 
 spec = workload.CONFIGS["map-ont-100k"]
-offs, a = workload.generate(spec, 0, 4096)
+offs, a = workload.generate(spec, 0, 16384 if "--dump" in sys.argv else 4096)
 prm = api.params(spec.preset)
 if "--dump" in sys.argv:                           # input file for the C harness (tools/dropin_rate.c)
     import numpy as np
