@@ -5,15 +5,22 @@
     python bench.py --impl reference --steps K --warmup W    # the reference's CPU mm_chain_dp on the host cores
 
 A step = one pass of the hot path (mm_chain_dp over every read of the workload: prep, fill, compaction,
-backtrack, gather) over one batch of synthetic reads.  Workload at N=1: BASELINE.json configs[1]
-("map-ont: 100k synthetic 10 kb Nanopore-like reads").  For N>1 every rank owns its own 100k reads (weak scaling,
-read-batch sharding, no collective on the data path).
+backtrack, gather) over one batch of synthetic reads.
+
+Headline (the line's top-level keys): BASELINE.json configs[1] "map-ont: 100k synthetic 10 kb Nanopore-like reads".
+For N>1 every rank owns its own 100k reads (weak scaling, read-batch sharding, no collective on the data path).
 
 * value : visited anchor pairs / s, whole job, anchors already resident in HBM, CUDA events, max over ranks
 * e2e   : the same through the C ABI call a reference-side batcher makes (mm2b200_chain_batch) with pinned HOST
-          buffers: H2D of the anchors, all kernels, D2H of the chains inside the timed region
-* roofline / roofline_issue : the fill kernel against HBM and against the measured integer-issue peak
-* cpu_baseline : the reference's own chain.c (oracle/_ref) under its kt_for on all host cores, bounded sample
+          buffers: H2D of the anchors, all kernels, D2H of the chains inside the timed region; plus the pageable-memory
+          variant, the PCIe ceiling of the same byte volume, rank 0 alone (for an e2e scaling efficiency) and -- at
+          N>1 -- `e2e_multi`: ONE host process driving all N GPUs through mm2b200_chain_batch_multi
+* roofline : the fill kernel against the measured integer-issue peak (the binding roofline); roofline_hbm: the
+          same kernel against the measured copy bandwidth (secondary: the kernel is not HBM bound)
+* cpu_baseline : the reference's own chain.c (oracle/_ref) under its kt_for on all host cores, SAME 100k reads
+* configs : the other BASELINE.json configs (ava-ont-50k, map-pb-ul-20k, asm5-50mb), each a FIXED workload split over
+          the N ranks (strong scaling), with value, e2e, fill roofline, stage times and parity against the compiled
+          reference on every read of a sample
 
 "visited pair" = one execution of the reference's inner loop body (chain.c:59-88); the count comes from the
 device (mm2b200_result_t.n_visited) and is cross-checked against the oracle on the CPU-baseline sample.
@@ -21,12 +28,12 @@ device (mm2b200_result_t.n_visited) and is cross-checked against the oracle on t
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import json
 import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 import numpy as np
@@ -41,7 +48,13 @@ METRIC = "chain_dp_anchor_pair_evals_per_sec"
 UNIT = "pairs/s"
 INT_OPS_PER_PAIR = 28          # integer ops the algorithm needs per visited pair
 BYTES_PER_ANCHOR = 40          # 16 B anchor in + 16 B anchor out + 8 B f,p
-CPU_SAMPLE_READS = 40_000      # bounded sample for the CPU arm (~10-30 s of CPU work on the map-ont workload)
+
+# the other BASELINE.json configs: reads per chunk (bounds pinned + device memory) and reads in the parity sample
+CONFIG_BLOCK = {
+    "ava-ont-50k": dict(chunk_reads=8000, parity_reads=2000),
+    "map-pb-ul-20k": dict(chunk_reads=2000, parity_reads=2000),
+    "asm5-50mb": dict(chunk_reads=8, parity_reads=8),
+}
 
 
 def host_cores() -> int:
@@ -49,6 +62,13 @@ def host_cores() -> int:
         return len(os.sched_getaffinity(0))
     except Exception:
         return os.cpu_count() or 1
+
+
+def numa_nodes() -> int:
+    try:
+        return len([d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()])
+    except Exception:
+        return 1
 
 
 def peaks():
@@ -61,7 +81,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed regions run."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed regions run."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -106,23 +126,39 @@ class ClockSampler:
         except Exception:
             pass
         if sm:
-            # median over the samples taken under load (clock above idle)
-            busy = [x for x in sm if x > 0.5 * max(sm)] or sm
+            busy = [x for x in sm if x > 0.5 * max(sm)] or sm     # samples taken under load (clock above idle)
             out.update(sm_mhz=float(np.median(busy)), sm_max_mhz=float(max(smax)), reasons=sorted(reasons), samples=len(sm))
         return out
 
 
-def cpu_reference_run(spec, offs, a, threads, want_outputs=False):
-    """The reference's mm_chain_dp over the sample under its kt_for (oracle/_ref), else the oracle port."""
+# ---------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own mm_chain_dp under its kt_for (oracle/_ref), else the oracle port
+# ---------------------------------------------------------------------------------------------------------
+def cpu_reference_timed(spec, offs, a, threads, passes=3, warmup=1, want_outputs=False):
+    """Best of `passes` after `warmup` untimed passes, for both of the reference's memory modes:
+    "malloc" (km = NULL, the authors' --no-kalloc run, run.sh:3; inputs copied per call OUTSIDE the timed region, as
+    BASELINE.md section 3 states) and "kalloc" (one km_init() arena per thread; the copy into the arena is inside the
+    timed region because the arena belongs to whichever worker steals the read).  Returns the faster one."""
     import oracle
     prm = oracle.params(spec.preset)
-    if oracle.have_ref():
-        res = oracle.ref_chain_batch(prm, offs, a, n_threads=threads, use_kalloc=True, keep=want_outputs)
-        return res, "reference", threads
-    t0 = time.perf_counter()
-    res = oracle.chain_batch(prm, offs, a)
-    res.seconds = time.perf_counter() - t0
-    return res, "port", 1
+    if not oracle.have_ref():
+        t0 = time.perf_counter()
+        res = oracle.chain_batch(prm, offs, a)
+        res.seconds = time.perf_counter() - t0
+        return res, dict(kind="port", cores=1, mode="oracle restatement, 1 thread", seconds=res.seconds, all={})
+    best, best_mode, allm, keep = None, None, {}, None
+    for mode, use_kalloc in (("malloc", False), ("kalloc", True)):
+        secs = []
+        for k in range(warmup + passes):
+            res = oracle.ref_chain_batch(prm, offs, a, n_threads=threads, use_kalloc=use_kalloc,
+                                         keep=want_outputs and k == warmup + passes - 1)
+            if k >= warmup:
+                secs.append(res.seconds)
+        allm[mode] = min(secs)
+        if best is None or min(secs) < best:
+            best, best_mode, keep = min(secs), mode, res
+    keep.seconds = best
+    return keep, dict(kind="reference", cores=threads, mode=best_mode, seconds=best, all=allm)
 
 
 def count_pairs_cpu(spec, offs, a, threads):
@@ -145,41 +181,493 @@ def count_pairs_cpu(spec, offs, a, threads):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores, on the SAME reads as
+    the b200 arm's headline (rank 0's 100k map-ont reads).  Loads only the workload generator and the oracle."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    from minimap2_chaindp_b200 import workload
-    import __graft_entry__ as ge
-    ge.build()
+    from minimap2_chaindp_b200 import build as pkg_build, workload
+    import oracle
+    pkg_build.build_workload()
+    oracle.build()
     spec = workload.CONFIGS[args.workload]
-    n_sample = min(args.cpu_reads, spec.n_reads)
-    offs, a = workload.generate(spec, 0, n_sample)
+    n_reads = args.reads or spec.n_reads
+    offs, a = workload.generate(spec, 0, n_reads)
     threads = host_cores()
     pairs = count_pairs_cpu(spec, offs, a, threads)
-    kind = "reference"
-    for _ in range(args.warmup):
-        _, kind, used = cpu_reference_run(spec, offs, a, threads)
-    secs = []
-    for _ in range(args.steps):
-        res, kind, used = cpu_reference_run(spec, offs, a, threads)
-        secs.append(res.seconds)
-    total = float(sum(secs))
-    value = pairs * args.steps / total
+    _, info = cpu_reference_timed(spec, offs, a, threads, passes=max(args.steps, 1), warmup=max(args.warmup, 1))
+    secs = info["seconds"]
+    value = pairs / secs
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * secs, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": f"{spec.name}: G-anc synthetic anchors, preset {spec.preset}", "reads_per_step": int(n_sample),
-                   "anchors_per_step": int(offs[-1]), "note": "CPU arm: bounded sample of the same read stream"},
-        "reads_per_s": n_sample * args.steps / total,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": kind,
-                         "sample": f"first {n_sample} reads of {spec.name} ({int(offs[-1])} anchors, {pairs} visited pairs) per step; "
-                                   f"reference mm_chain_dp under its kt_for, one kalloc arena per thread"},
+        "config": {"workload": f"{spec.name}: G-anc synthetic anchors, preset {spec.preset}", "reads_per_step": int(n_reads),
+                   "anchors_per_step": int(offs[-1]), "visited_pairs_per_step": int(pairs),
+                   "note": "CPU arm: the same reads as the b200 arm's rank 0; a rate, so comparable at every N"},
+        "reads_per_s": n_reads / secs,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
+                         "sample": f"all {n_reads} reads of {spec.name} ({int(offs[-1])} anchors, {pairs} visited pairs) per step; "
+                                   f"reference mm_chain_dp under its kt_for; best step of {max(args.steps, 1)} after {max(args.warmup, 1)} warm-up; "
+                                   f"memory mode '{info['mode']}' (faster of malloc/pre-copied inputs and kalloc arenas: "
+                                   + ", ".join(f"{k} {v * 1e3:.0f} ms" for k, v in info["all"].items()) + ")"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
     return 0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# b200 arm
+# ---------------------------------------------------------------------------------------------------------
+def result_arrays(res, n_reads):
+    """numpy views of a mm2b200_result_t (context-owned pinned memory; valid until the next call on the context)."""
+    u_off = np.frombuffer((C.c_char * (8 * (n_reads + 1))).from_address(res.u_off), dtype=np.int64)
+    b_off = np.frombuffer((C.c_char * (8 * (n_reads + 1))).from_address(res.b_off), dtype=np.int64)
+    gu = np.frombuffer((C.c_char * (8 * int(u_off[-1]))).from_address(res.u), dtype=np.uint64) if u_off[-1] else np.zeros(0, np.uint64)
+    gb = (np.frombuffer((C.c_char * (16 * int(b_off[-1]))).from_address(res.b), dtype=np.uint64).reshape(-1, 2)
+          if b_off[-1] else np.zeros((0, 2), np.uint64))
+    return u_off, b_off, gu, gb
+
+
+def parity_against_reference(spec, offs, a, res, n_sample, threads):
+    """Every read of the first n_sample reads: GPU chains (u, b, offsets) == compiled reference under kt_for."""
+    so = offs[:n_sample + 1].copy()
+    sa = a[:int(so[-1])]
+    ref, info = cpu_reference_timed(spec, so, sa, threads, passes=1, warmup=0, want_outputs=True)
+    u_off, b_off, gu, gb = result_arrays(res, offs.shape[0] - 1)
+    nu, nb = int(u_off[n_sample]), int(b_off[n_sample])
+    ok = bool(np.array_equal(u_off[:n_sample + 1], ref.u_off) and np.array_equal(b_off[:n_sample + 1], ref.b_off)
+              and np.array_equal(gu[:nu], ref.u) and np.array_equal(gb[:nb], ref.b))
+    return ok, ref, info, so, sa
+
+
+class Bench:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        from minimap2_chaindp_b200 import api, workload
+        self.torch, self.dist, self.api, self.workload = torch, dist, api, workload
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the chaining path has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.cpu_group = None
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("NCCL_DEBUG", "WARN")     # the driver's own setting wins (it reads NCCL's rank lines)
+            dist.init_process_group("nccl", device_id=self.dev)
+            # a CPU-side group: ranks that only WAIT (while rank 0 drives their GPUs in the single-process legs) must not
+            # sit in an NCCL kernel on the GPU they are lending
+            self.cpu_group = dist.new_group(backend="gloo")
+            dist.barrier()
+        self.stream = torch.cuda.current_stream()
+
+    # -- collectives (NCCL carries nothing but these scalars and the barrier) --
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def cpu_barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier(group=self.cpu_group)
+
+    def _reduce(self, x, op):
+        if self.world == 1:
+            return float(x)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def rmax(self, x):
+        return self._reduce(x, self.dist.ReduceOp.MAX if self.world > 1 else None)
+
+    def rsum(self, x):
+        return self._reduce(x, self.dist.ReduceOp.SUM if self.world > 1 else None)
+
+    # -- one chunk of reads, resident in pinned memory --------------------------------------------------------
+    def measure_chunk(self, ctx, cctx, prm, offs, pin, steps, warmup, e2e_steps):
+        """Device-resident passes (CUDA events) and end-to-end passes (host clock) over one chunk.  Returns a dict of
+        totals over the timed steps plus the last e2e result struct."""
+        torch, api = self.torch, self.api
+        n_reads, n_anchors = offs.shape[0] - 1, int(offs[-1])
+        d_a = torch.from_numpy(pin.array[:n_anchors].view(np.int64)).to(self.dev)
+        d_offs = torch.from_numpy(offs).to(self.dev)
+        torch.cuda.synchronize()
+        st = self.stream.cuda_stream
+        for _ in range(max(warmup, 1)):
+            ctx.chain_device(prm, n_reads, n_anchors, d_offs.data_ptr(), d_a.data_ptr(), st)
+        torch.cuda.synchronize()
+        res = None
+        for _ in range(max(min(warmup, 1), 1)):
+            res = ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
+        # metric numerator: reference-visited pairs, counted once by the instrumented kernel variant (untimed)
+        cres = cctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
+        out = dict(reads=n_reads, anchors=n_anchors, pairs=int(cres.n_visited), lanes=int(cres.n_lanes),
+                   units=int(res.n_units), sub_batches=int(res.n_sub_batches))
+        ctx.stage_reset()
+        l0 = ctx.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ev0.record(self.stream)
+        for _ in range(steps):
+            ctx.chain_device(prm, n_reads, n_anchors, d_offs.data_ptr(), d_a.data_ptr(), st)
+        ev1.record(self.stream)
+        torch.cuda.synchronize()
+        out["dev_ms"] = float(ev0.elapsed_time(ev1))
+        out["launches"] = ctx.launch_count() - l0
+        out["stage"] = {s: ctx.stage_ms(s)[0] for s in ("prep", "fill", "compact", "tail", "gather")}
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            res = ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
+        torch.cuda.synchronize()
+        out["e2e_s"] = time.perf_counter() - t0
+        h2d, wire_sub = ctx.upload_stats()
+        u_tot = int(np.frombuffer((C.c_char * 8).from_address(res.u_off + 8 * n_reads), dtype=np.int64)[0])
+        b_tot = int(np.frombuffer((C.c_char * 8).from_address(res.b_off + 8 * n_reads), dtype=np.int64)[0])
+        out.update(h2d=int(h2d), wire_sub=int(wire_sub), chains=u_tot, chain_anchors=b_tot,
+                   d2h=n_reads * (4 + 8 + 8) + u_tot * 8 + b_tot * 16 + int(res.n_sub_batches) * 64, res=res)
+        del d_a, d_offs
+        return out
+
+    # -- a fixed workload split over the ranks (strong scaling), processed in chunks ----------------------------
+    def run_config(self, name, steps, int_peak):
+        api, workload = self.api, self.workload
+        spec = workload.CONFIGS[name]
+        cb = CONFIG_BLOCK[name]
+        prm = api.params(spec.preset)
+        total_reads = spec.n_reads
+        lo = total_reads * self.rank // self.world
+        hi = total_reads * (self.rank + 1) // self.world
+        acc = dict(reads=0, anchors=0, pairs=0, lanes=0, dev_ms=0.0, e2e_s=0.0, launches=0, h2d=0, d2h=0, chunks=0,
+                   stage={s: 0.0 for s in ("prep", "fill", "compact", "tail", "gather")})
+        parity = cpu = None
+        ctx = api.ChainContext(device=self.local, profile=True)
+        cctx = api.ChainContext(device=self.local, count_visited=True)
+        try:
+            first = lo
+            while first < hi:
+                n = min(cb["chunk_reads"], hi - first)
+                offs = workload.count(spec, first, n)
+                pin = api.PinnedArray((max(int(offs[-1]), 1), 2), np.uint64)
+                workload.fill(spec, offs, pin.array, first)
+                m = self.measure_chunk(ctx, cctx, prm, offs, pin, steps, 1, 1)
+                for k in ("reads", "anchors", "pairs", "lanes", "launches", "h2d", "d2h"):
+                    acc[k] += m[k]
+                acc["dev_ms"] += m["dev_ms"] / steps
+                acc["e2e_s"] += m["e2e_s"]
+                for s in acc["stage"]:
+                    acc["stage"][s] += m["stage"][s] / steps
+                acc["chunks"] += 1
+                if parity is None and self.rank == 0:
+                    # every read of the sample against the compiled reference under kt_for (same pinned anchors)
+                    ns = min(cb["parity_reads"], n)
+                    ok, ref, info, so, sa = parity_against_reference(spec, offs, pin.array, m["res"], ns, host_cores())
+                    s_pairs = count_pairs_cpu(spec, so, sa, host_cores())
+                    parity = {"ok": ok, "reads": int(ns), "anchors": int(so[-1])}
+                    cpu = {"value": s_pairs / ref.seconds, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
+                           "reads_per_s": ns / ref.seconds, "sample": f"first {ns} reads ({int(so[-1])} anchors), 1 pass, mode {info['mode']}"}
+                pin.free()
+                first += n
+        finally:
+            ctx.close()
+            cctx.close()
+        # whole-job figures: every rank's share of the fixed workload, time = max over ranks
+        dev_ms = self.rmax(acc["dev_ms"])
+        e2e_s = self.rmax(acc["e2e_s"])
+        pairs, reads, anchors = self.rsum(acc["pairs"]), self.rsum(acc["reads"]), self.rsum(acc["anchors"])
+        fill_ms = acc["stage"]["fill"]
+        frac = (acc["pairs"] * INT_OPS_PER_PAIR / (fill_ms * 1e-3) / int_peak) if fill_ms > 0 and int_peak else None
+        if self.rank != 0:
+            return None
+        return {
+            "workload": f"{spec.name}: G-anc synthetic anchors, preset {spec.preset}; the FIXED {total_reads} reads split over {self.world} rank(s)",
+            "scaling": "strong", "reads": int(reads), "anchors": int(anchors), "visited_pairs": int(pairs),
+            "value": pairs / (dev_ms * 1e-3), "unit": UNIT, "ms_per_pass": dev_ms, "reads_per_s": reads / (dev_ms * 1e-3),
+            "e2e": {"value": pairs / e2e_s, "unit": UNIT, "ms_per_pass": 1e3 * e2e_s, "reads_per_s": reads / e2e_s,
+                    "h2d_bytes_rank0": acc["h2d"], "d2h_bytes_rank0": acc["d2h"]},
+            "roofline": {"kernel": "k_fill", "bound": "int-issue", "frac": frac, "fill_ms_rank0": fill_ms,
+                         "lane_efficiency": acc["pairs"] / acc["lanes"] if acc["lanes"] else None},
+            "stage_ms_rank0": acc["stage"], "chunks_rank0": acc["chunks"], "steps_per_chunk": steps,
+            "parity_with_reference": parity, "cpu_baseline": cpu,
+        }
+
+    # -- PCIe ceiling of the headline's byte volume: plain copies, every rank at once -----------------------------
+    def pcie_ceiling_ms(self, pin, n_anchors, d2h_bytes, reps=3):
+        torch = self.torch
+        d_in = torch.empty(n_anchors * 2, dtype=torch.int64, device=self.dev)
+        d_out = torch.empty(max(d2h_bytes // 8, 1), dtype=torch.int64, device=self.dev)
+        h_in = torch.from_numpy(pin.array[:n_anchors].view(np.int64).reshape(-1))
+        h_out = torch.empty(max(d2h_bytes // 8, 1), dtype=torch.int64).pin_memory()
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        best = None
+        for _ in range(reps + 1):
+            self.barrier()
+            t0 = time.perf_counter()
+            with torch.cuda.stream(s_up):
+                d_in.copy_(h_in, non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                h_out.copy_(d_out, non_blocking=True)
+            torch.cuda.synchronize()
+            dt = self.rmax(time.perf_counter() - t0)
+            best = dt if best is None or dt < best else best
+        return 1e3 * best
+
+    # -- the headline ------------------------------------------------------------------------------------------
+    def run(self):
+        args, api, workload, torch = self.args, self.api, self.workload, self.torch
+        rank, world, local = self.rank, self.world, self.local
+        spec = workload.CONFIGS[args.workload]
+        n_reads = args.reads or spec.n_reads
+        first = rank * n_reads
+        offs = workload.count(spec, first, n_reads)
+        n_anchors = int(offs[-1])
+        pin = api.PinnedArray((n_anchors, 2), np.uint64)       # generated straight into pinned memory
+        workload.fill(spec, offs, pin.array, first)
+        prm = api.params(spec.preset)
+        ctx = api.ChainContext(device=local, n_slots=args.slots, slot_anchors=args.slot_anchors, profile=True)
+        cctx = api.ChainContext(device=local, count_visited=True)
+        if args.wire:
+            ctx.set_upload(True, args.wire_threads)
+        steps, warm = args.steps, max(args.warmup, 1)
+
+        d_a = torch.from_numpy(pin.array.view(np.int64)).to(self.dev)
+        d_offs = torch.from_numpy(offs).to(self.dev)
+        torch.cuda.synchronize()
+        st = self.stream.cuda_stream
+
+        def device_step():
+            return ctx.chain_device(prm, n_reads, n_anchors, d_offs.data_ptr(), d_a.data_ptr(), st)
+
+        def e2e_step():
+            return ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
+
+        # warm-up (allocates workspaces and pinned result arenas outside the timed regions)
+        for _ in range(warm):
+            device_step()
+        torch.cuda.synchronize()
+        for _ in range(warm):
+            res = e2e_step()
+        cres = cctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
+        pairs_step, lanes_step = int(cres.n_visited), int(cres.n_lanes)
+        cctx.close()
+        chains_step = int(np.frombuffer((C.c_char * 8).from_address(res.u_off + 8 * n_reads), dtype=np.int64)[0])
+        canch_step = int(np.frombuffer((C.c_char * 8).from_address(res.b_off + 8 * n_reads), dtype=np.int64)[0])
+        n_units, n_sub = int(res.n_units), int(res.n_sub_batches)
+        d2h = n_reads * (4 + 8 + 8) + chains_step * 8 + canch_step * 16 + n_sub * 64
+
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+
+        # ---- timed region 1: device-resident inputs, CUDA events on the launching stream
+        ctx.stage_reset()
+        launches0 = ctx.launch_count()
+        self.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(self.stream)
+        for _ in range(steps):
+            device_step()
+        ev1.record(self.stream)
+        self.barrier()
+        dev_ms = self.rmax(ev0.elapsed_time(ev1))
+        launches = ctx.launch_count() - launches0
+        stage = {s: ctx.stage_ms(s) for s in ("prep", "fill", "compact", "tail", "gather")}
+
+        # ---- timed region 2: end to end through the C ABI with pinned host buffers (H2D + kernels + D2H inside), all ranks at once
+        self.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            res = e2e_step()
+        torch.cuda.synchronize()
+        e2e_s = self.rmax(time.perf_counter() - t0)
+        self.barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        h2d, wire_sub = ctx.upload_stats()      # bytes the last e2e step copied host -> device (counted by the library)
+
+        # ---- e2e side legs (untimed for the headline): rank 0 alone, pageable input, the PCIe ceiling
+        solo_s = page_s = None
+        self.cpu_barrier()
+        if rank == 0:
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                e2e_step()
+            torch.cuda.synchronize()
+            solo_s = (time.perf_counter() - t0) / steps
+            pageable = np.array(pin.array, copy=True)          # ordinary (pageable) host memory, what kalloc hands a caller
+            ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pageable.ctypes.data)
+            t0 = time.perf_counter()
+            res = ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pageable.ctypes.data)
+            torch.cuda.synchronize()
+            page_s = time.perf_counter() - t0
+            del pageable
+            res = e2e_step()
+        self.cpu_barrier()
+        pcie_ms = self.pcie_ceiling_ms(pin, n_anchors, d2h)
+
+        total_pairs = self.rsum(float(pairs_step))
+        total_reads = self.rsum(float(n_reads))
+        total_anchors = self.rsum(float(n_anchors))
+        value = total_pairs * steps / (dev_ms * 1e-3)
+        e2e_value = total_pairs * steps / e2e_s
+
+        # ---- rooflines of the dominant kernel (k_fill): per-launch averages from the events around it
+        fill_ms, _ = stage["fill"]
+        fill_ms_per_step = fill_ms / max(steps, 1)
+        hbm_peak, peak_src = peaks()
+        hbm_achieved = n_anchors * BYTES_PER_ANCHOR / (fill_ms_per_step * 1e-3) / 1e9 if fill_ms_per_step > 0 else 0.0
+        int_peak_mix = ctx.int_peak(1)
+        int_peak_alu = ctx.int_peak(0)
+        int_achieved = pairs_step * INT_OPS_PER_PAIR / (fill_ms_per_step * 1e-3) if fill_ms_per_step > 0 else 0.0
+        traffic, traffic_src = None, "not captured for this workload size"
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02_fill_traffic.json")))
+            if tj.get("workload") == spec.name and int(tj.get("reads", 0)) == n_reads:
+                traffic, traffic_src = int(tj["dram_bytes_per_launch"]), tj.get("source", "profiles/r02_fill_traffic.json")
+        except Exception:
+            pass
+
+        # ---- e2e_multi (N>1): ONE host process (rank 0) drives all N GPUs through mm2b200_chain_batch_multi
+        e2e_multi = None
+        if world > 1:
+            e2e_multi = self.run_multi(spec, prm, n_reads, steps, solo_s)
+
+        line = None
+        if rank == 0:
+            solo_value = pairs_step / solo_s
+            line = {
+                "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
+                "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int32", "data": "synthetic",
+                "config": {"workload": f"{spec.name}: G-anc synthetic anchors, preset {spec.preset} "
+                                       f"(max_dist {prm.max_dist_x}, bw {prm.bw}, max_skip {prm.max_skip}, max_iter unbounded = reference)",
+                           "reads_per_gpu": n_reads, "anchors_per_gpu": n_anchors, "visited_pairs_per_gpu": pairs_step,
+                           "runs_per_gpu": n_units, "sharding": f"reads x{world} (one process per GPU, no collective)",
+                           "l2": f"inputs larger than L2 ({n_anchors * 16 / 2**20:.0f} MiB of anchors + workspace vs 126 MB)",
+                           "sub_batches_e2e": n_sub,
+                           "host": {"cores": host_cores(), "numa_nodes": numa_nodes(),
+                                    "affinity": "no-op: single NUMA node" if numa_nodes() <= 1 else "not pinned"}},
+                "reads_per_s": total_reads * steps / (dev_ms * 1e-3),
+                "anchors_per_s": total_anchors * steps / (dev_ms * 1e-3),
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                        "reads_per_s": total_reads * steps / e2e_s, "ms_per_step": 1e3 * e2e_s / steps,
+                        "api": "mm2b200_chain_batch (pinned host anchors in, pinned host chains out), one process per GPU",
+                        "upload": (f"host batcher wire format ({wire_sub}/{n_sub} sub-batches, {h2d / max(n_anchors, 1):.2f} B/anchor, "
+                                   f"encoded by host threads inside the timed region)") if wire_sub else "raw mm128_t (16 B/anchor)",
+                        "pcie_ceiling_ms": pcie_ms,
+                        "pcie_ceiling_note": "plain H2D of the anchors + D2H of the result bytes on two streams, all ranks at once, max over ranks",
+                        "rank0_alone_ms_per_step": 1e3 * solo_s,
+                        "scaling_efficiency": e2e_value / (world * solo_value),
+                        "pageable_ms_per_step": 1e3 * page_s,
+                        "pageable_note": "anchors in ordinary host memory: the library stages every sub-batch through its own pinned buffer"},
+                "gpu_launches": int(launches),
+                "clocks": clocks,
+                "roofline": {"kernel": "k_fill", "bound": "int-issue", "achieved": int_achieved / 1e12, "peak": int_peak_mix / 1e12,
+                             "unit": "T lane-op/s", "frac": int_achieved / int_peak_mix if int_peak_mix else None,
+                             "traffic": traffic, "traffic_source": traffic_src,
+                             "peak_alu_pipe_only": int_peak_alu / 1e12, "ops_per_pair": INT_OPS_PER_PAIR,
+                             "lane_efficiency": pairs_step / lanes_step if lanes_step else None, "ms_per_launch": fill_ms_per_step,
+                             "peak_source": "measured live (mm2b200_int_peak: add/xor/mad.lo streams on all SMs)",
+                             "note": "the binding roofline of this path: 28 integer ops per reference-visited pair (SURVEY 8d) against the issue port"},
+                "roofline_hbm": {"kernel": "k_fill", "bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": hbm_achieved / hbm_peak, "peak_source": peak_src,
+                                 "algorithmic_bytes_per_launch": n_anchors * BYTES_PER_ANCHOR,
+                                 "note": "secondary: 40 B/anchor algorithmic; the kernel is not HBM bound"},
+                "stage_ms_per_step": {k: v[0] / max(steps, 1) for k, v in stage.items()},
+            }
+            if e2e_multi is not None:
+                line["e2e_multi"] = e2e_multi
+        # ---- CPU baseline beside it (rank 0, N=1 only): the reference on the SAME reads, and parity on every read
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            threads = host_cores()
+            ok, ref, info, so, sa = parity_against_reference(spec, offs, pin.array, res, n_reads, threads)
+            ref_t, info_t = cpu_reference_timed(spec, so, sa, threads, passes=3, warmup=1)
+            s_pairs = count_pairs_cpu(spec, so, sa, threads)
+            line["cpu_baseline"] = {"value": s_pairs / info_t["seconds"], "unit": UNIT, "cores": info_t["cores"], "kind": info_t["kind"],
+                                    "reads_per_s": n_reads / info_t["seconds"],
+                                    "sample": f"all {n_reads} reads of {spec.name} ({int(so[-1])} anchors, {s_pairs} visited pairs), "
+                                              f"reference mm_chain_dp under its kt_for, best of 3 after 1 warm-up, memory mode "
+                                              f"'{info_t['mode']}' ({', '.join(f'{k} {v * 1e3:.0f} ms' for k, v in info_t['all'].items())})",
+                                    "parity_with_gpu_on_sample": ok, "pairs_match_device_count": bool(s_pairs == pairs_step)}
+            if not ok:
+                line["parity_error"] = "GPU chains differ from the reference on the CPU-baseline sample"
+        ctx.close()
+        del d_a, d_offs
+        pin.free()
+        torch.cuda.empty_cache()
+
+        # ---- the other BASELINE.json configs, each a fixed workload split over the ranks
+        if args.configs != "none" and args.workload == "map-ont-100k":
+            names = list(CONFIG_BLOCK) if args.configs == "all" else [n for n in args.configs.split(",") if n in CONFIG_BLOCK]
+            block = {}
+            for name in names:
+                self.barrier()
+                t0 = time.perf_counter()
+                c = self.run_config(name, args.config_steps, int_peak_mix)
+                if rank == 0:
+                    c["wall_s_incl_generation"] = time.perf_counter() - t0
+                    block[name] = c
+            if rank == 0:
+                line["configs"] = block
+                bad = [k for k, v in block.items() if v["parity_with_reference"] and not v["parity_with_reference"]["ok"]]
+                if bad:
+                    line["parity_error"] = f"GPU chains differ from the reference on {bad}"
+        if rank == 0:
+            print(json.dumps(line))
+        if world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+        return 0
+
+    def run_multi(self, spec, prm, n_reads, steps, solo_s):
+        """Rank 0 alone owns N contexts (one per GPU) and N x n_reads reads in pinned memory and calls
+        mm2b200_chain_batch_multi -- the call INTEGRATION.md level 2 puts behind map.c's submit side.  The other ranks
+        wait on a CPU barrier (their GPUs are being driven by rank 0)."""
+        api, workload, torch = self.api, self.workload, self.torch
+        out = None
+        self.cpu_barrier()
+        if self.rank == 0:
+            N = self.world
+            offs = workload.count(spec, 0, N * n_reads)
+            pin = api.PinnedArray((int(offs[-1]), 2), np.uint64)
+            workload.fill(spec, offs, pin.array, 0)
+            ctxs = [api.ChainContext(device=k) for k in range(N)]
+            cuts = np.zeros(N + 1, dtype=np.int64)
+            resv = (api._Result * N)()
+            handles = (C.c_void_p * N)(*[c._h for c in ctxs])
+
+            def step():
+                api._check(api.lib().mm2b200_chain_batch_multi(handles, N, C.byref(prm), N * n_reads, offs.ctypes.data, pin.ptr,
+                                                               cuts.ctypes.data, resv))
+            step()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step()
+            dt = (time.perf_counter() - t0) / steps
+            with api.ChainContext(device=0, count_visited=True) as cc:
+                pairs0 = int(cc.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr).n_visited)
+            # visited pairs of the other shards: every rank's own count was summed in the headline; here the per-shard
+            # figure is estimated from anchors (identical generator, read ranges differ) -- reads/s is exact
+            est_pairs = pairs0 * float(offs[-1]) / float(offs[n_reads])
+            out = {"api": "mm2b200_chain_batch_multi: one host process, one context + host thread per GPU, pinned host buffers",
+                   "n_gpus": N, "reads_per_step": int(N * n_reads), "anchors_per_step": int(offs[-1]),
+                   "ms_per_step": 1e3 * dt, "reads_per_s": N * n_reads / dt,
+                   "value": est_pairs / dt, "unit": UNIT, "value_note": "visited pairs scaled from shard 0's count by anchors",
+                   "devices": sorted({c.device for c in ctxs}),
+                   "scaling_efficiency": (solo_s / dt) if solo_s else None,
+                   "scaling_efficiency_note": "reads/s of this call / (N x reads/s of rank 0 alone through mm2b200_chain_batch)",
+                   "shard_reads": np.diff(cuts).tolist()}
+            for c in ctxs:
+                c.close()
+            pin.free()
+        self.cpu_barrier()
+        return out
 
 
 def main():
@@ -190,7 +678,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="map-ont-100k")
     ap.add_argument("--reads", type=int, default=0, help="override reads per GPU (default: the config's)")
-    ap.add_argument("--cpu-reads", type=int, default=CPU_SAMPLE_READS)
+    ap.add_argument("--configs", default="all", help="'all', 'none' or a comma list of the other BASELINE.json configs to add as the configs block")
+    ap.add_argument("--config-steps", type=int, default=2, help="timed device-resident passes per chunk in the configs block")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--slot-anchors", type=int, default=0)
     ap.add_argument("--slots", type=int, default=0)
@@ -200,200 +689,10 @@ def main():
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
         return run_reference(args)
-
-    import torch
-    import torch.distributed as dist
-    from minimap2_chaindp_b200 import api, workload
-    import __graft_entry__ as ge
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if rank == 0:
+    if int(os.environ.get("RANK", "0")) == 0:
+        import __graft_entry__ as ge
         ge.build()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the chaining path has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line (NCCL is only used for the barrier / reductions)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        dist.barrier()
-    dev = torch.device("cuda", local)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def reduce_max(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def reduce_sum(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    # ---- this rank's shard of the read stream: reads [rank*n, (rank+1)*n), generated straight into pinned memory
-    spec = workload.CONFIGS[args.workload]
-    n_reads = args.reads or spec.n_reads
-    first = rank * n_reads
-    offs = workload.count(spec, first, n_reads)
-    n_anchors = int(offs[-1])
-    pin = api.PinnedArray((n_anchors, 2), np.uint64)
-    workload.fill(spec, offs, pin.array, first)
-    prm = api.params(spec.preset)
-
-    ctx = api.ChainContext(device=local, n_slots=args.slots, slot_anchors=args.slot_anchors, profile=True)
-    if args.wire:
-        ctx.set_upload(True, args.wire_threads)
-    stream = torch.cuda.current_stream()
-    d_a = torch.from_numpy(pin.array.view(np.int64)).to(dev)
-    d_offs = torch.from_numpy(offs).to(dev)
-    torch.cuda.synchronize()
-
-    def device_step():
-        return ctx.chain_device(prm, n_reads, n_anchors, d_offs.data_ptr(), d_a.data_ptr(), stream.cuda_stream)
-
-    def e2e_step():
-        return ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
-
-    # ---- warm-up (allocates workspaces and pinned result arenas outside the timed regions)
-    for _ in range(max(args.warmup, 1)):
-        out = device_step()
-    torch.cuda.synchronize()
-    for _ in range(max(args.warmup, 1)):
-        res = e2e_step()
-    import ctypes as C
-    # metric numerator: reference-visited pairs, counted once by the instrumented kernel variant (untimed)
-    with api.ChainContext(device=local, count_visited=True) as cctx:
-        cres = cctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
-        pairs_step = int(cres.n_visited)
-        lanes_step = int(cres.n_lanes)
-    chains_step = int(np.frombuffer((C.c_char * 8).from_address(res.u_off + 8 * n_reads), dtype=np.int64)[0])
-    canch_step = int(np.frombuffer((C.c_char * 8).from_address(res.b_off + 8 * n_reads), dtype=np.int64)[0])
-    n_units = int(res.n_units)
-    n_sub = int(res.n_sub_batches)
-
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-
-    # ---- timed region 1: device-resident inputs, CUDA events on the launching stream
-    ctx.stage_reset()
-    launches0 = ctx.launch_count()
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(stream)
-    for _ in range(args.steps):
-        device_step()
-    ev1.record(stream)
-    barrier()
-    dev_ms = reduce_max(ev0.elapsed_time(ev1))
-    launches = ctx.launch_count() - launches0
-    stage = {s: ctx.stage_ms(s) for s in ("prep", "fill", "compact", "tail", "gather")}
-
-    # ---- timed region 2: end to end through the C ABI with host buffers (H2D + kernels + D2H inside)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        res = e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = reduce_max(time.perf_counter() - t0)
-    barrier()
-    clocks = sampler.stop() if rank == 0 else None
-
-    total_pairs = reduce_sum(float(pairs_step))
-    total_reads = reduce_sum(float(n_reads))
-    total_anchors = reduce_sum(float(n_anchors))
-    value = total_pairs * args.steps / (dev_ms * 1e-3)
-    e2e_value = total_pairs * args.steps / e2e_s
-    h2d, wire_sub = ctx.upload_stats()      # bytes the last e2e step copied host -> device (counted by the library)
-    d2h = n_reads * (4 + 8 + 8) + chains_step * 8 + canch_step * 16 + n_sub * 64
-
-    # ---- rooflines of the dominant kernel (k_fill): per-launch averages from the events around it
-    fill_ms, fill_launches = stage["fill"]
-    fill_ms_per_step = fill_ms / max(args.steps, 1)
-    hbm_peak, peak_src = peaks()
-    hbm_achieved = n_anchors * BYTES_PER_ANCHOR / (fill_ms_per_step * 1e-3) / 1e9 if fill_ms_per_step > 0 else 0.0
-    int_peak_mix = ctx.int_peak(1)
-    int_peak_alu = ctx.int_peak(0)
-    int_achieved = pairs_step * INT_OPS_PER_PAIR / (fill_ms_per_step * 1e-3) if fill_ms_per_step > 0 else 0.0
-
-    traffic = None   # dram bytes of one k_fill launch from the committed ncu capture of this exact workload, else null
-    try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_fill_traffic.json")))
-        if tj.get("workload") == spec.name and int(tj.get("reads", 0)) == n_reads:
-            traffic = int(tj["dram_bytes_per_launch"])
-    except Exception:
-        traffic = None
-
-    line = None
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1),
-            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int32", "data": "synthetic",
-            "config": {"workload": f"{spec.name}: G-anc synthetic anchors, preset {spec.preset} "
-                                   f"(max_dist {prm.max_dist_x}, bw {prm.bw}, max_skip {prm.max_skip}, max_iter unbounded = reference)",
-                       "reads_per_gpu": n_reads, "anchors_per_gpu": n_anchors, "visited_pairs_per_gpu": pairs_step,
-                       "runs_per_gpu": n_units, "sharding": f"reads x{world} (one process per GPU, no collective)",
-                       "l2": f"inputs larger than L2 ({n_anchors * 16 / 2**20:.0f} MiB of anchors + workspace vs 126 MB)",
-                       "sub_batches_e2e": n_sub},
-            "reads_per_s": total_reads * args.steps / (dev_ms * 1e-3),
-            "anchors_per_s": total_anchors * args.steps / (dev_ms * 1e-3),
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "reads_per_s": total_reads * args.steps / e2e_s, "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "api": "mm2b200_chain_batch (pinned host anchors in, pinned host chains out)",
-                    "upload": (f"host batcher wire format ({wire_sub}/{n_sub} sub-batches, {h2d / max(n_anchors, 1):.2f} B/anchor, "
-                               f"encoded by host threads inside the timed region)") if wire_sub else "raw mm128_t (16 B/anchor)"},
-            "gpu_launches": int(launches),
-            "clocks": clocks,
-            "roofline": {"kernel": "k_fill", "bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": hbm_achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": n_anchors * BYTES_PER_ANCHOR, "ms_per_launch": fill_ms_per_step,
-                         "note": "k_fill is integer-issue bound, not HBM bound (see roofline_issue); 40 B/anchor algorithmic"},
-            "roofline_issue": {"kernel": "k_fill", "bound": "int-issue", "achieved": int_achieved / 1e12, "peak": int_peak_mix / 1e12,
-                               "unit": "T lane-op/s", "frac": int_achieved / int_peak_mix if int_peak_mix else None,
-                               "peak_alu_pipe_only": int_peak_alu / 1e12, "ops_per_pair": INT_OPS_PER_PAIR,
-                               "lane_efficiency": pairs_step / lanes_step if lanes_step else None,
-                               "peak_source": "measured live (mm2b200_int_peak: add/xor/mad.lo streams on all SMs)"},
-            "stage_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in stage.items()},
-        }
-    # ---- CPU baseline beside it (rank 0, N=1 only): the reference on a bounded sample, and a parity spot check
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        n_sample = min(args.cpu_reads, n_reads)
-        so = offs[:n_sample + 1].copy()
-        sa = pin.array[:int(so[-1])]
-        threads = host_cores()
-        ref, kind, used = cpu_reference_run(spec, so, sa, threads, want_outputs=True)
-        s_pairs = count_pairs_cpu(spec, so, sa, threads)
-        u_off = np.frombuffer((C.c_char * (8 * (n_sample + 1))).from_address(res.u_off), dtype=np.int64)
-        b_off = np.frombuffer((C.c_char * (8 * (n_sample + 1))).from_address(res.b_off), dtype=np.int64)
-        gu = np.frombuffer((C.c_char * (8 * int(u_off[-1]))).from_address(res.u), dtype=np.uint64) if u_off[-1] else np.zeros(0, np.uint64)
-        gb = np.frombuffer((C.c_char * (16 * int(b_off[-1]))).from_address(res.b), dtype=np.uint64).reshape(-1, 2) if b_off[-1] else np.zeros((0, 2), np.uint64)
-        parity = bool(np.array_equal(u_off, ref.u_off) and np.array_equal(b_off, ref.b_off)
-                      and np.array_equal(gu, ref.u) and np.array_equal(gb, ref.b))
-        line["cpu_baseline"] = {"value": s_pairs / ref.seconds, "unit": UNIT, "cores": used, "kind": kind,
-                                "reads_per_s": n_sample / ref.seconds,
-                                "sample": f"first {n_sample} reads of {spec.name} ({int(so[-1])} anchors, {s_pairs} visited pairs), "
-                                          f"reference mm_chain_dp under its kt_for, one kalloc arena per thread, 1 pass",
-                                "parity_with_gpu_on_sample": parity}
-        if not parity:
-            line["parity_error"] = "GPU chains differ from the reference on the CPU-baseline sample"
-    if rank == 0:
-        print(json.dumps(line))
-    ctx.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+    return Bench(args).run()
 
 
 if __name__ == "__main__":

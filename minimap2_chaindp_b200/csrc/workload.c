@@ -53,6 +53,40 @@ static int cmp_x(const void *pa, const void *pb)
 	return a->y < b->y ? -1 : a->y > b->y;
 }
 
+/* ascending by (x, y) -- the same total order as cmp_x, so the output is identical to qsort's (equal elements are
+ * indistinguishable); long reads (map-pb, asm5: 5e4..4e6 anchors) spend most of the generator's time here, so they get
+ * an LSD radix sort on x (16-bit digits, constant digits skipped) followed by an insertion pass over equal-x groups. */
+static void sort_anchors(wl_anchor_t *a, int64_t n)
+{
+	wl_anchor_t *src = a, *dst, *tmp;
+	uint32_t *cnt;
+	int pass;
+	int64_t i;
+	if (n < 4096) { if (n > 1) qsort(a, (size_t)n, sizeof(wl_anchor_t), cmp_x); return; }
+	tmp = (wl_anchor_t*)malloc((size_t)n * sizeof(wl_anchor_t));
+	cnt = (uint32_t*)malloc(65536 * sizeof(uint32_t));
+	dst = tmp;
+	for (pass = 0; pass < 4; ++pass) {
+		const int sh = 16 * pass;
+		uint32_t acc = 0, k;
+		memset(cnt, 0, 65536 * sizeof(uint32_t));
+		for (i = 0; i < n; ++i) ++cnt[(src[i].x >> sh) & 0xffff];
+		if (cnt[(src[0].x >> sh) & 0xffff] == (uint32_t)n) continue;      /* digit is the same everywhere */
+		for (k = 0; k < 65536; ++k) { const uint32_t c = cnt[k]; cnt[k] = acc; acc += c; }
+		for (i = 0; i < n; ++i) dst[cnt[(src[i].x >> sh) & 0xffff]++] = src[i];
+		{ wl_anchor_t *t = src; src = dst; dst = t; }
+	}
+	if (src != a) memcpy(a, src, (size_t)n * sizeof(wl_anchor_t));
+	for (i = 1; i < n; ++i)                                              /* ties on x: order by y */
+		if (a[i].x == a[i - 1].x && a[i].y < a[i - 1].y) {
+			wl_anchor_t v = a[i];
+			int64_t j = i;
+			while (j > 0 && a[j - 1].x == v.x && a[j - 1].y > v.y) { a[j] = a[j - 1]; --j; }
+			a[j] = v;
+		}
+	free(cnt); free(tmp);
+}
+
 static inline void emit(wl_anchor_t *out, int64_t *k, uint32_t strand, uint32_t rid, uint32_t rpos, int32_t span, int32_t qpos)
 {
 	if (out) {
@@ -121,7 +155,7 @@ static int64_t gen_read(const wl_spec_t *sp, int64_t read_id, wl_anchor_t *out)
 			gen_locus(sp, &rng, out, &k, strand, rid, r0, q0, q1);
 		}
 	}
-	if (out && k > 1) qsort(out, (size_t)k, sizeof(wl_anchor_t), cmp_x);
+	if (out && k > 1) sort_anchors(out, k);
 	return k;
 }
 
