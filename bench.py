@@ -39,6 +39,13 @@ import time
 import numpy as np
 
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # before CUDA initialises (see chain_api.cu: sub-batch streams)
+if os.environ.get("OMP_NUM_THREADS") == "1" and "LOCAL_WORLD_SIZE" in os.environ:
+    # torchrun's default of one OpenMP thread per rank would serialise the (untimed) workload generator
+    try:
+        _cores = len(os.sched_getaffinity(0))
+    except Exception:
+        _cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(max(1, _cores // max(int(os.environ.get("LOCAL_WORLD_SIZE", "1")), 1)))
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -259,7 +266,7 @@ class Bench:
         self.cpu_group = None
         if self.world > 1:
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-            os.environ.setdefault("NCCL_DEBUG", "WARN")     # the driver's own setting wins (it reads NCCL's rank lines)
+            # NCCL_DEBUG is left to the driver (it reads NCCL's rank lines); unset, NCCL prints nothing to stdout
             dist.init_process_group("nccl", device_id=self.dev)
             # a CPU-side group: ranks that only WAIT (while rank 0 drives their GPUs in the single-process legs) must not
             # sit in an NCCL kernel on the GPU they are lending
