@@ -66,6 +66,7 @@ struct LaunchCfg {
 	int sm_count;
 	int fill_blocks_per_sm;      // generic kernel
 	int count_visited;           // instrumented fast kernel (metric numerator) instead of the plain one
+	int fill_ring;               // ring depth of the fill kernel (0 = chosen per sub-batch from the anchors per read)
 };
 
 // launchers (chain_kernels.cu); every launcher returns the number of kernels it enqueued

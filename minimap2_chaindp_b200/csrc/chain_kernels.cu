@@ -272,12 +272,21 @@ __global__ void __launch_bounds__(128) k_fill_generic(Workspace w, mm2b200_param
 //  * IMPROVE lanes: one redux.max finds the chunk maximum M and the first lane L that attains it; if no earlier
 //    lane beats the running maximum, L is the only IMPROVE lane (the common case) and no prefix scan is needed.
 #define FILL_WARPS 4
-#define RING 64
-// dynamic shared memory of k_fill_fast, byte offsets from the CTA's base (per warp: 1 KB ring + 1 KB v + 512 B anchors)
-#define SM_RING   0                               // int4 {x, q, f, p} of the last RING anchors, 16 B each
-#define SM_VRING  (FILL_WARPS * RING * 16)        // v[] of the same anchors, 16-byte stride so one register addresses both
-#define SM_ABUF   (2 * FILL_WARPS * RING * 16)    // {x, q, span, -} of the current 32-aligned block of anchors
-#define SM_TAB    (SM_ABUF + FILL_WARPS * 32 * 16) // 16-bit gap costs, tab_entries per warp
+// Dynamic shared memory of k_fill_fast<RING>, byte offsets from the CTA's (RING*16-byte aligned) base.  Per warp:
+//   ring       RING x int4 {x, q, f, p} of the last RING anchors
+//   companion  RING x 16 B, same slot addressing: word 0 = v[] (chain.c:90), word 1 = mark tag (t[] of chain.c:83,87 for
+//              the anchors that are still in the ring; marks on older anchors go through t[] in global memory)
+//   abuf       32 x int4 {x, q, span, -} of the current 32-aligned block of anchors
+//   table      16-bit gap costs, tab_entries per warp
+// RING = 64 (two chunks; 3.5 KB per warp, 10 CTAs per SM) for ordinary reads, RING = 256 (eight chunks; 9.5 KB per warp)
+// for sub-batches of long reads, whose windows hold hundreds of predecessors (map-pb: 157 visited pairs per anchor).
+template <int RING> struct FillSmem {
+	static constexpr int ring = 0;
+	static constexpr int comp = FILL_WARPS * RING * 16;
+	static constexpr int abuf = 2 * FILL_WARPS * RING * 16;
+	static constexpr int tab = abuf + FILL_WARPS * 32 * 16;
+	static constexpr unsigned mask = RING * 16u - 1u;
+};
 
 // explicit 32-bit shared addresses: every access is one LDS/STS with an immediate offset, no generic-address math
 template <int OFF> static __device__ __forceinline__ int4 lds128(unsigned addr)
@@ -551,14 +560,22 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 // warp-uniform scalar code (two shuffles per scored lane).  Returns 0 = scan goes on, 1 = anchor finished,
 // 2 = too many scored lanes, nothing was changed: run the dense routine on this chunk.
 #define SPARSE_MAX 4
-template <bool TABLE, bool COUNT, bool WIDE>
+// a mark on anchor pj while anchor i is scanned (chain.c:87): in the ring's tag word while pj is still in the ring
+template <int RING>
+static __device__ __forceinline__ void publish_mark(const int pj, const int i, const unsigned ring_w, int32_t *t)
+{
+	if (i - pj <= RING) sts32<FillSmem<RING>::comp + 4>(ring_w + (((unsigned)pj & (RING - 1)) << 4), i);
+	else t[pj] = i;
+}
+
+template <bool TABLE, bool COUNT, bool WIDE, int RING>
 static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, int &vbest, int &budget, long long &visited,
                                                          const int i, const int jb, const int jlo, const int lane,
                                                          const int4 rj, const bool marked_mem,
                                                          const unsigned xi, const int qi, const int span,
                                                          const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
                                                          const int B0, const unsigned tab_w, const double avg,
-                                                         int32_t *t, const int32_t *vg)
+                                                         int32_t *t, const int32_t *vg, const unsigned ring_w)
 {
 	const int j = jb - lane;
 	const unsigned dr = xi - (unsigned)rj.x;
@@ -592,7 +609,8 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 		live &= live - 1u;
 		const int scL = __shfl_sync(FULL, sc, L), pjL = __shfl_sync(FULL, rj.w, L);
 		if (scL > max_f) {                                // chain.c:80-82
-			max_f = scL; max_j = jb - L; vbest = vg[jb - L];
+			max_f = scL; max_j = jb - L;
+			vbest = (i - max_j <= RING) ? lds32<FillSmem<RING>::comp>(ring_w + (((unsigned)max_j & (RING - 1)) << 4)) : vg[max_j];
 			budget = min(budget + 1, B0);
 		} else if (((mmem | lm) >> L) & 1u) {             // chain.c:83-85
 			if (--budget <= 0) {
@@ -603,7 +621,7 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 		if (pjL >= 0) {                                   // chain.c:87
 			const unsigned kt = (unsigned)(jb - pjL);
 			if (kt < 32u) lm |= 1u << kt;
-			else if (lane == 0) t[pjL] = i;
+			else if (lane == 0) publish_mark<RING>(pjL, i, ring_w, t);
 		}
 	} while (live);
 	return done;
@@ -611,18 +629,19 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 
 // FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
 // (register caps were tried: 40 registers / 12 CTAs per SM 5.70 ms, 32 / 16 CTAs 6.09 ms, 67 / 7 CTAs 5.07 ms, default 48 / 10 CTAs 4.89 ms)
-template <bool TABLE, bool FULLV, bool WIDE>
+template <bool TABLE, bool FULLV, bool WIDE, int RING>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
 	extern __shared__ int4 smem4[];
+	typedef FillSmem<RING> SM;
 	if (prm.is_cdna || (w.counters[CNT_MULTISEG] != 0)) return;   // the generic kernel handles those
 
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-	// 1 KB-aligned base: a warp's ring is then a naturally aligned 1 KB window and ring addresses wrap with one LOP3
-	const unsigned sbase = ((unsigned)__cvta_generic_to_shared(smem4) + 1023u) & ~1023u;
-	unsigned ring_w = sbase + SM_RING + wib * (RING * 16);
-	unsigned abuf_w = sbase + SM_ABUF + wib * (32 * 16);
-	unsigned tab_w = sbase + SM_TAB + wib * tab_entries * 2;
+	// base aligned to the ring size: a warp's ring is then a naturally aligned window and ring addresses wrap with one LOP3
+	const unsigned sbase = ((unsigned)__cvta_generic_to_shared(smem4) + SM::mask) & ~SM::mask;
+	unsigned ring_w = sbase + SM::ring + wib * (RING * 16);
+	unsigned abuf_w = sbase + SM::abuf + wib * (32 * 16);
+	unsigned tab_w = sbase + SM::tab + wib * tab_entries * 2;
 	// opaque to the optimiser: keep the three per-warp base addresses in registers instead of re-deriving them per access
 	asm volatile("" : "+r"(ring_w), "+r"(abuf_w), "+r"(tab_w));
 	const int one = 1 + (int)threadIdx.y;         // see addi_fma (threadIdx.y is 0, which ptxas cannot know)
@@ -643,6 +662,10 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 	int32_t *vg = w.v, *t = w.t;
 	unsigned tab_key = 0;
 	bool have_tab = false;
+
+	// no mark tag may match an anchor index before it is written (tags are batch-wide anchor indices, all >= 0)
+	for (int k = lane; k < RING; k += 32) sts32<SM::comp + 4>(ring_w + (unsigned)k * 16u, -1);
+	__syncwarp();
 
 	for (;;) {
 		// next run from the device-side queue; the redux makes the index provably warp-uniform for the compiler
@@ -669,7 +692,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			const int sp = (int)((a0.y >> 32) & 0xff);
 			const unsigned slot = ring_w + (unsigned)(s & (RING - 1)) * 16u;
 			sts128<0>(slot, make_int4((int)(unsigned)a0.x, (int)(unsigned)a0.y, sp, -1));
-			sts32<SM_VRING>(slot, sp);
+			sts32<SM::comp>(slot, sp);
 		}
 
 		// anchors are processed in 32-aligned blocks: lane l loads a[blk + l] once, every step broadcasts its own from
@@ -697,54 +720,47 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 
 			// chunk 0: anchors i-1 .. i-32 from the ring; no earlier chunk can have marked them
 			int4 rj = lds128<0>(raddr);
-			int vj = lds32<SM_VRING>(raddr);
+			int vj = lds32<SM::comp>(raddr);
 			int dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 			int cost = TABLE ? lds_u16(mad2_fma(min((unsigned)dd0, (unsigned)bw), tab_w)) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 			if (FULLV) ++n_chunks;
 			int done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, addi_fma<-1>(i, one), jlo, lane, rj, vj, false,
 			                                         xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
 			if (!done && addi_fma<-33>(i, one) >= jlo) {
-				if (__any_sync(FULL, far)) { if (far) t[rj.w] = i; }
-				// chunk 1: anchors i-33 .. i-64, still in the ring; marks from chunk 0 that fell here are in t[]
-				__syncwarp();
-				rj = lds128<0>(raddr ^ 512u);
-				const bool mmem = t[max(i - 33 - lane, jlo)] == i;        // (lanes below jlo are outside the window anyway)
-				if (FULLV) ++n_chunks;
-				done = scan_chunk_sparse<TABLE, FULLV, WIDE>(max_f, max_j, vbest, budget, visited, i, i - 33, jlo, lane, rj, mmem,
-				                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
-				if (done == 2) {                                  // many scored lanes: warp-wide replay
-					vj = lds32<SM_VRING>(raddr ^ 512u);
-					dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-					cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
-					done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, i - 33, jlo, lane, rj, vj, mmem,
-					                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
-					if (!done && far) t[rj.w] = i;                // marks beyond this chunk (the scalar path writes its own)
-				}
-				// deeper chunks: the same records from global memory (flushed there in 32-anchor blocks; L1/L2 hits)
-				for (int jb = i - 65; !done && jb >= jlo; jb -= 32) {
-					__syncwarp();
-					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo re-read anchor jlo and are masked
-					rj = wrec[jc];
-					const bool mg = t[jc] == i;
+				// marks of chunk 0 that fell beyond it: tag word of the ring slot (or t[] for anchors that left the ring)
+				if (__any_sync(FULL, far)) { if (far) publish_mark<RING>(rj.w, i, ring_w, t); }
+				// chunks 1 .. RING/32-1 read the same ring; deeper ones the records flushed to global memory (L1/L2 hits)
+				unsigned ra = raddr;
+				int c = 1;
+				for (int jb = i - 33; !done && jb >= jlo; jb -= 32, ++c) {
+					__syncwarp();                                     // marks published by the previous chunk are visible
+					const bool in_ring = c < RING / 32;
+					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo are masked (j >= jlo in the scan routines)
+					bool mg;
+					if (in_ring) {
+						ra = ring_w | (addi_fma<-512>(ra, one) & SM::mask);
+						rj = lds128<0>(ra);
+						mg = lds32<SM::comp + 4>(ra) == i;
+					} else { rj = wrec[jc]; mg = t[jc] == i; }
 					if (FULLV) ++n_chunks;
-					done = scan_chunk_sparse<TABLE, FULLV, WIDE>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
-					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg);
-					if (done == 2) {
-						vj = vg[jc];
+					done = scan_chunk_sparse<TABLE, FULLV, WIDE, RING>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
+					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg, ring_w);
+					if (done == 2) {                                  // many scored lanes: warp-wide replay
+						vj = in_ring ? lds32<SM::comp>(ra) : vg[jc];
 						dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
 						cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
 						done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
 						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
-						if (!done && far) t[rj.w] = i;
+						if (!done && far) publish_mark<RING>(rj.w, i, ring_w, t);   // (the scalar path publishes its own)
 					}
 				}
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
 			sts128<0>(waddr, make_int4((int)xi, qi, max_f, max_j));
-			sts32<SM_VRING>(waddr, max(vbest, max_f));
+			sts32<SM::comp>(waddr, max(vbest, max_f));
 			aaddr = addi_fma<16>(aaddr, one);
-			raddr = ring_w | (addi_fma<16>(raddr, one) & (RING * 16u - 1u));
-			waddr = ring_w | (addi_fma<16>(waddr, one) & (RING * 16u - 1u));
+			raddr = ring_w | (addi_fma<16>(raddr, one) & SM::mask);
+			waddr = ring_w | (addi_fma<16>(waddr, one) & SM::mask);
 			// (no warp sync needed: every lane stored the same words, so a later load by any lane sees at least its own store)
 		}
 			// flush the block (deep windows and the later kernels read the records from global memory)
@@ -753,7 +769,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				if (idx > s && idx < i1) {
 					const unsigned slot = ring_w + (unsigned)(idx & (RING - 1)) * 16u;
 					wrec[idx] = lds128<0>(slot);
-					vg[idx] = lds32<SM_VRING>(slot);
+					vg[idx] = lds32<SM::comp>(slot);
 				}
 			}
 		}
@@ -1406,7 +1422,7 @@ static inline int blocks_for(long long items, int per_block, int cap)
 	return (int)b;
 }
 
-static int fill_smem_bytes(int tab_entries) { return SM_TAB + FILL_WARPS * tab_entries * 2 + 1024; }   // + alignment slack
+template <int RING> static int fill_smem_bytes(int tab_entries) { return FillSmem<RING>::tab + FILL_WARPS * tab_entries * 2 + RING * 16; }   // + alignment slack
 static int fill_tab_entries(const mm2b200_params_t &prm)
 {	// 16-bit table of bw+1 gap costs per warp, only while it stays small (<= 2 KB per warp) and the costs fit
 	if (prm.bw < 0 || prm.bw > 1023) return 0;
@@ -1430,15 +1446,22 @@ static int cached_occupancy(OccCache &oc, K kern, int threads, int smem)
 	return oc.occ;
 }
 
-template <bool TABLE, bool FULLV, bool WIDE>
-static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
+template <bool TABLE, bool FULLV, bool WIDE, int RING>
+static void launch_fill_ring(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
-	const int smem = fill_smem_bytes(tab_entries);
-	auto kern = k_fill_fast<TABLE, FULLV, WIDE>;
+	const int smem = fill_smem_bytes<RING>(tab_entries);
+	auto kern = k_fill_fast<TABLE, FULLV, WIDE, RING>;
 	static thread_local OccCache oc;   // one cache per template instance
 	const int occ = cached_occupancy(oc, kern, FILL_WARPS * 32, smem);
 	const int per_sm = (g_fill_ctas_cap > 0 && g_fill_ctas_cap < occ) ? g_fill_ctas_cap : occ;
 	kern<<<sms * per_sm, FILL_WARPS * 32, smem, s>>>(w, prm, tab_entries);
+}
+template <bool TABLE, bool FULLV, bool WIDE>
+static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, int ring, cudaStream_t s)
+{
+	if (ring >= 256) launch_fill_ring<TABLE, FULLV, WIDE, 256>(w, prm, sms, tab_entries, s);
+	else if (ring >= 128) launch_fill_ring<TABLE, FULLV, WIDE, 128>(w, prm, sms, tab_entries, s);
+	else launch_fill_ring<TABLE, FULLV, WIDE, 64>(w, prm, sms, tab_entries, s);
 }
 
 void query_launch_cfg(LaunchCfg *cfg)
@@ -1452,6 +1475,8 @@ void query_launch_cfg(LaunchCfg *cfg)
 	cfg->fill_blocks_per_sm = occ;
 	const char *ec = getenv("MM2B200_FILL_CTAS");
 	g_fill_ctas_cap = ec ? atoi(ec) : 0;
+	const char *er = getenv("MM2B200_RING");       // force the fill kernel's ring depth (64, 128, 256); default: by read length
+	cfg->fill_ring = er ? atoi(er) : 0;
 }
 
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
@@ -1470,10 +1495,13 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 	if (!host_generic) {
 		const int te = fill_tab_entries(prm);
 		const bool full = cfg.count_visited || prm.max_iter > 0;   // instrumented / max_iter-aware variant
+		// ring depth: long reads (thousands of anchors per read: map-pb, asm5) scan hundreds of predecessors per anchor, which
+		// the 256-anchor ring keeps in shared memory; ordinary reads rarely leave the first two chunks and keep the occupancy
+		const int ring = cfg.fill_ring ? cfg.fill_ring : (w.n_reads > 0 && w.n_anchors / w.n_reads >= 4096 ? 256 : 64);
 		if (prm.max_dist_x >= (1 << 26)) {                         // per-lane window test not exact (33 gaps could wrap 2^32): general chunk routine only
-			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, s);
-		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, s); }
-		else { if (full) launch_fill_fast<false, true, false>(w, prm, cfg.sm_count, 0, s); else launch_fill_fast<false, false, false>(w, prm, cfg.sm_count, 0, s); }
+			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, ring, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, ring, s);
+		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, ring, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, ring, s); }
+		else { if (full) launch_fill_fast<false, true, false>(w, prm, cfg.sm_count, 0, ring, s); else launch_fill_fast<false, false, false>(w, prm, cfg.sm_count, 0, ring, s); }
 		++n;
 	}
 	k_fill_generic<<<cfg.sm_count * cfg.fill_blocks_per_sm, 128, 0, s>>>(w, prm); ++n;

@@ -66,6 +66,34 @@ def test_deep_windows(ctx, seed):
         assert_same(got, want, f"deep seed {seed} {over}")
 
 
+@pytest.mark.parametrize("ring", [64, 128, 256])
+def test_ring_depths(ring, monkeypatch):
+    """The fill kernel's ring depth (MM2B200_RING; 256 is what sub-batches of long reads get): chunks 1..RING/32-1 come from
+    shared memory with their marks in the ring's tag words, deeper ones from global memory with marks in t[].  Dense and
+    sparse windows, break budgets that cross several chunks, and the visited-pair counter, all against the oracle."""
+    monkeypatch.setenv("MM2B200_RING", str(ring))
+    rng = np.random.default_rng(7700 + ring)
+    reads = [random_colinear(rng, int(n), noise=float(rng.random()) * 0.6, step=int(rng.integers(1, 6))) for n in rng.integers(2, 2500, 20)]
+    reads += [interleaved_diagonals(rng, int(n), k, step=int(rng.integers(1, 4))) for k in (3, 9, 40) for n in rng.integers(200, 3000, 4)]
+    offs, a = concat_reads(reads)
+    with api.ChainContext(device=0) as c, api.ChainContext(device=0, count_visited=True) as cc:
+        for over in (dict(), dict(max_skip=3), dict(max_skip=200), dict(bw=100), dict(max_dist_x=20000, max_dist_y=20000),
+                     dict(max_iter=300), dict(min_cnt=1, min_sc=0)):
+            want = oracle.chain_batch(oracle.params("map-ont", **over), offs, a)
+            assert_same(c.chain_batch(api.params("map-ont", **over), offs, a), want, f"ring {ring} {over}")
+            got = cc.chain_batch(api.params("map-ont", **over), offs, a)
+            assert_same(got, want, f"ring {ring} counted {over}")
+            assert got.n_visited == want.visited, (ring, over)
+
+
+def test_long_reads_pick_the_deep_ring(ctx):
+    """A sub-batch of long reads (>= 4096 anchors per read on average) runs with the 256-anchor ring."""
+    spec = workload.CONFIGS["map-pb-ul-20k"]
+    offs, a = workload.generate(spec, 5, 3)
+    got = ctx.chain_batch(api.params(spec.preset), offs, a)
+    assert_same(got, oracle.chain_batch(oracle.params(spec.preset), offs, a), "map-pb reads, deep ring")
+
+
 @pytest.mark.parametrize("k", [2, 5, 9, 20, 33, 50])
 def test_sparse_chunks(ctx, k):
     """Chunks with 0-4 scored lanes (scalar path of the fill kernel), marks and breaks that cross chunk boundaries."""
