@@ -229,6 +229,10 @@ struct mm2b200_ctx {
 	int64_t h2d_bytes = 0, wire_sub_batches = 0;   // of the last batch call
 	// results (pinned)
 	PinnedBuf r_n_u, r_u_off, r_b_off, r_u, r_b, r_rec_off, r_rec;
+	// mm2b200_chain_device runs the two halves of a batch on the caller's stream and on this one
+	cudaStream_t aux_stream = nullptr;
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	bool split_device = true;
 	// profiling
 	StageAcc acc[ST_N];
 	std::vector<StageSpan> spans;
@@ -251,7 +255,7 @@ static int ensure_slot(mm2b200_ctx *ctx, Slot &s, size_t anchors, size_t reads)
 	void *pa = nullptr, *poffs = nullptr;
 	Item items[] = {
 		{ &pa, 16 * A }, { &poffs, 8 * (R + 1) },
-		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 16 * (A / 2 + 1) }, { (void**)&w.counters, 4 * CNT_N }, { (void**)&w.visited, 16 },
+		{ (void**)&w.avg, 4 * R }, { (void**)&w.units, 2 * 16 * (A / 2 + 1) }, { (void**)&w.counters, 2 * 4 * CNT_N }, { (void**)&w.visited, 16 },
 		{ (void**)&w.wrec, 16 * A }, { (void**)&w.f, 4 * A }, { (void**)&w.p, 4 * A }, { (void**)&w.v, 4 * A }, { (void**)&w.t, 4 * A },
 		{ (void**)&w.newid, 4 * A }, { (void**)&w.rec, 24 * A }, { (void**)&w.recp, 4 * A }, { (void**)&w.new_i, 4 * R },
 		{ (void**)&w.succ, A }, { (void**)&w.claimed, A }, { (void**)&w.members, 4 * A },
@@ -425,6 +429,14 @@ extern "C" int mm2b200_create(const mm2b200_config_t *cfg, mm2b200_ctx_t **out)
 	}
 	query_launch_cfg(&ctx->lc);
 	ctx->lc.count_visited = c.count_visited;
+	if (cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+	    cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+		int rc = fail(MM2B200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+		mm2b200_destroy(ctx);
+		return rc;
+	}
+	{ const char *es = getenv("MM2B200_SPLIT"); ctx->split_device = !(es && atoi(es) == 0); }
 	{	// host batcher threads: opt-in (MM2B200_WIRE=1 or mm2b200_set_upload; MM2B200_WIRE_THREADS overrides the thread count).
 		// Off by default: on the measured GPU box (16 vCPUs) encoding 77 M anchors costs more host memory time than the
 		// 0.55 GB it keeps off the PCIe bus (e2e 41 ms vs 27 ms raw, profiles/r01j_wire_upload.md).
@@ -455,6 +467,9 @@ extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 		if (s.stream) cudaStreamDestroy(s.stream);
 	}
 	drain_spans(ctx);
+	if (ctx->aux_stream) { cudaStreamSynchronize(ctx->aux_stream); cudaStreamDestroy(ctx->aux_stream); }
+	if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+	if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
 	for (auto e : ctx->ev_pool) cudaEventDestroy(e);
 	ctx->r_n_u.release(); ctx->r_u_off.release(); ctx->r_b_off.release(); ctx->r_u.release(); ctx->r_b.release();
 	ctx->r_rec_off.release(); ctx->r_rec.release();
@@ -883,9 +898,36 @@ extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	Workspace w = s.w;              // private copy pointing at the caller's inputs
 	w.a = (const ulonglong2*)d_a; w.offs = d_offs;
 	w.n_reads = (int32_t)n_reads; w.n_anchors = (int32_t)n_anchors;
-	enqueue_fill(ctx, w, *prm, st);
-	enqueue_compact(ctx, w, *prm, st);
-	enqueue_bottom(ctx, w, *prm, st);
+	if (ctx->split_device && n_reads >= 4096) {
+		// Two halves of the reads on two streams: the HBM-bound stages of one half (prep, compaction, chain ends / backtrack)
+		// run beside the issue-bound fill of the other.  Per-anchor arrays are shared (anchor indices are batch-wide), per-read
+		// arrays are offset views, each half has its own run list and counters; offsets, totals and the gather run once
+		// over all reads after the join.
+		const int64_t r1 = n_reads / 2;
+		Workspace h1 = w, h2 = w;
+		h1.half = 1; h1.n_reads = (int32_t)r1;
+		h2.half = 2; h2.n_reads = (int32_t)(n_reads - r1);
+		h2.offs = w.offs + r1; h2.avg = w.avg + r1; h2.new_i = w.new_i + r1; h2.n_u = w.n_u + r1; h2.n_v = w.n_v + r1;
+		h2.units = w.units + w.units_cap; h2.counters = w.counters + CNT_N;
+		CUDA_TRY(cudaMemsetAsync(w.visited, 0, 2 * sizeof(unsigned long long), st));
+		CUDA_TRY(cudaEventRecord(ctx->ev_fork, st));
+		CUDA_TRY(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+		const Workspace *hv[2] = { &h1, &h2 };
+		cudaStream_t sv[2] = { st, ctx->aux_stream };
+		for (int k = 0; k < 2; ++k) {
+			enqueue_fill(ctx, *hv[k], *prm, sv[k]);
+			enqueue_compact(ctx, *hv[k], *prm, sv[k]);
+			{ StageTimer t(ctx, sv[k], ST_TAIL); t.done(launch_tail_reads(*hv[k], *prm, sv[k])); }
+		}
+		CUDA_TRY(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
+		CUDA_TRY(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+		{ StageTimer t(ctx, st, ST_TAIL); t.done(launch_tail_scan(w, st)); }
+		{ StageTimer t(ctx, st, ST_GATHER); t.done(launch_gather(w, st)); }
+	} else {
+		enqueue_fill(ctx, w, *prm, st);
+		enqueue_compact(ctx, w, *prm, st);
+		enqueue_bottom(ctx, w, *prm, st);
+	}
 	CUDA_TRY(cudaGetLastError());
 	CUDA_TRY(cudaEventRecord(s.ev_user, st));
 	s.user_stream = st; s.user_pending = true;

@@ -28,7 +28,8 @@ struct Workspace {
 	float *avg;               // [n_reads] avg_qspan (chain.c:47)
 	Unit *units;              // [units_cap]: short runs from the front, long runs from the back
 	int32_t units_cap;
-	int32_t *counters;        // [CNT_N]
+	int32_t *counters;        // [2 * CNT_N]: the second set belongs to the second half of a split device batch
+	int32_t half;             // 0: a whole batch; 1 / 2: this view is the first / second half of a split device batch (mm2b200_chain_device)
 	unsigned long long *visited; // [2] reference-visited (i,j) pairs (chain.c:59-88 loop bodies); 32-lane chunks evaluated
 	// fill (chain.c:52-90)
 	int4 *wrec;               // [n_anchors] working record {low32(x), qpos, f, p}; p is a batch-wide index (or -1)
@@ -75,6 +76,8 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 int launch_compact(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
 int launch_split_records(const Workspace &w, cudaStream_t s);   // bottom_batch: rec[] uploaded by the host
 int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);
+int launch_tail_reads(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s);   // per-read part only
+int launch_tail_scan(const Workspace &w, cudaStream_t s);                                   // offsets + totals over all reads
 int launch_gather(const Workspace &w, cudaStream_t s);
 int launch_pack_records(const Workspace &w, cudaStream_t s);
 int launch_export_fp(const Workspace &w, cudaStream_t s);       // debug: wrec -> f[], p[] (per-read indices)

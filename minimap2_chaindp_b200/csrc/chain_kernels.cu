@@ -729,31 +729,40 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 			if (!done && addi_fma<-33>(i, one) >= jlo) {
 				// marks of chunk 0 that fell beyond it: tag word of the ring slot (or t[] for anchors that left the ring)
 				if (__any_sync(FULL, far)) { if (far) publish_mark<RING>(rj.w, i, ring_w, t); }
-				// chunks 1 .. RING/32-1 read the same ring; deeper ones the records flushed to global memory (L1/L2 hits)
-				unsigned ra = raddr;
-				int c = 1;
-				for (int jb = i - 33; !done && jb >= jlo; jb -= 32, ++c) {
+				// one chunk beyond the first: records and marks from the ring (chunks 1 .. RING/32-1) or from global memory
+				// (the records flushed there in 32-anchor blocks; L1/L2 hits)
+				auto deeper = [&](const bool in_ring, const unsigned ra, const int jb) -> int {
 					__syncwarp();                                     // marks published by the previous chunk are visible
-					const bool in_ring = c < RING / 32;
 					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo are masked (j >= jlo in the scan routines)
-					bool mg;
-					if (in_ring) {
-						ra = ring_w | (addi_fma<-512>(ra, one) & SM::mask);
-						rj = lds128<0>(ra);
-						mg = lds32<SM::comp + 4>(ra) == i;
-					} else { rj = wrec[jc]; mg = t[jc] == i; }
+					int4 rk; bool mg;
+					if (in_ring) { rk = lds128<0>(ra); mg = lds32<SM::comp + 4>(ra) == i; }
+					else { rk = wrec[jc]; mg = t[jc] == i; }
 					if (FULLV) ++n_chunks;
-					done = scan_chunk_sparse<TABLE, FULLV, WIDE, RING>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rj, mg,
+					int dn = scan_chunk_sparse<TABLE, FULLV, WIDE, RING>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rk, mg,
 					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg, ring_w);
-					if (done == 2) {                                  // many scored lanes: warp-wide replay
-						vj = in_ring ? lds32<SM::comp>(ra) : vg[jc];
-						dd0 = abs((int)(xi - (unsigned)rj.x) - (qi - rj.y));
-						cost = TABLE ? lds_u16(tab_w + min((unsigned)dd0, (unsigned)bw) * 2u) : lin_cost(dd0, avg) + ((31 - __clz(dd0 | 1)) >> 1);
-						done = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, far, jb, jlo, lane, rj, vj, mg,
-						                                     xi, qi, span, mdx, dr_max, dq_max, bw, dd0, cost, B0, max_skip, one);
-						if (!done && far) publish_mark<RING>(rj.w, i, ring_w, t);   // (the scalar path publishes its own)
+					if (dn == 2) {                                    // many scored lanes: warp-wide replay
+						const int vk = in_ring ? lds32<SM::comp>(ra) : vg[jc];
+						const int ddk = abs((int)(xi - (unsigned)rk.x) - (qi - rk.y));
+						const int ck = TABLE ? lds_u16(tab_w + min((unsigned)ddk, (unsigned)bw) * 2u) : lin_cost(ddk, avg) + ((31 - __clz(ddk | 1)) >> 1);
+						bool fk;
+						dn = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, fk, jb, jlo, lane, rk, vk, mg,
+						                                   xi, qi, span, mdx, dr_max, dq_max, bw, ddk, ck, B0, max_skip, one);
+						if (!dn && fk) publish_mark<RING>(rk.w, i, ring_w, t);   // (the scalar path publishes its own)
+					}
+					return dn;
+				};
+				unsigned ra = ring_w | (addi_fma<-512>(raddr, one) & SM::mask);
+				done = deeper(true, ra, i - 33);                      // chunk 1 is always in the ring
+				int jb = i - 65;
+				if (RING > 64) {
+#pragma unroll 1
+					for (int c = 2; c < RING / 32 && !done && jb >= jlo; ++c, jb -= 32) {
+						ra = ring_w | (addi_fma<-512>(ra, one) & SM::mask);
+						done = deeper(true, ra, jb);
 					}
 				}
+#pragma unroll 1
+				for (; !done && jb >= jlo; jb -= 32) done = deeper(false, 0u, jb);
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
 			sts128<0>(waddr, make_int4((int)xi, qi, max_f, max_j));
@@ -1281,7 +1290,8 @@ __global__ void __launch_bounds__(1024) k_scan_block_offsets(Workspace w, int n_
 	}
 	if (threadIdx.x == 0) {
 		w.u_off[w.n_reads] = s_carry[0]; w.b_off[w.n_reads] = s_carry[1]; w.rec_off[w.n_reads] = s_carry[2];
-		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS] + w.counters[CNT_LONG_UNITS]; w.totals[3] = s_carry[2];
+		w.totals[0] = s_carry[0]; w.totals[1] = s_carry[1]; w.totals[2] = w.counters[CNT_UNITS] + w.counters[CNT_LONG_UNITS] + w.counters[CNT_N + CNT_UNITS] + w.counters[CNT_N + CNT_LONG_UNITS];   // (+ second half, see chain_device)
+		w.totals[3] = s_carry[2];
 		w.totals[4] = (long long)w.visited[0]; w.totals[5] = (long long)w.visited[1];
 	}
 }
@@ -1481,8 +1491,10 @@ void query_launch_cfg(LaunchCfg *cfg)
 
 int launch_prep(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {
-	cudaMemsetAsync(w.counters, 0, CNT_N * sizeof(int32_t), s);
-	cudaMemsetAsync(w.visited, 0, 2 * sizeof(unsigned long long), s);
+	// a whole batch clears both counter sets; a half of a split device batch only its own (the halves run on two streams,
+	// and the caller clears visited[] before it forks)
+	cudaMemsetAsync(w.counters, 0, (w.half ? 1 : 2) * CNT_N * sizeof(int32_t), s);
+	if (!w.half) cudaMemsetAsync(w.visited, 0, 2 * sizeof(unsigned long long), s);
 	k_prep<<<blocks_for(w.n_reads, 8, 148 * 64), 256, 0, s>>>(w, prm.max_dist_x);
 	return 1;
 }
@@ -1519,6 +1531,16 @@ int launch_split_records(const Workspace &w, cudaStream_t s)
 	k_split_records<<<blocks_for(w.n_anchors > w.n_reads ? w.n_anchors : w.n_reads, 256 * 4, 148 * 16), 256, 0, s>>>(w);
 	return 1;
 }
+
+// the two halves of launch_tail, for callers that run the per-read part of several read ranges on different streams and
+// the scan over all reads once
+int launch_tail_reads(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
+{
+	k_tail_warp<<<blocks_for(w.n_reads, TW_WARPS, 148 * 16), TW_WARPS * 32, 0, s>>>(w, prm.min_cnt, prm.min_sc);
+	k_tail<<<blocks_for(w.n_reads, 1, 148 * 64), TAIL_T, 0, s>>>(w, prm.min_cnt, prm.min_sc, TW_CAP);
+	return 2;
+}
+int launch_tail_scan(const Workspace &w, cudaStream_t s) { return launch_scan_reads(w, 1, s); }
 
 int launch_tail(const Workspace &w, const mm2b200_params_t &prm, cudaStream_t s)
 {

@@ -40,6 +40,9 @@ int launch_tail(const Workspace &w, const mm2b200_params_t &, cudaStream_t)
 	return 1;
 }
 
+int launch_tail_reads(const Workspace &w, const mm2b200_params_t &p, cudaStream_t s) { return launch_tail(w, p, s); }
+int launch_tail_scan(const Workspace &, cudaStream_t) { return 1; }
+
 int launch_gather(const Workspace &w, cudaStream_t)
 {
 	for (int r = 0; r < w.n_reads; ++r)
