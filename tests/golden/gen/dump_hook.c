@@ -27,6 +27,10 @@ mm128_t *ref_real_bottom(int min_cnt, int min_sc, int n_segs, int *n_u_, uint64_
 
 static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
 
+/* seeding fixtures (make_seed_golden.sh): loopback_stub.c sets this to record the anchors collect_seed_hits (map.c:187)
+ * hands to the DP, in the order of the reads of the request packet it is working on */
+void (*golden_on_fpga_input)(int64_t n, const mm128_t *a) = 0;
+
 static FILE *dump_open(void)
 {
 	const char *path = getenv("MM2_GOLDEN_DUMP");
@@ -40,6 +44,7 @@ struct new_seed *mm_chain_dp_fpga(int max_dist_x, int max_dist_y, int bw, int ma
 	struct new_seed *rec;
 	FILE *fp;
 	if (n > 0) memcpy(copy, a, (size_t)n * sizeof(mm128_t));
+	if (golden_on_fpga_input) golden_on_fpga_input(n, a);
 	rec = ref_real_fpga(max_dist_x, max_dist_y, bw, max_skip, min_sc, is_cdna, n_segs, n, a, _new_i);   /* frees a */
 	pthread_mutex_lock(&mu);
 	if ((fp = dump_open()) != 0) {
