@@ -174,6 +174,16 @@ typedef struct {
 int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
                          const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_result_t *out);
 
+/* mm_chain_dp_fpga on anchors already resident in HBM: like mm2b200_chain_device, but stops after the compaction
+ * (chain.c:93-122).  d_rec[d_rec_off[r] .. d_rec_off[r+1]) are read r's new_seed records, d_totals[3] = their number. */
+typedef struct {
+	const int64_t *d_rec_off;        /* [n_reads+1] */
+	const struct new_seed *d_rec;
+	const int64_t *d_totals;         /* [8], as in mm2b200_dev_result_t */
+} mm2b200_dev_records_t;
+int mm2b200_fill_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
+                        const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_records_t *out);
+
 /* kernel launches issued by this context so far (bench.py's gpu_launches) */
 int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx);
 

@@ -34,7 +34,7 @@ EXPORTED_SYMBOLS = (
     "mm2b200_pinned_alloc", "mm2b200_pinned_free",
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
     "mm2b200_partition_reads", "mm2b200_chain_batch_multi",
-    "mm2b200_chain_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
+    "mm2b200_chain_device", "mm2b200_fill_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
     "mm2b200_set_upload", "mm2b200_upload_stats", "mm2b200_wire_encode", "mm2b200_version",
 )
 

@@ -38,8 +38,9 @@ def _stale(target: str, sources) -> bool:
 
 
 def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
-    srcs = [os.path.join(CSRC, f) for f in ("chain_kernels.cu", "chain_api.cu")]
-    deps = srcs + [os.path.join(CSRC, "chain_internal.h"), os.path.join(ROOT, "include", "mm2chain_b200.h")]
+    srcs = [os.path.join(CSRC, f) for f in ("chain_kernels.cu", "chain_api.cu", "seed_kernels.cu", "seed_api.cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("chain_internal.h", "seed_internal.h", "sort_exact.cuh")] + \
+        [os.path.join(ROOT, "include", f) for f in ("mm2chain_b200.h", "mm2seed_b200.h")]
     if force or _stale(LIB, deps):
         cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-o", LIB, *srcs, "-lpthread"]
         if verbose:

@@ -936,6 +936,47 @@ extern "C" int mm2b200_chain_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *
 	return MM2B200_OK;
 }
 
+// what seed_api.cu needs from a context without seeing its layout
+namespace mm2b200 {
+int api_fail(int code, const char *msg) { return fail(code, "%s", msg); }
+int ctx_device(const mm2b200_ctx *ctx) { return ctx->device; }
+int ctx_profile(const mm2b200_ctx *ctx) { return ctx->profile; }
+int ctx_sm_count(const mm2b200_ctx *ctx) { return ctx->lc.sm_count; }
+}
+
+extern "C" int mm2b200_fill_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
+                                   const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_records_t *out)
+{
+	int rc;
+	if (!ctx || !out) return fail(MM2B200_ERR_ARG, "NULL ctx or result");
+	if ((rc = check_params(prm))) return rc;
+	if (n_reads < 0 || n_anchors < 0 || !d_offs || (n_anchors && !d_a)) return fail(MM2B200_ERR_ARG, "bad device batch arguments");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	CUDA_TRY(cudaSetDevice(ctx->device));
+	Slot &s = ctx->slots[0];
+	if (s.state) return fail(MM2B200_ERR_STATE, "slot 0 busy");
+	cudaStream_t st = (cudaStream_t)stream;
+	if (s.user_pending && s.user_stream != st) { CUDA_TRY(cudaEventSynchronize(s.ev_user)); s.user_pending = false; }
+	if ((rc = ensure_slot(ctx, s, (size_t)n_anchors, (size_t)n_reads))) return rc;
+	if (s.cap_rec_out < s.cap_anchors || !s.d_rec_out) {
+		// the record buffer may still be read by the previous call on this stream
+		if (s.user_pending) { CUDA_TRY(cudaEventSynchronize(s.ev_user)); s.user_pending = false; }
+		if ((rc = ensure_rec_out(s))) return rc;
+	}
+	Workspace w = s.w;
+	w.a = (const ulonglong2*)d_a; w.offs = d_offs;
+	w.n_reads = (int32_t)n_reads; w.n_anchors = (int32_t)n_anchors;
+	w.rec_out = (new_seed*)s.d_rec_out;
+	enqueue_fill(ctx, w, *prm, st);
+	enqueue_compact(ctx, w, *prm, st);
+	{ StageTimer t(ctx, st, ST_GATHER); t.done(launch_pack_records(w, st)); }
+	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaEventRecord(s.ev_user, st));
+	s.user_stream = st; s.user_pending = true;
+	out->d_rec_off = w.rec_off; out->d_rec = w.rec_out; out->d_totals = w.totals;
+	return MM2B200_OK;
+}
+
 extern "C" int mm2b200_int_peak(mm2b200_ctx_t *ctx, int mode, double *lane_ops_per_s)
 {
 	if (!ctx || !lane_ops_per_s) return fail(MM2B200_ERR_ARG, "NULL argument");

@@ -12,6 +12,7 @@
 // round-to-nearest double multiplies in the reference's association order so the result is bit-identical.
 #include <cstdlib>
 #include "chain_internal.h"
+#include "sort_exact.cuh"
 
 namespace mm2b200 {
 
@@ -879,7 +880,6 @@ __global__ void __launch_bounds__(256) k_split_records(Workspace w)
 // k_tail: chain.c:127-214 for one read per CTA.
 // ---------------------------------------------------------------------------------------------------------
 #define TAIL_T 128
-#define RS_MIN 64   // RS_MIN_SIZE, ksort.h:98
 
 // ascending in-place sort of z[0..n) by the whole CTA ("flip" bitonic network: every compare-exchange is
 // ascending, so a virtual +inf padding beyond n never has to move)
@@ -898,60 +898,6 @@ static __device__ void cta_sort_u64(uint64_t *z, int n)
 				if (l > i && l < n) { const uint64_t x = z[i], y = z[l]; if (x > y) { z[i] = y; z[l] = x; } }
 			}
 			__syncthreads();
-		}
-	}
-}
-
-// rs_insertsort (ksort.h:105-115) on parallel arrays (key, payload)
-static __device__ void ins_sort_kv(uint64_t *kx, uint64_t *ky, int beg, int end)
-{
-	for (int i = beg + 1; i < end; ++i) {
-		if (kx[i] < kx[i - 1]) {
-			const uint64_t tx = kx[i], ty = ky[i];
-			int j = i;
-			for (; j > beg && tx < kx[j - 1]; --j) { kx[j] = kx[j - 1]; ky[j] = ky[j - 1]; }
-			kx[j] = tx; ky[j] = ty;
-		}
-	}
-}
-
-// radix_sort_128x (ksort.h:116-151, misc.c:136-137) replayed step for step by one thread so that the
-// (unstable) order of equal keys matches the reference.  Sub-buckets are independent, so the recursion is
-// replaced by an explicit stack of (beg, end, shift) in stk[].
-static __device__ void radix_sort_kv_exact(uint64_t *kx, uint64_t *ky, int n, int32_t *stk, int *head, int *tail)
-{
-	if (n <= RS_MIN) { ins_sort_kv(kx, ky, 0, n); return; }
-	int sp = 0;
-	stk[0] = 0; stk[1] = n; stk[2] = 56; sp = 3;
-	while (sp) {
-		sp -= 3;
-		const int beg = stk[sp], end = stk[sp + 1], shift = stk[sp + 2];
-		for (int k = 0; k < 256; ++k) head[k] = 0;
-		for (int i = beg; i < end; ++i) ++head[(kx[i] >> shift) & 0xff];
-		for (int k = 0, acc = beg; k < 256; ++k) { const int c = head[k]; head[k] = acc; acc += c; tail[k] = acc; }
-		for (int k = 0; k < 256;) {
-			if (head[k] != tail[k]) {
-				int l = (int)((kx[head[k]] >> shift) & 0xff);
-				if (l != k) {
-					uint64_t tx = kx[head[k]], ty = ky[head[k]];
-					do {
-						const uint64_t sx = tx, sy = ty;
-						tx = kx[head[l]]; ty = ky[head[l]];
-						kx[head[l]] = sx; ky[head[l]] = sy; ++head[l];
-						l = (int)((tx >> shift) & 0xff);
-					} while (l != k);
-					kx[head[k]] = tx; ky[head[k]] = ty; ++head[k];
-				} else ++head[k];
-			} else ++k;
-		}
-		if (shift) {
-			const int next = shift > 8 ? shift - 8 : 0;
-			for (int k = 0, st = beg; k < 256; ++k) {
-				const int en = tail[k], sz = en - st;
-				if (sz > RS_MIN) { stk[sp] = st; stk[sp + 1] = en; stk[sp + 2] = next; sp += 3; }
-				else if (sz > 1) ins_sort_kv(kx, ky, st, en);
-				st = en;
-			}
 		}
 	}
 }

@@ -1,0 +1,520 @@
+// seed_api.cu -- host side of the seeding stage (include/mm2seed_b200.h): the index streams in HBM, the batch calls that go
+// minimizers -> anchors -> chains without the anchors ever leaving the device, and the packet-level entry that speaks the
+// fork's request / response format (map.c:286-324, 484-575).
+//
+// No CPU fallback: every call needs the device the context was created on.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include <new>
+#include <string>
+#include <utility>
+#include <vector>
+#include "seed_internal.h"
+
+using namespace mm2b200;
+
+namespace {
+
+int failf(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
+int failf(int code, const char *fmt, ...)
+{
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	return api_fail(code, buf);
+}
+
+#define CU_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+	return failf(MM2B200_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
+
+struct DevBuf {
+	void *p = nullptr; size_t cap = 0;
+	int reserve(size_t bytes)
+	{
+		if (bytes <= cap && p) return MM2B200_OK;
+		size_t want = bytes + bytes / 4 + 4096;
+		if (p) { cudaFree(p); p = nullptr; cap = 0; }
+		if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaMalloc(%zu bytes) failed in the seeding stage", want); }
+		cap = want;
+		return MM2B200_OK;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct PinBuf {
+	void *p = nullptr; size_t cap = 0;
+	int reserve(size_t bytes)
+	{
+		if (bytes <= cap && p) return MM2B200_OK;
+		size_t want = bytes + bytes / 4 + 4096;
+		if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+		if (cudaHostAlloc(&p, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaHostAlloc(%zu bytes) failed in the seeding stage", want); }
+		cap = want;
+		return MM2B200_OK;
+	}
+	void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+	template <class T> T *as() { return (T*)p; }
+};
+
+// carves one device allocation into arrays
+struct Carver {
+	struct Item { void **pp; size_t bytes; };
+	std::vector<Item> items;
+	template <class T> void add(T **pp, size_t bytes) { items.push_back(Item{(void**)pp, bytes}); }
+	size_t total() const { size_t t = 0; for (auto &it : items) t += up256(it.bytes); return t; }
+	void place(void *base) { char *cur = (char*)base; for (auto &it : items) { *it.pp = cur; cur += up256(it.bytes); } }
+};
+
+} // namespace
+
+struct mm2b200_index {
+	mm2b200_ctx_t *ctx = nullptr;
+	int device = 0;
+	std::mutex mu;
+	// upload
+	std::vector<uint8_t> host[4];          // B, H, V, P chunks appended until commit
+	bool committed = false;
+	DevBuf d_stream[4];
+	DevIndex dix{};
+	int64_t resident_bytes = 0;
+	// per-batch state
+	cudaStream_t stream = nullptr;
+	DevBuf d_in, d_work, d_anchor;
+	PinBuf h_stage, h_totals, h_rep, h_mini_off, h_mini, h_a_off, h_a;
+	PinBuf h_n_u, h_u_off, h_b_off, h_u, h_b, h_rec_off, h_rec;
+	int64_t launches = 0;
+	cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
+	double ms[3] = { 0, 0, 0 };
+};
+
+extern "C" int mm2b200_index_create(mm2b200_ctx_t *ctx, mm2b200_index_t **out)
+{
+	if (!ctx || !out) return failf(MM2B200_ERR_ARG, "NULL ctx or index pointer");
+	*out = nullptr;
+	mm2b200_index *ix = new mm2b200_index();
+	ix->ctx = ctx;
+	ix->device = ctx_device(ctx);
+	cudaError_t e = cudaSetDevice(ix->device);
+	if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
+	for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreate(&ix->ev[k]);
+	if (e != cudaSuccess) {
+		int rc = failf(MM2B200_ERR_CUDA, "index_create: %s", cudaGetErrorString(e));
+		delete ix;
+		return rc;
+	}
+	*out = ix;
+	return MM2B200_OK;
+}
+
+extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
+{
+	if (!ix) return;
+	cudaSetDevice(ix->device);
+	if (ix->stream) cudaStreamSynchronize(ix->stream);
+	for (auto &b : ix->d_stream) b.release();
+	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release();
+	for (PinBuf *b : { &ix->h_stage, &ix->h_totals, &ix->h_rep, &ix->h_mini_off, &ix->h_mini, &ix->h_a_off, &ix->h_a,
+	                   &ix->h_n_u, &ix->h_u_off, &ix->h_b_off, &ix->h_u, &ix->h_b, &ix->h_rec_off, &ix->h_rec }) b->release();
+	for (auto &e : ix->ev) if (e) cudaEventDestroy(e);
+	if (ix->stream) cudaStreamDestroy(ix->stream);
+	delete ix;
+}
+
+extern "C" int mm2b200_index_load(mm2b200_index_t *ix, const void *addr, int64_t size, int type)
+{
+	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");
+	if (type < MM2B200_INDEX_B || type > MM2B200_INDEX_P) return failf(MM2B200_ERR_ARG, "index stream type %d is not one of B/H/V/P (4..7)", type);
+	if (size < 0 || (size > 0 && !addr)) return failf(MM2B200_ERR_ARG, "bad index chunk");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	if (ix->committed) {            // a new index replaces the old one
+		ix->committed = false;
+		for (auto &h : ix->host) h.clear();
+	}
+	std::vector<uint8_t> &h = ix->host[type - MM2B200_INDEX_B];
+	try { h.insert(h.end(), (const uint8_t*)addr, (const uint8_t*)addr + size); }
+	catch (const std::bad_alloc &) { return failf(MM2B200_ERR_NOMEM, "out of host memory while buffering an index stream"); }
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_index_commit(mm2b200_index_t *ix)
+{
+	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	const size_t nB = ix->host[0].size(), nH = ix->host[1].size(), nV = ix->host[2].size(), nP = ix->host[3].size();
+	int b = 0;
+	while (((size_t)16 << b) < nB && b < 40) ++b;
+	if (nB < 16 || ((size_t)16 << b) != nB) return failf(MM2B200_ERR_ARG, "B stream of %zu bytes is not 16 bytes x a power of two of buckets", nB);
+	if (nH % 64 || nV % 8 || nP % 8 || nV / 8 != nH / 64 * 8)
+		return failf(MM2B200_ERR_ARG, "index streams disagree: H %zu bytes (64 per 8 slots), V %zu bytes (8 per slot), P %zu bytes", nH, nV, nP);
+	CU_TRY(cudaSetDevice(ix->device));
+	CU_TRY(cudaStreamSynchronize(ix->stream));
+	ix->resident_bytes = 0;
+	for (int k = 0; k < 4; ++k) {
+		const size_t n = ix->host[k].size();
+		int rc = ix->d_stream[k].reserve(n ? n : 256);
+		if (rc) return rc;
+		if (n) CU_TRY(cudaMemcpy(ix->d_stream[k].p, ix->host[k].data(), n, cudaMemcpyHostToDevice));
+		ix->resident_bytes += (int64_t)n;
+		std::vector<uint8_t>().swap(ix->host[k]);
+	}
+	ix->dix.B = (const uint4*)ix->d_stream[0].p;
+	ix->dix.H = (const uint8_t*)ix->d_stream[1].p;
+	ix->dix.V = (const uint64_t*)ix->d_stream[2].p;
+	ix->dix.P = (const uint64_t*)ix->d_stream[3].p;
+	ix->dix.b = b;
+	ix->dix.n_slots = (int64_t)(nV / 8);
+	ix->dix.n_pos = (int64_t)(nP / 8);
+	ix->committed = true;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_index_info(const mm2b200_index_t *ix, int32_t *b, int64_t *bytes)
+{
+	if (!ix || !ix->committed) return failf(MM2B200_ERR_STATE, "index not committed");
+	if (b) *b = ix->dix.b;
+	if (bytes) *bytes = ix->resident_bytes;
+	return MM2B200_OK;
+}
+
+extern "C" int64_t mm2b200_seed_launch_count(const mm2b200_index_t *ix) { return ix ? ix->launches : 0; }
+
+extern "C" int mm2b200_seed_stage_ms(mm2b200_index_t *ix, double *lookup_ms, double *expand_ms, double *sort_ms)
+{
+	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");
+	if (lookup_ms) *lookup_ms = ix->ms[0];
+	if (expand_ms) *expand_ms = ix->ms[1];
+	if (sort_ms) *sort_ms = ix->ms[2];
+	return MM2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// minimizers -> sorted anchors in HBM
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+struct SeedOut {
+	SeedWork w{};
+	int64_t n_anchors = 0, n_mini = 0, n_exact = 0;
+};
+
+int check_seed_args(const mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off, const mm128_t *mv,
+                    const uint32_t *bid, const int32_t *qlen)
+{
+	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");
+	if (!ix->committed) return failf(MM2B200_ERR_STATE, "index not committed (mm2b200_index_commit)");
+	if (!prm) return failf(MM2B200_ERR_ARG, "params is NULL");
+	if (n_reads < 0 || n_reads >= ((int64_t)1 << 31) - 1) return failf(MM2B200_ERR_ARG, "bad number of reads");
+	if (n_reads && (!mv_off || !bid || !qlen)) return failf(MM2B200_ERR_ARG, "NULL per-read array");
+	for (int64_t r = 0; r < n_reads; ++r)
+		if (mv_off[r + 1] < mv_off[r]) return failf(MM2B200_ERR_ARG, "mv_off is not non-decreasing at read %lld", (long long)r);
+	if (n_reads && mv_off[n_reads] > mv_off[0] && !mv) return failf(MM2B200_ERR_ARG, "NULL minimizer array");
+	return MM2B200_OK;
+}
+
+// uploads the batch, runs lookup -> (sync for the anchor count) -> expand -> sort on ix->stream.  On return the sorted
+// anchors and their offsets are in HBM (out.w.a, out.w.a_off) and the stream holds the remaining work.
+int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off, const mm128_t *mv,
+               const uint32_t *bid, const int32_t *qlen, SeedOut &out)
+{
+	int rc;
+	CU_TRY(cudaSetDevice(ix->device));
+	cudaStream_t st = ix->stream;
+	const int64_t m_base = n_reads ? mv_off[0] : 0;
+	const int64_t n_mv = n_reads ? mv_off[n_reads] - m_base : 0;
+	const size_t R = (size_t)n_reads, M = (size_t)n_mv;
+	SeedWork &w = out.w;
+	// inputs
+	ulonglong2 *d_mv; int64_t *d_mv_off; uint32_t *d_bid; int32_t *d_qlen;
+	{
+		Carver c;
+		c.add(&d_mv, 16 * (M + 1)); c.add(&d_mv_off, 8 * (R + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
+		if ((rc = ix->d_in.reserve(c.total()))) return rc;
+		c.place(ix->d_in.p);
+	}
+	{
+		Carver c;
+		c.add(&w.src, 8 * (M + 1)); c.add(&w.cnt, 4 * (M + 1)); c.add(&w.aofs, 4 * (M + 1)); c.add(&w.mread, 4 * (M + 1));
+		c.add(&w.mini_sparse, 8 * (M + 1)); c.add(&w.mini_out, 8 * (M + 1));
+		c.add(&w.n_a, 4 * (R + 1)); c.add(&w.n_mini, 4 * (R + 1)); c.add(&w.rep_len, 4 * (R + 1));
+		c.add(&w.a_off, 8 * (R + 1)); c.add(&w.mini_off, 8 * (R + 1)); c.add(&w.totals, 8 * ST_TOTALS);
+		if ((rc = ix->d_work.reserve(c.total()))) return rc;
+		c.place(ix->d_work.p);
+	}
+	// offsets relative to the first minimizer of the batch, staged in pinned memory together with bid / qlen
+	if ((rc = ix->h_stage.reserve(8 * (R + 1) + 8 * (R + 1)))) return rc;
+	int64_t *h_off = ix->h_stage.as<int64_t>();
+	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? mv_off[r] - m_base : 0;
+	CU_TRY(cudaMemcpyAsync(d_mv_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	if (R) {
+		CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
+		CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
+	}
+	if (M) CU_TRY(cudaMemcpyAsync(d_mv, mv + m_base, 16 * M, cudaMemcpyHostToDevice, st));
+	w.mv = d_mv; w.mv_off = d_mv_off; w.bid = d_bid; w.qlen = d_qlen;
+	w.n_reads = (int32_t)n_reads; w.n_mv = n_mv;
+	w.flag = prm->flag; w.max_occ = prm->max_occ;
+	const bool prof = ctx_profile(ix->ctx) != 0;
+	if (prof) CU_TRY(cudaEventRecord(ix->ev[0], st));
+	ix->launches += launch_seed_lookup(ix->dix, w, ctx_sm_count(ix->ctx), st);
+	if (prof) CU_TRY(cudaEventRecord(ix->ev[1], st));
+	if ((rc = ix->h_totals.reserve(8 * ST_TOTALS * 2))) return rc;
+	int64_t *tot = ix->h_totals.as<int64_t>();
+	CU_TRY(cudaMemcpyAsync(tot, w.totals, 8 * ST_TOTALS, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	CU_TRY(cudaGetLastError());
+	if (tot[ST_ERROR] & SE_INDEX_RANGE) return failf(MM2B200_ERR_ARG, "index streams are inconsistent: a bucket or position list points outside H/V/P");
+	if (tot[ST_ERROR] & SE_READ_TOO_LONG)
+		return failf(MM2B200_ERR_ARG, "a read has %lld anchors; the seeding stage numbers a read's anchors in %d bits", (long long)tot[ST_MAX_READ], SEED_IDX_BITS);
+	const int64_t A = tot[ST_ANCHORS];
+	if (A >= ((int64_t)1 << 31) - 64) return failf(MM2B200_ERR_ARG, "batch yields %lld anchors: beyond the 2^31 index space of one sub-batch, send fewer reads per call", (long long)A);
+	out.n_anchors = A; out.n_mini = tot[ST_MINI];
+	{
+		Carver c;
+		const size_t a = (size_t)A + 1;
+		c.add(&w.a_un, 16 * a); c.add(&w.a, 16 * a); c.add(&w.key, 8 * a); c.add(&w.ky, 8 * a); c.add(&w.stk, 4 * a + 64);
+		if ((rc = ix->d_anchor.reserve(c.total()))) return rc;
+		c.place(ix->d_anchor.p);
+	}
+	if (A) {
+		ix->launches += launch_seed_expand(ix->dix, w, st);
+		if (prof) CU_TRY(cudaEventRecord(ix->ev[2], st));
+		ix->launches += launch_seed_sort(w, st);
+		if (prof) CU_TRY(cudaEventRecord(ix->ev[3], st));
+	}
+	CU_TRY(cudaGetLastError());
+	// what the host always gets from this stage: rep_len, mini_pos, anchor offsets
+	if ((rc = ix->h_rep.reserve(4 * (R + 1))) || (rc = ix->h_mini_off.reserve(8 * (R + 1))) || (rc = ix->h_a_off.reserve(8 * (R + 1))) ||
+	    (rc = ix->h_mini.reserve(8 * ((size_t)out.n_mini + 1)))) return rc;
+	if (R) CU_TRY(cudaMemcpyAsync(ix->h_rep.p, w.rep_len, 4 * R, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_mini_off.p, w.mini_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_a_off.p, w.a_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	if (out.n_mini) CU_TRY(cudaMemcpyAsync(ix->h_mini.p, w.mini_out, 8 * (size_t)out.n_mini, cudaMemcpyDeviceToHost, st));
+	return MM2B200_OK;
+}
+
+// after the stream has been synchronised: stage times and the exact-sort counter
+int seed_finish(mm2b200_index *ix, SeedOut &out)
+{
+	if (ctx_profile(ix->ctx)) {
+		float t = 0;
+		if (cudaEventElapsedTime(&t, ix->ev[0], ix->ev[1]) == cudaSuccess) ix->ms[0] += t;
+		if (out.n_anchors) {
+			if (cudaEventElapsedTime(&t, ix->ev[1], ix->ev[2]) == cudaSuccess) ix->ms[1] += t;   // includes the host's wait for the count
+			if (cudaEventElapsedTime(&t, ix->ev[2], ix->ev[3]) == cudaSuccess) ix->ms[2] += t;
+		}
+		cudaGetLastError();
+	}
+	return MM2B200_OK;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------
+// batch calls
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int mm2b200_seed_chain_batch(mm2b200_index_t *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off,
+                                        const mm128_t *mv, const uint32_t *bid, const int32_t *qlen, int want_anchors,
+                                        mm2b200_seed_result_t *res)
+{
+	int rc;
+	if (!res) return failf(MM2B200_ERR_ARG, "NULL result");
+	if ((rc = check_seed_args(ix, prm, n_reads, mv_off, mv, bid, qlen))) return rc;
+	std::lock_guard<std::mutex> lk(ix->mu);
+	memset(res, 0, sizeof(*res));
+	SeedOut so;
+	if ((rc = seed_stage(ix, prm, n_reads, mv_off, mv, bid, qlen, so))) return rc;
+	cudaStream_t st = ix->stream;
+	const size_t R = (size_t)n_reads, A = (size_t)so.n_anchors;
+	if (want_anchors) {
+		if ((rc = ix->h_a.reserve(16 * (A + 1)))) return rc;
+		if (A) CU_TRY(cudaMemcpyAsync(ix->h_a.p, so.w.a, 16 * A, cudaMemcpyDeviceToHost, st));
+	}
+	// the chaining DP reads the anchors where the sort left them
+	mm2b200_dev_result_t dev;
+	if ((rc = mm2b200_chain_device(ix->ctx, &prm->chain, n_reads, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
+	int64_t *tot = ix->h_totals.as<int64_t>() + ST_TOTALS;
+	CU_TRY(cudaMemcpyAsync(tot, dev.d_totals, 64, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_totals.p, so.w.totals, 8 * ST_TOTALS, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	const size_t tu = (size_t)tot[0], tb = (size_t)tot[1];
+	if ((rc = ix->h_n_u.reserve(4 * (R + 1))) || (rc = ix->h_u_off.reserve(8 * (R + 1))) || (rc = ix->h_b_off.reserve(8 * (R + 1))) ||
+	    (rc = ix->h_u.reserve(8 * (tu + 1))) || (rc = ix->h_b.reserve(16 * (tb + 1)))) return rc;
+	if (R) CU_TRY(cudaMemcpyAsync(ix->h_n_u.p, dev.d_n_u, 4 * R, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_u_off.p, dev.d_u_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_b_off.p, dev.d_b_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	if (tu) CU_TRY(cudaMemcpyAsync(ix->h_u.p, dev.d_u, 8 * tu, cudaMemcpyDeviceToHost, st));
+	if (tb) CU_TRY(cudaMemcpyAsync(ix->h_b.p, dev.d_b, 16 * tb, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	seed_finish(ix, so);
+	res->chains.n_reads = n_reads;
+	res->chains.n_u = ix->h_n_u.as<int32_t>(); res->chains.u_off = ix->h_u_off.as<int64_t>(); res->chains.b_off = ix->h_b_off.as<int64_t>();
+	res->chains.u = ix->h_u.as<uint64_t>(); res->chains.b = ix->h_b.as<mm128_t>();
+	res->chains.n_units = tot[2]; res->chains.n_sub_batches = 1; res->chains.n_visited = tot[4]; res->chains.n_lanes = 32 * tot[5];
+	res->n_anchors = so.n_anchors;
+	res->rep_len = ix->h_rep.as<int32_t>(); res->mini_off = ix->h_mini_off.as<int64_t>(); res->mini_pos = ix->h_mini.as<uint64_t>();
+	res->a_off = ix->h_a_off.as<int64_t>(); res->a = want_anchors ? ix->h_a.as<mm128_t>() : nullptr;
+	res->n_exact_sorts = ix->h_totals.as<int64_t>()[ST_EXACT];
+	return MM2B200_OK;
+}
+
+namespace {
+// seeding + fill + compaction; records land in ix->h_rec / h_rec_off.  Caller holds ix->mu.
+int seed_fill_locked(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off, const mm128_t *mv,
+                     const uint32_t *bid, const int32_t *qlen, mm2b200_seed_records_t *res)
+{
+	int rc;
+	SeedOut so;
+	if ((rc = seed_stage(ix, prm, n_reads, mv_off, mv, bid, qlen, so))) return rc;
+	cudaStream_t st = ix->stream;
+	const size_t R = (size_t)n_reads;
+	mm2b200_dev_records_t dev;
+	if ((rc = mm2b200_fill_device(ix->ctx, &prm->chain, n_reads, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
+	int64_t *tot = ix->h_totals.as<int64_t>() + ST_TOTALS;
+	CU_TRY(cudaMemcpyAsync(tot, dev.d_totals, 64, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	const size_t tr = (size_t)tot[3];
+	if ((rc = ix->h_rec_off.reserve(8 * (R + 1))) || (rc = ix->h_rec.reserve(24 * (tr + 1)))) return rc;
+	CU_TRY(cudaMemcpyAsync(ix->h_rec_off.p, dev.d_rec_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	if (tr) CU_TRY(cudaMemcpyAsync(ix->h_rec.p, dev.d_rec, 24 * tr, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	seed_finish(ix, so);
+	ix->h_rec_off.as<int64_t>()[R] = (int64_t)tr;
+	res->n_anchors = so.n_anchors;
+	res->rec_off = ix->h_rec_off.as<int64_t>(); res->rec = (const struct new_seed*)ix->h_rec.p;
+	res->rep_len = ix->h_rep.as<int32_t>(); res->mini_off = ix->h_mini_off.as<int64_t>(); res->mini_pos = ix->h_mini.as<uint64_t>();
+	return MM2B200_OK;
+}
+} // namespace
+
+extern "C" int mm2b200_seed_fill_batch(mm2b200_index_t *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off,
+                                       const mm128_t *mv, const uint32_t *bid, const int32_t *qlen, mm2b200_seed_records_t *res)
+{
+	int rc;
+	if (!res) return failf(MM2B200_ERR_ARG, "NULL result");
+	if ((rc = check_seed_args(ix, prm, n_reads, mv_off, mv, bid, qlen))) return rc;
+	std::lock_guard<std::mutex> lk(ix->mu);
+	memset(res, 0, sizeof(*res));
+	return seed_fill_locked(ix, prm, n_reads, mv_off, mv, bid, qlen, res);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// packet level: the fork's wire format
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+// fpga_chaindp.h:79-87
+struct __attribute__((__packed__)) PktHead { uint32_t magic, size; uint16_t tid, num; uint8_t type, lat; uint8_t reserve1[50]; };
+// fpga_chaindp.h:46-58
+struct __attribute__((__packed__)) PktTask { int32_t gap_qry, gap_ref, seednum, qlensum; uint32_t read_id, bid; int16_t n_segs; char b; char reserve1[1]; uint64_t mv_a; char reserve2[28]; };
+// fpga_chaindp.h:60-68
+struct __attribute__((__packed__)) PktResult { uint32_t err_flag, read_id, sub_size, n_a, n_minipos, rep_len; char reserve1[40]; };
+static_assert(sizeof(PktHead) == 64 && sizeof(PktTask) == 64 && sizeof(PktResult) == 64, "packet headers are 64 bytes");
+inline int64_t up64(int64_t x) { return (x + 63) & ~(int64_t)63; }
+}
+
+extern "C" int mm2b200_seed_work(mm2b200_index_t *ix, const mm2b200_seed_params_t *prm, const void *req, int64_t req_size,
+                                 void *resp, int64_t resp_cap, int64_t *resp_size)
+{
+	int rc;
+	if (!ix || !prm || !req || !resp || !resp_size) return failf(MM2B200_ERR_ARG, "NULL argument");
+	if (!ix->committed) return failf(MM2B200_ERR_STATE, "index not committed (mm2b200_index_commit)");
+	if (req_size < (int64_t)sizeof(PktHead)) return failf(MM2B200_ERR_ARG, "request packet shorter than its header");
+	const char *p = (const char*)req, *end = p + req_size;
+	PktHead head;
+	memcpy(&head, p, sizeof(head));
+	if (head.type != 3) return failf(MM2B200_ERR_ARG, "request packet type %d, expected 3 (map.c:491)", head.type);
+	const int num = head.num;
+	// walk the tasks (map.c:505-567)
+	std::vector<PktTask> tasks((size_t)num);
+	std::vector<const char*> mvp((size_t)num);
+	p += sizeof(PktHead);
+	int64_t n_mv = 0;
+	for (int i = 0; i < num; ++i) {
+		if (p + sizeof(PktTask) > end) return failf(MM2B200_ERR_ARG, "request packet truncated at task %d", i);
+		memcpy(&tasks[i], p, sizeof(PktTask));
+		if (tasks[i].seednum < 0) return failf(MM2B200_ERR_ARG, "task %d has a negative minimizer count", i);
+		mvp[i] = p + sizeof(PktTask);
+		const int64_t body = up64((int64_t)tasks[i].seednum * 16);
+		if (mvp[i] + body > end && mvp[i] + (int64_t)tasks[i].seednum * 16 > end) return failf(MM2B200_ERR_ARG, "request packet truncated inside task %d", i);
+		n_mv += tasks[i].seednum;
+		p = mvp[i] + body;
+	}
+	std::lock_guard<std::mutex> lk(ix->mu);
+	// reads grouped by (gap_ref, gap_qry): one device batch per group (one group in practice, map.c:358-366)
+	std::vector<int> order((size_t)num), group_of((size_t)num, -1);
+	std::vector<std::pair<int32_t, int32_t>> groups;
+	for (int i = 0; i < num; ++i) {
+		const int32_t g_ref = tasks[i].gap_ref, g_qry = tasks[i].gap_qry;
+		const std::pair<int32_t, int32_t> key(g_ref, g_qry);
+		size_t g = 0;
+		while (g < groups.size() && groups[g] != key) ++g;
+		if (g == groups.size()) groups.push_back(key);
+		group_of[i] = (int)g;
+	}
+	struct ReadOut { std::vector<new_seed> rec; std::vector<uint64_t> mini; int32_t rep_len = 0; };
+	std::vector<ReadOut> outs((size_t)num);
+	std::vector<mm128_t> mv;
+	std::vector<int64_t> off;
+	std::vector<uint32_t> bid;
+	std::vector<int32_t> qlen;
+	std::vector<int> members;
+	for (size_t g = 0; g < groups.size(); ++g) {
+		mv.clear(); off.assign(1, 0); bid.clear(); qlen.clear(); members.clear();
+		for (int i = 0; i < num; ++i) {
+			if (group_of[i] != (int)g) continue;
+			members.push_back(i);
+			const size_t at = mv.size();
+			mv.resize(at + (size_t)tasks[i].seednum);
+			if (tasks[i].seednum) memcpy(mv.data() + at, mvp[i], (size_t)tasks[i].seednum * 16);
+			off.push_back((int64_t)mv.size());
+			bid.push_back((uint32_t)tasks[i].bid); qlen.push_back((int32_t)tasks[i].qlensum);
+		}
+		mm2b200_seed_params_t q = *prm;
+		q.chain.max_dist_x = groups[g].first;     // max_chain_gap_ref, map.c:515
+		q.chain.max_dist_y = groups[g].second;    // max_chain_gap_qry, map.c:516
+		q.chain.n_segs = groups[g].second;        // map.c:517 reads n_segs from gap_qry
+		mm2b200_seed_records_t rr;
+		memset(&rr, 0, sizeof(rr));
+		if ((rc = seed_fill_locked(ix, &q, (int64_t)members.size(), off.data(), mv.data(), bid.data(), qlen.data(), &rr))) return rc;
+		for (size_t k = 0; k < members.size(); ++k) {
+			ReadOut &o = outs[(size_t)members[k]];
+			o.rec.assign(rr.rec + rr.rec_off[k], rr.rec + rr.rec_off[k + 1]);
+			o.mini.assign(rr.mini_pos + rr.mini_off[k], rr.mini_pos + rr.mini_off[k + 1]);
+			o.rep_len = rr.rep_len[k];
+		}
+	}
+	// response packet (map.c:495-501, 533-565); padding bytes are zero here (the reference leaves them uninitialised)
+	int64_t need = sizeof(PktHead);
+	for (int i = 0; i < num; ++i) need += (int64_t)sizeof(PktResult) + up64((int64_t)outs[i].rec.size() * 24) + up64((int64_t)outs[i].mini.size() * 8);
+	if (need > resp_cap) return failf(MM2B200_ERR_ARG, "response needs %lld bytes, buffer holds %lld", (long long)need, (long long)resp_cap);
+	memset(resp, 0, (size_t)need);
+	char *o = (char*)resp;
+	PktHead oh;
+	memset(&oh, 0, sizeof(oh));
+	oh.magic = head.magic; oh.tid = head.tid; oh.num = head.num; oh.type = head.type; oh.lat = head.lat; oh.size = (uint32_t)need;
+	memcpy(o, &oh, sizeof(oh));
+	o += sizeof(oh);
+	for (int i = 0; i < num; ++i) {
+		const ReadOut &ro = outs[(size_t)i];
+		const int64_t rec_b = up64((int64_t)ro.rec.size() * 24), mini_b = up64((int64_t)ro.mini.size() * 8);
+		PktResult pr;
+		memset(&pr, 0, sizeof(pr));
+		pr.err_flag = 0; pr.read_id = tasks[i].read_id; pr.n_a = (uint32_t)ro.rec.size(); pr.n_minipos = (uint32_t)ro.mini.size();
+		pr.rep_len = (uint32_t)ro.rep_len; pr.sub_size = (uint32_t)(sizeof(PktResult) + rec_b + mini_b);
+		memcpy(o, &pr, sizeof(pr));
+		o += sizeof(pr);
+		if (!ro.rec.empty()) memcpy(o, ro.rec.data(), ro.rec.size() * 24);
+		o += rec_b;
+		if (!ro.mini.empty()) memcpy(o, ro.mini.data(), ro.mini.size() * 8);
+		o += mini_b;
+	}
+	*resp_size = need;
+	return MM2B200_OK;
+}

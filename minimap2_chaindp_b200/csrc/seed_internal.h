@@ -1,0 +1,65 @@
+// seed_internal.h -- shared between the seeding kernels (seed_kernels.cu) and their host side (seed_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "mm2seed_b200.h"
+
+namespace mm2b200 {
+
+// The four index streams of the fork (index.c:603-720) as they lie in HBM.  Nothing is re-encoded: the probe reads the
+// same bytes the fork's device would.
+struct DevIndex {
+	const uint4 *B;        // [2^b] {B[0] lo, B[0] hi, B[1] lo, B[1] hi}
+	const uint8_t *H;      // 64 B per group of 8 slots
+	const uint64_t *V;     // [n_slots]
+	const uint64_t *P;     // [n_pos]
+	int32_t b;
+	int64_t n_slots, n_pos;
+};
+
+enum SeedTotal { ST_ANCHORS = 0, ST_MINI = 1, ST_ERROR = 2, ST_EXACT = 3, ST_MAX_READ = 4, ST_TOTALS = 8 };
+enum SeedError { SE_INDEX_RANGE = 1, SE_READ_TOO_LONG = 2 };
+
+#define SEED_IDX_BITS 21                       // anchors of one read are numbered in 21 bits inside the sort key
+#define SEED_MAX_READ_ANCHORS (1 << SEED_IDX_BITS)
+
+struct SeedWork {
+	// inputs (device copies)
+	const ulonglong2 *mv;   // [n_mv] minimizers {x = hash<<8 | span, y = seg<<32 | pos<<1 | strand}
+	const int64_t *mv_off;  // [n_reads+1]
+	const uint32_t *bid;    // [n_reads]
+	const int32_t *qlen;    // [n_reads]
+	int32_t n_reads;
+	int64_t n_mv;
+	int32_t flag, max_occ;
+	// per minimizer (written by the lookup)
+	uint64_t *src;          // the one position (single-occurrence key) or the index of the first position in P
+	int32_t *cnt;           // occurrences to expand (0: absent or repetitive) | 1<<30 single | 1<<31 tandem
+	int32_t *aofs;          // offset of the minimizer's first anchor within its read
+	int32_t *mread;         // owning read
+	uint64_t *mini_sparse;  // mini_pos of read r at mv_off[r] ..
+	// per read
+	int32_t *n_a, *n_mini, *rep_len;
+	int64_t *a_off, *mini_off;     // [n_reads+1]
+	uint64_t *mini_out;     // [n_mv] packed
+	int64_t *totals;        // [ST_TOTALS]
+	// per anchor (allocated once the count is known)
+	ulonglong2 *a_un;       // collection order (map.c:200-229)
+	ulonglong2 *a;          // sorted (map.c:233)
+	uint64_t *key;          // sort keys: order-preserving 43-bit image of x, then the anchor's number within the read
+	uint64_t *ky;           // payload copy for the exact replay
+	int32_t *stk;           // explicit stack of the exact replay
+};
+
+// from chain_api.cu
+int api_fail(int code, const char *msg);       // records the thread's last error, returns code
+int ctx_device(const mm2b200_ctx *ctx);
+int ctx_profile(const mm2b200_ctx *ctx);
+int ctx_sm_count(const mm2b200_ctx *ctx);
+
+// launchers; each returns the number of kernels it enqueued
+int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cudaStream_t s);   // + scans over reads, totals, mini_pos packing
+int launch_seed_expand(const DevIndex &ix, const SeedWork &w, cudaStream_t s);
+int launch_seed_sort(const SeedWork &w, cudaStream_t s);
+
+} // namespace mm2b200

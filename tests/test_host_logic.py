@@ -11,8 +11,8 @@ from minimap2_chaindp_b200 import api, shard, workload
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared_symbols():
-    src = open(os.path.join(ROOT, "include", "mm2chain_b200.h")).read()
+def _declared_symbols(header="mm2chain_b200.h"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(mm2b200_[a-z0-9_]+|mm_chain_dp[a-z_]*)\s*\(", src)))
 
@@ -25,6 +25,31 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(L, n), f"{n} declared in include/mm2chain_b200.h but not exported"
     assert sorted(api.EXPORTED_SYMBOLS) == names
     assert b"sm_100a" in L.mm2b200_version()
+
+
+def test_library_exports_every_seeding_symbol():
+    from minimap2_chaindp_b200 import seed
+    names = _declared_symbols("mm2seed_b200.h")
+    assert len(names) >= 10 and "mm2b200_index_load" in names and "mm2b200_seed_work" in names
+    L = api.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mm2seed_b200.h but not exported"
+    assert sorted(seed.EXPORTED_SYMBOLS) == names
+    import ctypes as C
+    assert C.sizeof(seed.SeedParams) == 44
+
+
+def test_index_streams_are_validated_without_a_gpu():
+    """size checks of mm2b200_index_commit come before any device work; without a context nothing can be created"""
+    import torch
+    from minimap2_chaindp_b200 import seed
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    L = seed._lib()
+    import ctypes as C
+    h = C.c_void_p()
+    assert L.mm2b200_index_create(None, C.byref(h)) == api.ERR_ARG
+    assert L.mm2b200_index_load(None, None, 0, 4) == api.ERR_ARG
 
 
 def test_struct_layouts_match_the_reference():
