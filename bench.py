@@ -625,12 +625,113 @@ class Bench:
                 bad = [k for k, v in block.items() if v["parity_with_reference"] and not v["parity_with_reference"]["ok"]]
                 if bad:
                     line["parity_error"] = f"GPU chains differ from the reference on {bad}"
+        if rank == 0 and world == 1 and args.seeded_reads > 0 and args.workload == "map-ont-100k":
+            line["seeded"] = self.run_seeded(args.seeded_reads, max(1, min(steps, 3)))
+            if not line["seeded"]["parity_with_oracle"]["ok"]:
+                line["parity_error"] = "seeded path differs from the oracle"
         if rank == 0:
             print(json.dumps(line))
         if world > 1:
             self.dist.barrier()
             self.dist.destroy_process_group()
         return 0
+
+    # ---- seeding on the device: minimizers in, chains out, anchors never on the host
+    def run_seeded(self, n_reads, steps):
+        """One GPU, rank 0: mm2b200_seed_chain_batch on a G-idx workload (synthetic index streams far larger than L2 + reads
+        given as minimizers), with the oracle's collect_seed_hits timed beside it on a bounded sample and parity on a sample."""
+        from concurrent.futures import ThreadPoolExecutor
+        from minimap2_chaindp_b200 import seed as mseed
+        api, workload, torch = self.api, self.workload, self.torch
+        spec = workload.SEED_CONFIGS["map-ont-100k-seeded"]
+        t0 = time.perf_counter()
+        W = workload.SeedWorkload(spec)
+        build_s = time.perf_counter() - t0
+        ctx = api.ChainContext(device=self.local, profile=True)
+        ix = mseed.SeedIndex(ctx).load_streams(W.B, W.H, W.V, W.P)
+        # sizes first, then the minimizers straight into pinned memory
+        off0 = np.zeros(n_reads + 1, np.int64)
+        ql = np.zeros(n_reads, np.int32)
+        bd = np.zeros(n_reads, np.uint32)
+        m = workload.lib().wls_reads_count(W._h, C.byref(W._rs), 0, n_reads, off0.ctypes.data, ql.ctypes.data, bd.ctypes.data)
+        pin = api.PinnedArray((int(m), 2), np.uint64)
+        workload.lib().wls_reads_fill(W._h, C.byref(W._rs), 0, n_reads, off0.ctypes.data, pin.array.ctypes.data)
+        prm = mseed.seed_params(api.params(spec.preset), spec.flag, spec.max_occ)
+        L = mseed._lib()
+        res = mseed._SeedResult()
+
+        def call(want_anchors=0):
+            rc = L.mm2b200_seed_chain_batch(ix._h, C.byref(prm), n_reads, off0.ctypes.data, pin.array.ctypes.data, bd.ctypes.data,
+                                            ql.ctypes.data, want_anchors, C.byref(res))
+            if rc:
+                raise api.ChainError(rc, api.last_error())
+        call()                                   # warm-up: allocations, first touch
+        call()
+        ctx.stage_reset()
+        ms0 = ix.stage_ms()
+        l0 = ix.launch_count() + ctx.launch_count()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            call()
+        dt = (time.perf_counter() - t0) / steps
+        ms1 = ix.stage_ms()
+        n_anchors = int(res.n_anchors)
+        n_chains = int(np.frombuffer((C.c_char * 8).from_address(res.chains.u_off + 8 * n_reads), np.int64)[0])
+        n_b = int(np.frombuffer((C.c_char * 8).from_address(res.chains.b_off + 8 * n_reads), np.int64)[0])
+        stage = {k: (ms1[k] - ms0[k]) / steps for k in ms1}
+        stage.update({k: ctx.stage_ms(k)[0] / steps for k in ("prep", "fill", "compact", "tail", "gather")})
+        launches = (ix.launch_count() + ctx.launch_count() - l0) // steps
+        h2d = int(m) * 16 + (n_reads + 1) * 8 + n_reads * 8
+        d2h = n_reads * 4 + 4 * (n_reads + 1) * 8 + n_reads * 4 + n_chains * 8 + n_b * 16 + int(off0[-1]) * 0
+        mini_total = int(np.frombuffer((C.c_char * 8).from_address(res.mini_off + 8 * n_reads), np.int64)[0])
+        d2h += mini_total * 8
+        # parity on a sample: anchors, rep_len, mini_pos and chains against the oracle
+        import oracle
+        from oracle import seed as oseed
+        oix = oseed.SeedIndex(W.B, W.H, W.V, W.P)
+        ns = min(2000, n_reads)
+        out = ix.seed_chain_batch(prm, off0[:ns + 1], pin.array, bd[:ns], ql[:ns], want_anchors=True)
+        ok = True
+        want_a, want_off = [], [0]
+        for r in range(ns):
+            a, rep, mini = oseed.collect_seed_hits(oix, spec.flag, spec.max_occ, pin.array[off0[r]:off0[r + 1]], int(bd[r]), int(ql[r]))
+            ok = ok and np.array_equal(out.a[out.a_off[r]:out.a_off[r + 1]], a) and int(out.rep_len[r]) == rep and \
+                np.array_equal(out.mini_pos[out.mini_off[r]:out.mini_off[r + 1]], mini)
+            want_a.append(a); want_off.append(want_off[-1] + a.shape[0])
+        want = oracle.chain_batch(oracle.params(spec.preset), np.array(want_off, np.int64), np.concatenate(want_a))
+        ok = bool(ok and np.array_equal(out.chains.n_u, want.n_u) and np.array_equal(out.chains.u, want.u) and np.array_equal(out.chains.b, want.b))
+        # CPU beside it: the oracle's collect_seed_hits (a port of map.c:112-236) on a bounded sample, all host threads
+        threads = host_cores()
+        nc = min(20000, n_reads)
+
+        def part(k):
+            tot = 0
+            for r in range(k, nc, threads):
+                a, _, _ = oseed.collect_seed_hits(oix, spec.flag, spec.max_occ, pin.array[off0[r]:off0[r + 1]], int(bd[r]), int(ql[r]))
+                tot += a.shape[0]
+            return tot
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(part, range(threads)))          # warm-up: page in the index
+            t0 = time.perf_counter()
+            list(ex.map(part, range(threads)))
+            cpu_s = time.perf_counter() - t0
+        blk = {
+            "workload": f"{spec.name}: G-idx synthetic index ({spec.n_sites} minimizer sites, {W.n_keys} keys, streams B/H/V/P "
+                        f"{sum(x.size for x in W.streams) / 2**20:.0f} MiB, max occurrence {W.max_occ_seen}, mid_occ {spec.max_occ}), "
+                        f"{n_reads} reads x {spec.read_len} bases given as minimizers",
+            "api": "mm2b200_seed_chain_batch: pinned host minimizers in, pinned host chains + rep_len + mini_pos out (one call, one sub-batch)",
+            "reads": n_reads, "minimizers": int(m), "anchors": n_anchors, "chains": n_chains,
+            "ms_per_step": 1e3 * dt, "reads_per_s": n_reads / dt, "minimizers_per_s": int(m) / dt,
+            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "stage_ms_per_step": stage, "gpu_launches": int(launches),
+            "parity_with_oracle": {"ok": ok, "reads": ns},
+            "cpu_seeding_only": {"reads_per_s": nc / cpu_s, "cores": threads, "kind": "port",
+                                 "sample": f"first {nc} reads, oracle collect_seed_hits (lookup + expand + radix_sort_128x) over {threads} threads via ctypes"},
+            "index_build_s_host": build_s,
+        }
+        ix.close(); ctx.close(); pin.free(); W.close()
+        torch.cuda.empty_cache()
+        return blk
 
     def run_multi(self, spec, prm, n_reads, steps, solo_s):
         """Rank 0 alone owns N contexts (one per GPU) and N x n_reads reads in pinned memory and calls
@@ -692,6 +793,8 @@ def main():
     ap.add_argument("--slots", type=int, default=0)
     ap.add_argument("--wire", action="store_true", help="e2e: upload through the host batcher's 8-byte wire format (default: raw mm128_t)")
     ap.add_argument("--wire-threads", type=int, default=0, help="e2e: host encoder threads (0 = library default)")
+    ap.add_argument("--seeded-reads", type=int, default=100000, help="reads of the seeded leg (minimizers in, chains out; N=1 only); 0 = skip")
+    ap.add_argument("--only-seeded", action="store_true", help="run the seeded leg alone and print its block")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -699,6 +802,10 @@ def main():
     if int(os.environ.get("RANK", "0")) == 0:
         import __graft_entry__ as ge
         ge.build()
+    if args.only_seeded:
+        b = Bench(args)
+        print(json.dumps(b.run_seeded(args.seeded_reads, max(1, min(args.steps, 3)))))
+        return 0
     return Bench(args).run()
 
 

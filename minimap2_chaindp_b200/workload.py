@@ -111,3 +111,114 @@ def generate(spec: WorkloadSpec, first: int = 0, n_reads: int | None = None):
     a = np.zeros((int(offs[-1]), 2), dtype=np.uint64)
     fill(spec, offs, a, first)
     return offs, a
+
+
+# ---------------------------------------------------------------------------------------------------------
+# "G-idx": synthetic index streams + reads given as minimizers, for the seeding stage (csrc/workload_seed.c)
+# ---------------------------------------------------------------------------------------------------------
+class _IdxSpec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n_sites", C.c_int64), ("hash_bits", C.c_int32), ("b", C.c_int32), ("gap_max", C.c_int32),
+                ("ref_len", C.c_int32), ("p_dup", C.c_double), ("p_hot", C.c_double), ("n_hot", C.c_int32), ("reserved", C.c_int32)]
+
+
+class _ReadSpec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("read_len", C.c_int32), ("span", C.c_int32), ("p_match", C.c_double), ("p_drift", C.c_double)]
+
+
+@dataclass(frozen=True)
+class SeedWorkloadSpec:
+    name: str
+    preset: str
+    n_reads: int
+    seed: int
+    n_sites: int              # minimizer sites of the reference (~ bases * 2 / (w + 1))
+    read_len: int
+    hash_bits: int = 30       # 2k, k = 15
+    b: int = 14               # mi->b
+    gap_max: int = 10         # w
+    ref_len: int = 2_000_000  # the fork packs refpos in 21 bits
+    p_dup: float = 0.03
+    p_hot: float = 0.004
+    n_hot: int = 40
+    span: int = 15
+    p_match: float = 0.9 ** 15            # (1 - e)^k at 10 % error, as in G-anc map-ont-100k
+    p_drift: float = 0.10 / 3
+    max_occ: int = 50         # opt->mid_occ
+    flag: int = 0
+
+
+SEED_CONFIGS = {
+    # 100k x 10 kb reads against ~100 Mb of reference (19 M sites): index streams ~ 0.6 GB, far beyond L2
+    "map-ont-100k-seeded": SeedWorkloadSpec("map-ont-100k-seeded", "map-ont", 100_000, _SEED + 12, 19_000_000, 10_000),
+    "map-ont-small-seeded": SeedWorkloadSpec("map-ont-small-seeded", "map-ont", 2_000, _SEED + 13, 400_000, 10_000),
+}
+
+
+class SeedWorkload:
+    """The built index (streams as numpy views over C memory) and a sampler of reads."""
+
+    def __init__(self, spec: SeedWorkloadSpec):
+        L = lib()
+        if not hasattr(L, "_seed_bound"):
+            L.wls_build.restype = C.c_void_p
+            L.wls_build.argtypes = [C.POINTER(_IdxSpec)]
+            L.wls_free.argtypes = [C.c_void_p]
+            L.wls_free.restype = None
+            L.wls_streams.argtypes = [C.c_void_p] + [C.POINTER(C.c_void_p), C.POINTER(C.c_int64)] * 4 + [C.POINTER(C.c_int64)] * 2
+            L.wls_streams.restype = None
+            L.wls_reads_count.restype = C.c_int64
+            L.wls_reads_count.argtypes = [C.c_void_p, C.POINTER(_ReadSpec), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+            L.wls_reads_fill.restype = None
+            L.wls_reads_fill.argtypes = [C.c_void_p, C.POINTER(_ReadSpec), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+            L._seed_bound = True
+        self.spec = spec
+        cs = _IdxSpec(spec.seed, spec.n_sites, spec.hash_bits, spec.b, spec.gap_max, spec.ref_len, spec.p_dup, spec.p_hot, spec.n_hot, 0)
+        self._h = L.wls_build(C.byref(cs))
+        if not self._h:
+            raise MemoryError("wls_build failed")
+        ptr = [C.c_void_p() for _ in range(4)]
+        size = [C.c_int64() for _ in range(4)]
+        nk, mo = C.c_int64(), C.c_int64()
+        args = []
+        for p, s in zip(ptr, size):
+            args += [C.byref(p), C.byref(s)]
+        L.wls_streams(self._h, *args, C.byref(nk), C.byref(mo))
+        self.streams = []
+        for p, s in zip(ptr, size):
+            n = int(s.value)
+            self.streams.append(np.frombuffer((C.c_char * max(n, 1)).from_address(p.value), np.uint8, n) if n else np.zeros(0, np.uint8))
+        self.n_keys, self.max_occ_seen = int(nk.value), int(mo.value)
+        self._rs = _ReadSpec(spec.seed ^ 0xABCDEF, spec.read_len, spec.span, spec.p_match, spec.p_drift)
+
+    @property
+    def B(self): return self.streams[0]
+    @property
+    def H(self): return self.streams[1]
+    @property
+    def V(self): return self.streams[2]
+    @property
+    def P(self): return self.streams[3]
+
+    def reads(self, first: int = 0, n_reads: int | None = None, out: np.ndarray | None = None):
+        """-> (mv_off[n+1] int64, mv[(m, 2)] uint64, bid[n] uint32, qlen[n] int32) for reads [first, first + n)."""
+        n = self.spec.n_reads - first if n_reads is None else n_reads
+        off = np.zeros(n + 1, np.int64)
+        qlen = np.zeros(max(n, 1), np.int32)
+        bid = np.zeros(max(n, 1), np.uint32)
+        m = lib().wls_reads_count(self._h, C.byref(self._rs), first, n, off.ctypes.data, qlen.ctypes.data, bid.ctypes.data)
+        mv = out if out is not None else np.zeros((int(m), 2), np.uint64)
+        assert mv.dtype == np.uint64 and mv.size >= 2 * int(m)
+        lib().wls_reads_fill(self._h, C.byref(self._rs), first, n, off.ctypes.data, mv.ctypes.data)
+        return off, mv, bid[:n], qlen[:n]
+
+    def close(self):
+        if self._h:
+            self.streams = []
+            lib().wls_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
