@@ -329,7 +329,14 @@ class Bench:
         torch.cuda.synchronize()
         out["dev_ms"] = float(ev0.elapsed_time(ev1))
         out["launches"] = ctx.launch_count() - l0
+        # per-kernel durations: one more pass per step with every kernel alone on the stream (see run())
+        ctx.set_split(False)
+        ctx.stage_reset()
+        for _ in range(steps):
+            ctx.chain_device(prm, n_reads, n_anchors, d_offs.data_ptr(), d_a.data_ptr(), st)
+        torch.cuda.synchronize()
         out["stage"] = {s: ctx.stage_ms(s)[0] for s in ("prep", "fill", "compact", "tail", "gather")}
+        ctx.set_split(True)
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             res = ctx.chain_batch_raw(prm, n_reads, offs.ctypes.data, pin.ptr)
@@ -485,7 +492,22 @@ class Bench:
         self.barrier()
         dev_ms = self.rmax(ev0.elapsed_time(ev1))
         launches = ctx.launch_count() - launches0
+        stage_overlapped = {s: ctx.stage_ms(s) for s in ("prep", "fill", "compact", "tail", "gather")}
+        # per-kernel durations for the roofline: the same passes with every kernel ALONE on the stream (the timed region
+        # above runs the two halves of the batch on two streams, where the durations of concurrent kernels overlap)
+        ctx.set_split(False)
+        device_step()
+        torch.cuda.synchronize()
+        ctx.stage_reset()
+        ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev2.record(self.stream)
+        for _ in range(steps):
+            device_step()
+        ev3.record(self.stream)
+        torch.cuda.synchronize()
+        unsplit_ms = ev2.elapsed_time(ev3) / steps
         stage = {s: ctx.stage_ms(s) for s in ("prep", "fill", "compact", "tail", "gather")}
+        ctx.set_split(True)
 
         # ---- timed region 2: end to end through the C ABI with pinned host buffers (H2D + kernels + D2H inside), all ranks at once
         self.barrier()
@@ -587,6 +609,11 @@ class Bench:
                                  "algorithmic_bytes_per_launch": n_anchors * BYTES_PER_ANCHOR,
                                  "note": "secondary: 40 B/anchor algorithmic; the kernel is not HBM bound"},
                 "stage_ms_per_step": {k: v[0] / max(steps, 1) for k, v in stage.items()},
+                "stage_note": ("stage_ms_per_step, roofline.ms_per_launch: CUDA events around each kernel in an extra pass with every "
+                               "kernel alone on the stream (ms_per_step_unsplit); the timed region of `value` runs the two halves of the "
+                               "batch on two streams (stage_ms_overlapped: the same events there, durations of concurrent kernels overlap)"),
+                "ms_per_step_unsplit": unsplit_ms,
+                "stage_ms_overlapped": {k: v[0] / max(steps, 1) for k, v in stage_overlapped.items()},
             }
             if e2e_multi is not None:
                 line["e2e_multi"] = e2e_multi
@@ -679,8 +706,12 @@ class Bench:
         n_chains = int(np.frombuffer((C.c_char * 8).from_address(res.chains.u_off + 8 * n_reads), np.int64)[0])
         n_b = int(np.frombuffer((C.c_char * 8).from_address(res.chains.b_off + 8 * n_reads), np.int64)[0])
         stage = {k: (ms1[k] - ms0[k]) / steps for k in ms1}
-        stage.update({k: ctx.stage_ms(k)[0] / steps for k in ("prep", "fill", "compact", "tail", "gather")})
         launches = (ix.launch_count() + ctx.launch_count() - l0) // steps
+        ctx.set_split(False)                     # chaining kernels alone on the stream for their own durations (see run())
+        ctx.stage_reset()
+        call()
+        stage.update({k: ctx.stage_ms(k)[0] for k in ("prep", "fill", "compact", "tail", "gather")})
+        ctx.set_split(True)
         h2d = int(m) * 16 + (n_reads + 1) * 8 + n_reads * 8
         d2h = n_reads * 4 + 4 * (n_reads + 1) * 8 + n_reads * 4 + n_chains * 8 + n_b * 16 + int(off0[-1]) * 0
         mini_total = int(np.frombuffer((C.c_char * 8).from_address(res.mini_off + 8 * n_reads), np.int64)[0])

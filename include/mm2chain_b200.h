@@ -184,6 +184,12 @@ typedef struct {
 int mm2b200_fill_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,
                         const int64_t *d_offs, const mm128_t *d_a, void *stream, mm2b200_dev_records_t *out);
 
+/* mm2b200_chain_device on >= 4096 reads runs the two halves of the batch on two streams, so that the HBM-bound stages
+ * of one half run beside the issue-bound fill of the other (default on; MM2B200_SPLIT=0 at context creation turns it off).
+ * With on = 0 every kernel of a pass runs alone on the caller's stream -- the setting under which a kernel's own duration
+ * (mm2b200_stage_ms, the roofline of bench.py) is measured. */
+int mm2b200_set_split(mm2b200_ctx_t *ctx, int32_t on);
+
 /* kernel launches issued by this context so far (bench.py's gpu_launches) */
 int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx);
 

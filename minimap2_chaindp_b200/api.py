@@ -35,7 +35,7 @@ EXPORTED_SYMBOLS = (
     "mm2b200_chain_batch", "mm2b200_fill_batch", "mm2b200_bottom_batch",
     "mm2b200_partition_reads", "mm2b200_chain_batch_multi",
     "mm2b200_chain_device", "mm2b200_fill_device", "mm2b200_launch_count", "mm2b200_stage_ms", "mm2b200_stage_reset", "mm2b200_int_peak",
-    "mm2b200_set_upload", "mm2b200_upload_stats", "mm2b200_wire_encode", "mm2b200_version",
+    "mm2b200_set_split", "mm2b200_set_upload", "mm2b200_upload_stats", "mm2b200_wire_encode", "mm2b200_version",
 )
 
 
@@ -130,6 +130,7 @@ def lib() -> C.CDLL:
         L.mm2b200_stage_reset.restype = None
         L.mm2b200_int_peak.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
         L.mm2b200_set_upload.argtypes = [vp, i32, i32]
+        L.mm2b200_set_split.argtypes = [vp, i32]
         L.mm2b200_upload_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
         L.mm2b200_wire_encode.argtypes = [vp, i64, vp, C.c_size_t] + [C.POINTER(C.c_size_t)] * 3
         # reference entry points
@@ -314,6 +315,10 @@ class ChainContext:
 
     def stage_reset(self):
         lib().mm2b200_stage_reset(self._h)
+
+    def set_split(self, on: bool = True):
+        """chain_device: two halves of a batch on two streams (default) or every kernel alone on the caller's stream."""
+        _check(lib().mm2b200_set_split(self._h, 1 if on else 0))
 
     def set_upload(self, wire: bool = True, threads: int = 0):
         """Host batcher: 8-byte wire format for the anchor upload (default on) and its encoder thread count (0 = all cores)."""

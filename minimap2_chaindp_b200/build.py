@@ -37,16 +37,44 @@ def _stale(target: str, sources) -> bool:
     return any(os.path.getmtime(s) > t for s in sources)
 
 
+CU_SOURCES = ("chain_kernels.cu", "chain_api.cu", "seed_kernels.cu", "seed_api.cu", "fpgadrv_shim.cu")
+CU_HEADERS = ("chain_internal.h", "seed_internal.h", "sort_exact.cuh", "packet_format.h")
+API_HEADERS = ("mm2chain_b200.h", "mm2seed_b200.h", "mm2fpgadrv_b200.h")
+OBJ_DIR = os.path.join(PKG, "_obj")
+
+
 def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
-    srcs = [os.path.join(CSRC, f) for f in ("chain_kernels.cu", "chain_api.cu", "seed_kernels.cu", "seed_api.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("chain_internal.h", "seed_internal.h", "sort_exact.cuh")] + \
-        [os.path.join(ROOT, "include", f) for f in ("mm2chain_b200.h", "mm2seed_b200.h")]
-    if force or _stale(LIB, deps):
-        cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-o", LIB, *srcs, "-lpthread"]
-        if verbose:
-            cmd.insert(1, "-Xptxas=-v")
-            print(" ".join(cmd), file=sys.stderr)
-        subprocess.run(cmd, check=True)
+    """Every .cu is compiled to its own object (in parallel, only when it or a header changed), then linked."""
+    from concurrent.futures import ThreadPoolExecutor
+    srcs = [os.path.join(CSRC, f) for f in CU_SOURCES]
+    hdrs = [os.path.join(CSRC, f) for f in CU_HEADERS] + [os.path.join(ROOT, "include", f) for f in API_HEADERS]
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    tag = os.path.join(OBJ_DIR, "flags.txt")
+    flags = " ".join([*NVCC_FLAGS, *extra])
+    if not os.path.exists(tag) or open(tag).read() != flags:
+        force = True
+    compile_flags = [f for f in NVCC_FLAGS if f not in ("--shared",)]
+    for drop in ("-Xlinker", "-Bsymbolic-functions", "-cudart", "static"):
+        compile_flags.remove(drop)
+    jobs = []
+    for src in srcs:
+        obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")
+        if force or _stale(obj, [src, *hdrs]):
+            cmd = [_nvcc(), *compile_flags, *extra, "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-c", "-o", obj, src]
+            if verbose:
+                cmd.insert(1, "-Xptxas=-v")
+                print(" ".join(cmd), file=sys.stderr)
+            jobs.append(cmd)
+    if jobs:
+        with ThreadPoolExecutor(len(jobs)) as ex:
+            for r in ex.map(lambda c: subprocess.run(c), jobs):
+                if r.returncode:
+                    raise subprocess.CalledProcessError(r.returncode, r.args)
+    objs = [os.path.join(OBJ_DIR, f[:-3] + ".o") for f in CU_SOURCES]
+    if jobs or force or _stale(LIB, objs):
+        subprocess.run([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "--shared", "-Xlinker", "-Bsymbolic-functions",
+                        "-cudart", "static", "-o", LIB, *objs, "-lpthread"], check=True)
+        open(tag, "w").write(flags)
     return LIB
 
 

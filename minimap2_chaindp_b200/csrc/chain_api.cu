@@ -478,6 +478,14 @@ extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 
 extern "C" int64_t mm2b200_launch_count(const mm2b200_ctx_t *ctx) { return ctx ? ctx->launches.load() : 0; }
 
+extern "C" int mm2b200_set_split(mm2b200_ctx_t *ctx, int32_t on)
+{
+	if (!ctx) return fail(MM2B200_ERR_ARG, "NULL context");
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	ctx->split_device = on != 0;
+	return MM2B200_OK;
+}
+
 extern "C" int mm2b200_set_upload(mm2b200_ctx_t *ctx, int32_t wire, int32_t threads)
 {
 	if (!ctx || threads < 0) return fail(MM2B200_ERR_ARG, "bad upload settings");

@@ -1,0 +1,506 @@
+// fpgadrv_shim.cu -- the fork's driver boundary (fpga.h:37-62) on B200s: the 11 symbols the
+// fork's objects expect from the closed libfpgadrv.a, implemented over the seeding + chaining device path of this library.
+// See include/mm2fpgadrv_b200.h for the contract.  Host code only: the device work is mm2b200_seed_fill_batch.
+//
+// Structure (B200-first, not the FPGA's ring of fixed buffers):
+//   fpga_writebuf_submit  -> a queue of request packets
+//   one worker per GPU    -> takes everything that waits (bounded), copies the minimizers of all packets once into a pinned
+//                            staging array (so the H2D copy is one DMA), runs ONE device batch for all reads, cuts the
+//                            records / mini_pos back into one response packet per request packet
+//   fpga_get_retbuf       -> a queue of finished response packets
+// A batch the device refuses (allocation failure, anchor count beyond the index space) is halved and retried; a single read
+// that still fails is answered with err_flag = 1, the fork's own "host, redo this read" protocol (map.c:933-944).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <utility>
+#include <vector>
+#include "mm2fpgadrv_b200.h"
+#include "seed_internal.h"
+#include "packet_format.h"
+
+using namespace mm2b200;
+
+namespace {
+
+struct Packet { void *buf; uint32_t size; };
+
+struct ShimDevice {
+	int ordinal = 0;
+	mm2b200_ctx_t *ctx = nullptr;
+	mm2b200_index_t *idx = nullptr;
+	bool index_dirty = false;          // streams loaded since the last commit (guarded by Shim::mu)
+	std::thread th;
+	// pinned staging of one batch (owned by the worker)
+	mm128_t *mv = nullptr; size_t mv_cap = 0;
+};
+
+struct Shim {
+	std::mutex mu;
+	std::condition_variable cv_work, cv_ret, cv_idle;
+	std::deque<Packet> pending;
+	std::deque<Packet> done;
+	int64_t pending_bytes = 0;         // request bytes handed out by get_writebuf and not yet worked off
+	int busy = 0;                      // workers inside a batch
+	bool exit_block = false, stop = false;
+	bool have_params = false, have_index = false;
+	mm2b200_seed_params_t prm{};
+	std::vector<std::unique_ptr<ShimDevice>> dev;
+	int64_t max_bytes = (int64_t)1 << 30;
+	int64_t batch_mv = (int64_t)8 << 20;
+	std::atomic<int64_t> n_packets{0}, n_reads{0}, n_batches{0}, n_err{0};
+};
+
+Shim *g_shim = nullptr;
+std::mutex g_shim_mu;                  // guards creation / destruction of g_shim
+
+bool shim_abort_on_error()
+{
+	const char *e = getenv("MM2B200_ON_ERROR");
+	return !(e && !strcmp(e, "null"));
+}
+
+void shim_fatal(const char *what, const char *msg)
+{
+	fprintf(stderr, "[mm2chain-b200] driver shim: %s: %s -- aborting\n", what, msg ? msg : "");
+	abort();
+}
+
+int64_t env_i64(const char *name, int64_t dflt)
+{
+	const char *e = getenv(name);
+	if (!e || !*e) return dflt;
+	char *end = nullptr;
+	long long v = strtoll(e, &end, 10);
+	if (end && (*end == 'k' || *end == 'K')) v <<= 10;
+	else if (end && (*end == 'm' || *end == 'M')) v <<= 20;
+	else if (end && (*end == 'g' || *end == 'G')) v <<= 30;
+	return v > 0 ? (int64_t)v : dflt;
+}
+
+std::vector<int> shim_devices()
+{
+	std::vector<int> out;
+	const int n = mm2b200_device_count();
+	const char *e = getenv("MM2B200_DEVICES");
+	if (e && !strcmp(e, "all")) {
+		for (int i = 0; i < n; ++i) out.push_back(i);
+	} else if (e && *e) {
+		const char *p = e;
+		while (*p) {
+			char *end = nullptr;
+			long v = strtol(p, &end, 10);
+			if (end == p) break;
+			if (v >= 0 && v < n) out.push_back((int)v);
+			p = *end == ',' ? end + 1 : end;
+		}
+	}
+	if (out.empty()) {
+		const char *d = getenv("MM2B200_DEVICE");
+		out.push_back(d ? atoi(d) : 0);
+	}
+	return out;
+}
+
+// ---- one read of a batch ----------------------------------------------------------------------------------------
+struct ReadRef {
+	int pkt, slot;                     // request packet and position inside it
+	PktTask task;
+	const char *mv;                    // minimizers inside the request packet
+	// result: either a view into the index object's arenas (valid until its next call) or owned copies
+	const struct new_seed *rec = nullptr; int64_t n_rec = 0;
+	const uint64_t *mini = nullptr; int64_t n_mini = 0;
+	int32_t rep_len = 0;
+	bool err = false, in_arena = false;
+	std::vector<char> keep;
+};
+
+// results of the previous device call still live in the arenas: copy them out before the next call overwrites them
+void evacuate(std::vector<ReadRef> &reads, const std::vector<int> &members)
+{
+	for (int k : members) {
+		ReadRef &r = reads[(size_t)k];
+		if (!r.in_arena) continue;
+		const size_t rb = (size_t)r.n_rec * sizeof(struct new_seed), mb = (size_t)r.n_mini * 8;
+		r.keep.resize(rb + mb + 8);
+		if (rb) memcpy(r.keep.data(), r.rec, rb);
+		char *m = r.keep.data() + ((rb + 7) & ~(size_t)7);
+		if (mb) memcpy(m, r.mini, mb);
+		r.rec = (const struct new_seed*)r.keep.data();
+		r.mini = (const uint64_t*)m;
+		r.in_arena = false;
+	}
+}
+
+bool ensure_stage(ShimDevice &d, size_t n_mv)
+{
+	if (n_mv <= d.mv_cap && d.mv) return true;
+	if (d.mv) mm2b200_pinned_free(d.mv);
+	d.mv_cap = n_mv + n_mv / 4 + 1024;
+	d.mv = (mm128_t*)mm2b200_pinned_alloc(d.mv_cap * sizeof(mm128_t));
+	if (!d.mv) { d.mv_cap = 0; return false; }
+	return true;
+}
+
+// one device call over reads members[lo..hi) (all share gap_ref / gap_qry); false = the device refused
+bool run_range(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &prm, std::vector<ReadRef> &reads, const std::vector<int> &members,
+               size_t lo, size_t hi, std::vector<int> &last_call, std::string &err)
+{
+	evacuate(reads, last_call);
+	last_call.clear();
+	size_t n_mv = 0;
+	for (size_t k = lo; k < hi; ++k) n_mv += (size_t)reads[(size_t)members[k]].task.seednum;
+	if (!ensure_stage(d, n_mv + 1)) { err = "pinned staging allocation failed"; return false; }
+	const size_t R = hi - lo;
+	std::vector<int64_t> off(R + 1, 0);
+	std::vector<uint32_t> bid(R);
+	std::vector<int32_t> qlen(R);
+	size_t at = 0;
+	for (size_t k = lo; k < hi; ++k) {
+		const ReadRef &r = reads[(size_t)members[k]];
+		const size_t n = (size_t)r.task.seednum;
+		if (n) memcpy(d.mv + at, r.mv, n * sizeof(mm128_t));
+		at += n;
+		off[k - lo + 1] = (int64_t)at;
+		bid[k - lo] = r.task.bid;
+		qlen[k - lo] = r.task.qlensum;
+	}
+	mm2b200_seed_records_t rr;
+	memset(&rr, 0, sizeof(rr));
+	const int rc = mm2b200_seed_fill_batch(d.idx, &prm, (int64_t)R, off.data(), d.mv, bid.data(), qlen.data(), &rr);
+	if (rc != MM2B200_OK) {
+		err = mm2b200_last_error();
+		// a CUDA / state error is not a property of the reads: never turn it into silent host work unless asked to
+		if ((rc == MM2B200_ERR_CUDA || rc == MM2B200_ERR_STATE) && shim_abort_on_error()) shim_fatal("device batch failed", err.c_str());
+		return false;
+	}
+	S.n_batches.fetch_add(1);
+	for (size_t k = lo; k < hi; ++k) {
+		ReadRef &r = reads[(size_t)members[k]];
+		const size_t q = k - lo;
+		r.rec = rr.rec + rr.rec_off[q]; r.n_rec = rr.rec_off[q + 1] - rr.rec_off[q];
+		r.mini = rr.mini_pos + rr.mini_off[q]; r.n_mini = rr.mini_off[q + 1] - rr.mini_off[q];
+		r.rep_len = rr.rep_len[q];
+		r.in_arena = true; r.err = false;
+		last_call.push_back(members[k]);
+	}
+	return true;
+}
+
+// all reads of one (gap_ref, gap_qry) group: whole group first, halves on refusal, err_flag for a single refused read
+void run_group(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &prm, std::vector<ReadRef> &reads, const std::vector<int> &members,
+               std::vector<int> &last_call)
+{
+	std::vector<std::pair<size_t, size_t>> todo;
+	todo.emplace_back((size_t)0, members.size());
+	std::string err;
+	while (!todo.empty()) {
+		const std::pair<size_t, size_t> r = todo.back();
+		todo.pop_back();
+		if (r.first >= r.second) continue;
+		if (run_range(S, d, prm, reads, members, r.first, r.second, last_call, err)) continue;
+		if (r.second - r.first == 1) {
+			ReadRef &rd = reads[(size_t)members[r.first]];
+			rd.err = true; rd.n_rec = rd.n_mini = 0; rd.in_arena = false;
+			S.n_err.fetch_add(1);
+			fprintf(stderr, "[mm2chain-b200] driver shim: read %u goes back to the host (err_flag = 1): %s\n", rd.task.read_id, err.c_str());
+			continue;
+		}
+		const size_t mid = r.first + (r.second - r.first) / 2;
+		todo.emplace_back(mid, r.second);
+		todo.emplace_back(r.first, mid);
+	}
+}
+
+// parse, run, answer.  Appends one response packet per request packet to `out`.
+void process_batch(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &base, const std::vector<Packet> &pkts, std::vector<Packet> &out)
+{
+	std::vector<ReadRef> reads;
+	std::vector<PktHead> heads(pkts.size());
+	std::vector<std::pair<size_t, size_t>> span(pkts.size());      // reads[first, last) of packet p
+	for (size_t p = 0; p < pkts.size(); ++p) {
+		const char *b = (const char*)pkts[p].buf, *end = b + pkts[p].size;
+		if (pkts[p].size < sizeof(PktHead)) shim_fatal("malformed request", "packet shorter than its header");
+		memcpy(&heads[p], b, sizeof(PktHead));
+		if (heads[p].type != MM2B200_PKT_TYPE) shim_fatal("malformed request", "chaindp_sndhdr_t.type is not 3 (map.c:301,491)");
+		b += sizeof(PktHead);
+		span[p].first = reads.size();
+		for (int i = 0; i < (int)heads[p].num; ++i) {
+			if (b + sizeof(PktTask) > end) shim_fatal("malformed request", "packet truncated at a task header");
+			ReadRef r;
+			r.pkt = (int)p; r.slot = i;
+			memcpy(&r.task, b, sizeof(PktTask));
+			if (r.task.seednum < 0) shim_fatal("malformed request", "negative minimizer count");
+			r.mv = b + sizeof(PktTask);
+			if (r.mv + (int64_t)r.task.seednum * 16 > end) shim_fatal("malformed request", "packet truncated inside a task");
+			b = r.mv + pkt_up64((int64_t)r.task.seednum * 16);
+			reads.push_back(std::move(r));
+		}
+		span[p].second = reads.size();
+	}
+	S.n_packets.fetch_add((int64_t)pkts.size());
+	S.n_reads.fetch_add((int64_t)reads.size());
+	// groups of equal (gap_ref, gap_qry): one in practice (map.c:358-366 derives both from the options for long reads)
+	std::vector<std::pair<int32_t, int32_t>> keys;
+	std::vector<std::vector<int>> groups;
+	for (size_t k = 0; k < reads.size(); ++k) {
+		const int32_t g_ref = reads[k].task.gap_ref, g_qry = reads[k].task.gap_qry;
+		const std::pair<int32_t, int32_t> key(g_ref, g_qry);
+		size_t g = 0;
+		while (g < keys.size() && keys[g] != key) ++g;
+		if (g == keys.size()) { keys.push_back(key); groups.emplace_back(); }
+		groups[g].push_back((int)k);
+	}
+	std::vector<int> last_call;
+	for (size_t g = 0; g < groups.size(); ++g) {
+		mm2b200_seed_params_t q = base;
+		q.chain.max_dist_x = keys[g].first;       // max_chain_gap_ref, map.c:515
+		q.chain.max_dist_y = keys[g].second;      // max_chain_gap_qry, map.c:516
+		q.chain.n_segs = keys[g].second;          // the fork's device model reads n_segs from gap_qry (map.c:517)
+		run_group(S, d, q, reads, groups[g], last_call);
+	}
+	// response packets (map.c:495-501,533-565); padding is zero
+	for (size_t p = 0; p < pkts.size(); ++p) {
+		int64_t need = sizeof(PktHead);
+		for (size_t k = span[p].first; k < span[p].second; ++k) {
+			const ReadRef &r = reads[k];
+			need += (int64_t)sizeof(PktResult);
+			if (!r.err) need += pkt_up64(r.n_rec * (int64_t)sizeof(struct new_seed)) + pkt_up64(r.n_mini * 8);
+		}
+		if (need > 0x7fffffffLL) shim_fatal("response", "a response packet exceeds 2 GiB (fpga_get_retbuf reports its size as int)");
+		char *o = (char*)calloc(1, (size_t)need);
+		if (!o) shim_fatal("response", "out of host memory");
+		PktHead oh;
+		memset(&oh, 0, sizeof(oh));
+		oh.magic = heads[p].magic; oh.tid = heads[p].tid; oh.num = heads[p].num; oh.type = heads[p].type; oh.lat = heads[p].lat;
+		oh.size = (uint32_t)need;
+		memcpy(o, &oh, sizeof(oh));
+		char *w = o + sizeof(oh);
+		for (size_t k = span[p].first; k < span[p].second; ++k) {
+			const ReadRef &r = reads[k];
+			PktResult pr;
+			memset(&pr, 0, sizeof(pr));
+			pr.read_id = r.task.read_id;
+			if (r.err) {
+				pr.err_flag = 1; pr.sub_size = sizeof(PktResult);
+				memcpy(w, &pr, sizeof(pr));
+				w += sizeof(pr);
+				continue;
+			}
+			const int64_t rec_b = pkt_up64(r.n_rec * (int64_t)sizeof(struct new_seed)), mini_b = pkt_up64(r.n_mini * 8);
+			pr.n_a = (uint32_t)r.n_rec; pr.n_minipos = (uint32_t)r.n_mini; pr.rep_len = (uint32_t)r.rep_len;
+			pr.sub_size = (uint32_t)(sizeof(PktResult) + rec_b + mini_b);
+			memcpy(w, &pr, sizeof(pr));
+			w += sizeof(pr);
+			if (r.n_rec) memcpy(w, r.rec, (size_t)r.n_rec * sizeof(struct new_seed));
+			w += rec_b;
+			if (r.n_mini) memcpy(w, r.mini, (size_t)r.n_mini * 8);
+			w += mini_b;
+		}
+		out.push_back(Packet{o, (uint32_t)need});
+	}
+}
+
+void worker_main(Shim *S, ShimDevice *d)
+{
+	std::vector<Packet> take, out;
+	for (;;) {
+		bool commit = false;
+		mm2b200_seed_params_t prm;
+		{
+			std::unique_lock<std::mutex> lk(S->mu);
+			S->cv_work.wait(lk, [&] { return S->stop || !S->pending.empty(); });
+			if (S->pending.empty()) break;       // stop requested and nothing left
+			take.clear();
+			int64_t mv = 0;
+			while (!S->pending.empty() && (take.empty() || mv < S->batch_mv)) {
+				take.push_back(S->pending.front());
+				mv += S->pending.front().size / 16;
+				S->pending.pop_front();
+			}
+			++S->busy;
+			commit = d->index_dirty; d->index_dirty = false;
+			prm = S->prm;
+			if (!S->have_params) shim_fatal("request before fpga_set_params", "the DP parameters are not in the packets (main.c:243)");
+			if (!S->have_index) shim_fatal("request before fpga_load_index", "no index streams were loaded (main.c:201-204)");
+		}
+		if (commit && mm2b200_index_commit(d->idx) != MM2B200_OK) shim_fatal("index commit failed", mm2b200_last_error());
+		out.clear();
+		process_batch(*S, *d, prm, take, out);
+		int64_t bytes = 0;
+		for (const Packet &p : take) { bytes += p.size; free(p.buf); }
+		{
+			std::lock_guard<std::mutex> lk(S->mu);
+			for (const Packet &p : out) S->done.push_back(p);
+			S->pending_bytes -= bytes;
+			--S->busy;
+			S->cv_ret.notify_all();
+			if (S->pending.empty() && S->busy == 0) S->cv_idle.notify_all();
+		}
+	}
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fpga.h
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int fpga_init(int flag)
+{
+	(void)flag;
+	std::lock_guard<std::mutex> gl(g_shim_mu);
+	if (g_shim) return 0;
+	std::unique_ptr<Shim> S(new Shim());
+	S->max_bytes = env_i64("MM2B200_SHIM_MAX_BYTES", S->max_bytes);
+	S->batch_mv = env_i64("MM2B200_SHIM_BATCH_MV", S->batch_mv);
+	for (int ord : shim_devices()) {
+		std::unique_ptr<ShimDevice> d(new ShimDevice());
+		d->ordinal = ord;
+		mm2b200_config_t cfg;
+		memset(&cfg, 0, sizeof(cfg));
+		cfg.device = ord;
+		cfg.n_slots = 1;
+		if (mm2b200_create(&cfg, &d->ctx) != MM2B200_OK || mm2b200_index_create(d->ctx, &d->idx) != MM2B200_OK) {
+			fprintf(stderr, "[mm2chain-b200] fpga_init: device %d: %s\n", ord, mm2b200_last_error());
+			if (shim_abort_on_error()) abort();
+			return -1;
+		}
+		S->dev.push_back(std::move(d));
+	}
+	for (auto &d : S->dev) d->th = std::thread(worker_main, S.get(), d.get());
+	g_shim = S.release();
+	return 0;
+}
+
+extern "C" void fpga_finalize()
+{
+	std::lock_guard<std::mutex> gl(g_shim_mu);
+	Shim *S = g_shim;
+	if (!S) return;
+	{ std::lock_guard<std::mutex> lk(S->mu); S->stop = true; }
+	S->cv_work.notify_all();
+	for (auto &d : S->dev) if (d->th.joinable()) d->th.join();
+	for (auto &d : S->dev) {
+		if (d->mv) mm2b200_pinned_free(d->mv);
+		if (d->idx) mm2b200_index_destroy(d->idx);
+		if (d->ctx) mm2b200_destroy(d->ctx);
+	}
+	for (const Packet &p : S->done) free(p.buf);
+	g_shim = nullptr;
+	delete S;
+}
+
+extern "C" void fpga_set_params(int bw, int is_cdna, int max_skip, int min_sc, int flag, int max_occ)
+{
+	Shim *S = g_shim;
+	if (!S) shim_fatal("fpga_set_params", "fpga_init has not run");
+	std::lock_guard<std::mutex> lk(S->mu);
+	memset(&S->prm, 0, sizeof(S->prm));
+	S->prm.chain.bw = bw; S->prm.chain.is_cdna = is_cdna; S->prm.chain.max_skip = max_skip; S->prm.chain.min_sc = min_sc;
+	S->prm.chain.min_cnt = 1;                  // stays on the host (mm_chain_dp_bottom); unused by the device half
+	S->prm.chain.n_segs = 1; S->prm.chain.max_iter = 0;
+	S->prm.flag = flag; S->prm.max_occ = max_occ;
+	S->have_params = true;
+}
+
+extern "C" void fpga_load_index(void *addr, int size, int type)
+{
+	Shim *S = g_shim;
+	if (!S) shim_fatal("fpga_load_index", "fpga_init has not run");
+	std::unique_lock<std::mutex> lk(S->mu);
+	// a new index part replaces the old one: everything submitted against the old one must be through
+	S->cv_idle.wait(lk, [&] { return S->pending.empty() && S->busy == 0; });
+	for (auto &d : S->dev) {
+		if (mm2b200_index_load(d->idx, addr, size, type) != MM2B200_OK) shim_fatal("fpga_load_index", mm2b200_last_error());
+		d->index_dirty = true;
+	}
+	S->have_index = true;
+}
+
+extern "C" void *fpga_get_writebuf_thread(unsigned long size, BUF_TYPE type, int tid)
+{
+	(void)type; (void)tid;
+	Shim *S = g_shim;
+	if (!S) return nullptr;
+	{
+		std::lock_guard<std::mutex> lk(S->mu);
+		if (S->pending_bytes > 0 && S->pending_bytes + (int64_t)size > S->max_bytes) return nullptr;   // back-pressure: the caller sleeps and retries
+		S->pending_bytes += (int64_t)size;
+	}
+	void *p = malloc(size ? size : 1);
+	if (!p) { std::lock_guard<std::mutex> lk(S->mu); S->pending_bytes -= (int64_t)size; }
+	return p;
+}
+
+extern "C" void *fpga_get_writebuf(unsigned long size, BUF_TYPE type) { return fpga_get_writebuf_thread(size, type, -1); }
+
+extern "C" int fpga_writebuf_submit(void *addr, unsigned int size, unsigned int type)
+{
+	(void)type;
+	Shim *S = g_shim;
+	if (!S || !addr) return -1;
+	{
+		std::lock_guard<std::mutex> lk(S->mu);
+		S->pending.push_back(Packet{addr, size});
+	}
+	S->cv_work.notify_one();
+	return 0;
+}
+
+extern "C" void *fpga_get_retbuf(int *len, RET_TYPE type)
+{
+	(void)type;
+	Shim *S = g_shim;
+	if (len) *len = 0;
+	if (!S) return nullptr;
+	std::unique_lock<std::mutex> lk(S->mu);
+	S->cv_ret.wait(lk, [&] { return !S->done.empty() || (S->exit_block && S->pending.empty() && S->busy == 0); });
+	if (S->done.empty()) return nullptr;
+	const Packet p = S->done.front();
+	S->done.pop_front();
+	if (len) *len = (int)p.size;
+	return p.buf;
+}
+
+extern "C" int fpga_release_retbuf(void *addr) { free(addr); return 0; }
+
+extern "C" void fpga_exit_block()
+{
+	Shim *S = g_shim;
+	if (!S) return;
+	{ std::lock_guard<std::mutex> lk(S->mu); S->exit_block = true; }
+	S->cv_ret.notify_all();
+}
+
+extern "C" void fpga_set_block()
+{
+	Shim *S = g_shim;
+	if (!S) return;
+	std::lock_guard<std::mutex> lk(S->mu);
+	S->exit_block = false;
+}
+
+extern "C" int mm2b200_shim_stats(int64_t *n_packets, int64_t *n_reads, int64_t *n_batches, int64_t *n_err_reads, int64_t *n_launches)
+{
+	Shim *S = g_shim;
+	if (!S) return -1;
+	if (n_packets) *n_packets = S->n_packets.load();
+	if (n_reads) *n_reads = S->n_reads.load();
+	if (n_batches) *n_batches = S->n_batches.load();
+	if (n_err_reads) *n_err_reads = S->n_err.load();
+	if (n_launches) {
+		int64_t n = 0;
+		for (auto &d : S->dev) n += mm2b200_launch_count(d->ctx) + mm2b200_seed_launch_count(d->idx);
+		*n_launches = n;
+	}
+	return 0;
+}

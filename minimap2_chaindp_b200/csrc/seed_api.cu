@@ -14,6 +14,7 @@
 #include <utility>
 #include <vector>
 #include "seed_internal.h"
+#include "packet_format.h"
 
 using namespace mm2b200;
 
@@ -409,14 +410,7 @@ extern "C" int mm2b200_seed_fill_batch(mm2b200_index_t *ix, const mm2b200_seed_p
 // packet level: the fork's wire format
 // ---------------------------------------------------------------------------------------------------------
 namespace {
-// fpga_chaindp.h:79-87
-struct __attribute__((__packed__)) PktHead { uint32_t magic, size; uint16_t tid, num; uint8_t type, lat; uint8_t reserve1[50]; };
-// fpga_chaindp.h:46-58
-struct __attribute__((__packed__)) PktTask { int32_t gap_qry, gap_ref, seednum, qlensum; uint32_t read_id, bid; int16_t n_segs; char b; char reserve1[1]; uint64_t mv_a; char reserve2[28]; };
-// fpga_chaindp.h:60-68
-struct __attribute__((__packed__)) PktResult { uint32_t err_flag, read_id, sub_size, n_a, n_minipos, rep_len; char reserve1[40]; };
-static_assert(sizeof(PktHead) == 64 && sizeof(PktTask) == 64 && sizeof(PktResult) == 64, "packet headers are 64 bytes");
-inline int64_t up64(int64_t x) { return (x + 63) & ~(int64_t)63; }
+inline int64_t up64(int64_t x) { return pkt_up64(x); }
 }
 
 extern "C" int mm2b200_seed_work(mm2b200_index_t *ix, const mm2b200_seed_params_t *prm, const void *req, int64_t req_size,

@@ -39,6 +39,25 @@ def test_library_exports_every_seeding_symbol():
     assert C.sizeof(seed.SeedParams) == 44
 
 
+def test_library_exports_every_driver_symbol():
+    """include/mm2fpgadrv_b200.h: the 11 symbols the fork's objects expect from libfpgadrv.a (fpga.h:37-62)"""
+    from minimap2_chaindp_b200 import fpgadrv
+    src = open(os.path.join(ROOT, "include", "mm2fpgadrv_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = sorted(set(re.findall(r"\b(fpga_[a-z_]+|mm2b200_[a-z0-9_]+)\s*\(", src)))
+    assert len([n for n in names if n.startswith("fpga_")]) == 11
+    L = api.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mm2fpgadrv_b200.h but not exported"
+    assert sorted(fpgadrv.EXPORTED_SYMBOLS) == names
+    # without fpga_init nothing is served: no buffer, no packet, no counters
+    F = fpgadrv._lib()
+    import ctypes as C
+    n = C.c_int(5)
+    assert not F.fpga_get_writebuf(64, 0) and not F.fpga_get_retbuf(C.byref(n), 3) and n.value == 0
+    assert F.mm2b200_shim_stats(None, None, None, None, None) == -1
+
+
 def test_index_streams_are_validated_without_a_gpu():
     """size checks of mm2b200_index_commit come before any device work; without a context nothing can be created"""
     import torch
