@@ -233,6 +233,9 @@ struct mm2b200_ctx {
 	cudaStream_t aux_stream = nullptr;
 	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	bool split_device = true;
+	// state of the stages built around the DP (post-processing, sketching): owned by their own translation units
+	void *ext[4] = { nullptr, nullptr, nullptr, nullptr };
+	void (*ext_free[4])(void*) = { nullptr, nullptr, nullptr, nullptr };
 	// profiling
 	StageAcc acc[ST_N];
 	std::vector<StageSpan> spans;
@@ -466,6 +469,7 @@ extern "C" void mm2b200_destroy(mm2b200_ctx_t *ctx)
 		if (s.ev_user) cudaEventDestroy(s.ev_user);
 		if (s.stream) cudaStreamDestroy(s.stream);
 	}
+	for (int k = 0; k < 4; ++k) if (ctx->ext[k] && ctx->ext_free[k]) { ctx->ext_free[k](ctx->ext[k]); ctx->ext[k] = nullptr; }
 	drain_spans(ctx);
 	if (ctx->aux_stream) { cudaStreamSynchronize(ctx->aux_stream); cudaStreamDestroy(ctx->aux_stream); }
 	if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
@@ -950,6 +954,9 @@ int api_fail(int code, const char *msg) { return fail(code, "%s", msg); }
 int ctx_device(const mm2b200_ctx *ctx) { return ctx->device; }
 int ctx_profile(const mm2b200_ctx *ctx) { return ctx->profile; }
 int ctx_sm_count(const mm2b200_ctx *ctx) { return ctx->lc.sm_count; }
+void *ctx_ext(const mm2b200_ctx *ctx, int k) { return ctx->ext[k]; }
+void ctx_set_ext(mm2b200_ctx *ctx, int k, void *p, void (*free_fn)(void*)) { ctx->ext[k] = p; ctx->ext_free[k] = free_fn; }
+void ctx_add_launches(mm2b200_ctx *ctx, int64_t n) { ctx->launches.fetch_add(n); }
 }
 
 extern "C" int mm2b200_fill_device(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, int64_t n_reads, int64_t n_anchors,

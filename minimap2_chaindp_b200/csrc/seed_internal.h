@@ -56,6 +56,10 @@ int api_fail(int code, const char *msg);       // records the thread's last erro
 int ctx_device(const mm2b200_ctx *ctx);
 int ctx_profile(const mm2b200_ctx *ctx);
 int ctx_sm_count(const mm2b200_ctx *ctx);
+// per-context state of the stages around the DP (k = 0: post-processing, 1: sketching); freed by mm2b200_destroy
+void *ctx_ext(const mm2b200_ctx *ctx, int k);
+void ctx_set_ext(mm2b200_ctx *ctx, int k, void *p, void (*free_fn)(void*));
+void ctx_add_launches(mm2b200_ctx *ctx, int64_t n);
 
 // launchers; each returns the number of kernels it enqueued
 int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cudaStream_t s);   // + scans over reads, totals, mini_pos packing

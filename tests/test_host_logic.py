@@ -39,6 +39,17 @@ def test_library_exports_every_seeding_symbol():
     assert C.sizeof(seed.SeedParams) == 44
 
 
+def test_library_exports_every_post_processing_symbol():
+    from minimap2_chaindp_b200 import post
+    import ctypes as C
+    names = _declared_symbols("mm2post_b200.h")
+    L = api.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mm2post_b200.h but not exported"
+    assert sorted(post.EXPORTED_SYMBOLS) == names
+    assert C.sizeof(post.PostParams) == 36 and post.REG_DTYPE.itemsize == 80
+
+
 def test_library_exports_every_driver_symbol():
     """include/mm2fpgadrv_b200.h: the 11 symbols the fork's objects expect from libfpgadrv.a (fpga.h:37-62)"""
     from minimap2_chaindp_b200 import fpgadrv
