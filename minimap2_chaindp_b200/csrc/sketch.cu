@@ -1,0 +1,468 @@
+// sketch.cu -- mm_sketch (sketch.c:77-143) on the device (include/mm2sketch_b200.h).
+//
+// The reference walks a read base by base with a ring of the last w k-mers and a running minimum.  The same output follows
+// from per-position quantities that need only prefix sums ("sketching"):
+//   token   one per base, or one per homopolymer run with HPC (its last base carries the run length); an ambiguous base is a token
+//   k-mer   of a valid token = the last k valid tokens (ambiguous bases do not shift the k-mer, they only reset the counters)
+//   step    a token that reaches the ring: ambiguous ones (as an empty entry) and valid ones whose k-mer is not its own reverse
+//           complement (a symmetric k-mer leaves no trace in l, the ring or its position, sketch.c:109)
+//   l       non-symmetric valid tokens since the last ambiguous base; an entry is real iff l >= k and span < 256
+//   min     before / after step s = the newest minimum of steps [s-w, s-1] / [s-w+1, s] -- the reference's `min` variable is
+//           always exactly that, so what a step pushes (the old minimum when it is replaced or leaves the window, the equal
+//           k-mers after a rescan, the first-window special case) is a function of the w+1 entries around it
+// One CTA per read walks it in tiles of 512 bases; three block scans per tile place tokens, steps and emitted minimizers.
+// A read's minimizers are first written to a slot of len entries (mm_sketch emits at most one per base), then packed.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include "mm2sketch_b200.h"
+#include "seed_internal.h"
+
+using namespace mm2b200;
+
+namespace {
+
+#define FULL 0xffffffffu
+#define SK_T 512                   // bases per tile = threads per CTA
+#define SK_HALO 256                // ring entries carried between tiles (w < 256)
+#define SK_KH 32                   // valid tokens carried between tiles (k <= 28)
+#define NONE 0xffffffffffffffffull
+
+struct SketchWork {
+	const uint8_t *seq; const int64_t *seq_off; const uint32_t *rid;
+	int32_t n_reads, w, k, is_hpc;
+	ulonglong2 *raw;               // slot of read r at seq_off[r]
+	int32_t *n_mv; int64_t *mv_off; ulonglong2 *mv; int64_t *totals;
+};
+
+__device__ __forceinline__ uint64_t hash64m(uint64_t key, uint64_t mask)     // sketch.c:27-37
+{
+	key = (~key + (key << 21)) & mask;
+	key = key ^ key >> 24;
+	key = ((key + (key << 3)) + (key << 8)) & mask;
+	key = key ^ key >> 14;
+	key = ((key + (key << 2)) + (key << 4)) & mask;
+	key = key ^ key >> 28;
+	key = (key + (key << 31)) & mask;
+	return key;
+}
+
+__device__ __forceinline__ int nt4(uint8_t ch)                               // seq_nt4_table, sketch.c:8-25
+{
+	if (ch < 4) return ch;
+	const uint8_t u = ch | 0x20;
+	return u == 'a' ? 0 : u == 'c' ? 1 : u == 'g' ? 2 : (u == 't' || u == 'u') ? 3 : 4;
+}
+
+// inclusive block scan (sum) of a 64-bit value holding up to four 16-bit counters
+__device__ __forceinline__ unsigned long long block_scan(unsigned long long v, unsigned long long *s_warp, int tid)
+{
+	const int lane = tid & 31, wid = tid >> 5;
+	for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(FULL, v, d); if (lane >= d) v += t; }
+	__syncthreads();                       // s_warp may still be read from the previous scan
+	if (lane == 31) s_warp[wid] = v;
+	__syncthreads();
+	if (wid == 0) {
+		unsigned long long x = lane < SK_T / 32 ? s_warp[lane] : 0;
+		for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(FULL, x, d); if (lane >= d) x += t; }
+		if (lane < SK_T / 32) s_warp[lane] = x;
+	}
+	__syncthreads();
+	return v + (wid ? s_warp[wid - 1] : 0);
+}
+
+__global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
+{
+	__shared__ unsigned long long sx[SK_HALO + SK_T], sy[SK_HALO + SK_T];
+	__shared__ int sl[SK_HALO + SK_T];
+	__shared__ uint8_t vcode[SK_KH + SK_T];
+	__shared__ uint16_t vskip[SK_KH + SK_T];
+	__shared__ uint16_t recV[SK_T], recS[SK_T];          // per ambiguous token of the tile: valid / non-symmetric tokens up to it
+	__shared__ unsigned long long s_warp[SK_T / 32];
+	__shared__ int c_V0, c_VN0, c_L0, c_E0;                // carried: valid tokens so far (saturated), valid / non-symmetric since the last ambiguous base, emitted
+	const int tid = threadIdx.x;
+	const int w = W.w, k = W.k, hpc = W.is_hpc;
+	const uint64_t mask = (1ULL << 2 * k) - 1;
+	const int shift1 = 2 * (k - 1);
+	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
+		const int64_t s0 = W.seq_off[r];
+		const int len = (int)(W.seq_off[r + 1] - s0);
+		const uint8_t *str = W.seq + s0;
+		ulonglong2 *out = W.raw + s0;
+		const uint32_t rid = W.rid ? W.rid[r] : 0;
+		__syncthreads();
+		if (tid < SK_HALO) { sx[tid] = NONE; sy[tid] = NONE; sl[tid] = 0; }
+		if (tid < SK_KH) { vcode[tid] = 0; vskip[tid] = 0; }
+		if (tid == 0) { c_V0 = 0; c_VN0 = 0; c_L0 = 0; c_E0 = 0; }
+		__syncthreads();
+		for (int P0 = 0; P0 < len; P0 += SK_T) {
+			// ---- tokens
+			const int p = P0 + tid;
+			const bool active = p < len;
+			const int c = active ? nt4(str[p]) : 4;
+			bool is_tok = active;
+			int skip_len = 1;
+			if (hpc && active && c < 4) {
+				const int cn = p + 1 < len ? nt4(str[p + 1]) : 5;
+				is_tok = cn != c;                            // the last base of a homopolymer run stands for the run
+				if (is_tok) while (skip_len < 256 && p - skip_len >= 0 && nt4(str[p - skip_len]) == c) ++skip_len;   // 256+ can never be a real entry (span < 256)
+			}
+			const bool valid = is_tok && c < 4, isN = is_tok && c >= 4;
+			const unsigned long long a_in = (unsigned long long)is_tok | (unsigned long long)valid << 16 | (unsigned long long)isN << 32;
+			const unsigned long long a_sc = block_scan(a_in, s_warp, tid);
+			const int valid_incl = (int)(a_sc >> 16 & 0xffff), nN_incl = (int)(a_sc >> 32 & 0xffff);
+			const int vr = valid_incl - (valid ? 1 : 0);
+			if (valid) { vcode[SK_KH + vr] = (uint8_t)c; vskip[SK_KH + vr] = (uint16_t)skip_len; }
+			if (isN) recV[nN_incl - 1] = (uint16_t)valid_incl;
+			__syncthreads();
+			// ---- k-mers of the valid tokens
+			const int V0 = c_V0, VN0 = c_VN0, L0 = c_L0, E0 = c_E0;
+			uint64_t kmer0 = 0, kmer1 = 0;
+			int span_hpc = 0;
+			bool nonsym = false;
+			if (valid) {
+				const int before = V0 + vr;                  // valid tokens before this one (saturated, only compared with j < 28)
+				const int sinceN = nN_incl > 0 ? valid_incl - (int)recV[nN_incl - 1] : VN0 + valid_incl;
+				const int nsum = sinceN < k ? sinceN : k;
+				for (int j = 0; j < k; ++j) {
+					const uint64_t code = vcode[SK_KH + vr - j];
+					kmer0 |= code << 2 * j;                  // tokens before the first one are zero here like in the reference's zero-initialised k-mer
+					if (j <= before) kmer1 |= (3ULL ^ code) << (shift1 - 2 * j);
+					if (j < nsum) span_hpc += vskip[SK_KH + vr - j];
+				}
+				nonsym = kmer0 != kmer1;
+			}
+			const bool step = isN || nonsym;
+			const unsigned long long b_sc = block_scan((unsigned long long)nonsym | (unsigned long long)step << 16, s_warp, tid);
+			const int nonsym_incl = (int)(b_sc & 0xffff), step_incl = (int)(b_sc >> 16 & 0xffff);
+			if (isN) recS[nN_incl - 1] = (uint16_t)nonsym_incl;
+			__syncthreads();
+			if (step) {
+				uint64_t ix = NONE, iy = NONE;
+				int l = 0;
+				if (nonsym) {
+					l = nN_incl > 0 ? nonsym_incl - (int)recS[nN_incl - 1] : L0 + nonsym_incl;
+					const int span = hpc ? span_hpc : (l < k ? l : k);
+					if (l >= k && span < 256) {
+						const int z = kmer0 < kmer1 ? 0 : 1;
+						ix = hash64m(z ? kmer1 : kmer0, mask) << 8 | (uint64_t)span;
+						iy = (uint64_t)rid << 32 | (uint64_t)((uint32_t)p << 1) | (uint64_t)z;
+					}
+				}
+				const int si = SK_HALO + step_incl - 1;
+				sx[si] = ix; sy[si] = iy; sl[si] = l;
+			}
+			__syncthreads();
+			// ---- what each step pushes (sketch.c:118-137)
+			__shared__ int s_tot[5];                         // tile totals: valid, ambiguous, non-symmetric tokens, steps, emissions
+			if (tid == SK_T - 1) { s_tot[0] = valid_incl; s_tot[1] = nN_incl; s_tot[2] = nonsym_incl; s_tot[3] = step_incl; }
+			__syncthreads();
+			const int n_steps = s_tot[3];
+			int cnt = 0, s = 0, l = 0, prev_i = 0, cur_i = 0;
+			uint64_t prev_x = NONE;
+			bool emitA = false, emitPrev = false, emitDup = false;
+			if (tid < n_steps) {
+				s = SK_HALO + tid;
+				l = sl[s];
+				const uint64_t info_x = sx[s];
+				prev_i = s - w;
+				prev_x = sx[s - w];
+				for (int i = s - w + 1; i < s; ++i) { const uint64_t x = sx[i]; if (x <= prev_x) { prev_x = x; prev_i = i; } }   // newest minimum of [s-w, s-1]
+				if (l == w + k - 1 && prev_x != NONE) {
+					emitA = true;
+					for (int i = s - w + 1; i < s; ++i) cnt += (sx[i] == prev_x && i != prev_i);
+				}
+				if (info_x <= prev_x) {                      // the minimum is replaced
+					if (l >= w + k && prev_x != NONE) { emitPrev = true; ++cnt; }
+				} else if (prev_i == s - w) {                // the minimum has left the window: rescan
+					if (l >= w + k - 1 && prev_x != NONE) { emitPrev = true; ++cnt; }
+					uint64_t cur_x = NONE;
+					cur_i = s;
+					for (int i = s - w + 1; i <= s; ++i) { const uint64_t x = sx[i]; if (x <= cur_x) { cur_x = x; cur_i = i; } }
+					if (l >= w + k - 1 && cur_x != NONE) {
+						emitDup = true;
+						for (int i = s - w + 1; i <= s; ++i) cnt += (sx[i] == cur_x && i != cur_i);
+					}
+				}
+			}
+			const unsigned long long e_sc = block_scan((unsigned long long)cnt, s_warp, tid);
+			if (cnt) {
+				ulonglong2 *o = out + E0 + (int)(e_sc - (unsigned long long)cnt);
+				if (emitA) for (int i = s - w + 1; i < s; ++i) if (sx[i] == prev_x && i != prev_i) *o++ = make_ulonglong2(sx[i], sy[i]);
+				if (emitPrev) *o++ = make_ulonglong2(prev_x, sy[prev_i]);
+				if (emitDup) { const uint64_t cur_x = sx[cur_i]; for (int i = s - w + 1; i <= s; ++i) if (sx[i] == cur_x && i != cur_i) *o++ = make_ulonglong2(sx[i], sy[i]); }
+			}
+			if (tid == SK_T - 1) s_tot[4] = (int)e_sc;
+			__syncthreads();
+			// ---- carry to the next tile: the last SK_HALO ring entries, the last SK_KH valid tokens, the counters
+			const int tv = s_tot[0], tn = s_tot[1], ts = s_tot[2], te = s_tot[4];
+			unsigned long long hx = 0, hy = 0; int hl = 0; uint8_t hc = 0; uint16_t hs = 0;
+			if (tid < SK_HALO) { hx = sx[n_steps + tid]; hy = sy[n_steps + tid]; hl = sl[n_steps + tid]; }
+			if (tid < SK_KH) { hc = vcode[tv + tid]; hs = vskip[tv + tid]; }
+			__syncthreads();
+			if (tid < SK_HALO) { sx[tid] = hx; sy[tid] = hy; sl[tid] = hl; }
+			if (tid < SK_KH) { vcode[tid] = hc; vskip[tid] = hs; }
+			if (tid == 0) {
+				c_V0 = V0 + tv > 64 ? 64 : V0 + tv;
+				c_VN0 = tn > 0 ? tv - (int)recV[tn - 1] : VN0 + tv;
+				c_L0 = tn > 0 ? ts - (int)recS[tn - 1] : L0 + ts;
+				c_E0 = E0 + te;
+			}
+			__syncthreads();
+		}
+		// ---- the minimum that is still current at the end of the read (sketch.c:141-142)
+		if (tid == 0) {
+			int e = c_E0;
+			uint64_t bx = NONE; int bi = SK_HALO - 1;
+			for (int i = SK_HALO - w; i < SK_HALO; ++i) if (sx[i] <= bx) { bx = sx[i]; bi = i; }
+			if (bx != NONE) out[e++] = make_ulonglong2(bx, sy[bi]);
+			W.n_mv[r] = e;
+		}
+	}
+}
+
+// exclusive scan of n_mv over the reads by one CTA
+__global__ void __launch_bounds__(1024) k_sketch_scan(SketchWork W)
+{
+	__shared__ long long s_warp[32];
+	__shared__ long long s_carry;
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	if (tid == 0) s_carry = 0;
+	__syncthreads();
+	for (int r0 = 0; r0 < W.n_reads; r0 += 1024) {
+		const int r = r0 + tid;
+		const long long v = r < W.n_reads ? W.n_mv[r] : 0;
+		long long incl = v;
+		for (int d = 1; d < 32; d <<= 1) { const long long t = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += t; }
+		if (lane == 31) s_warp[wid] = incl;
+		__syncthreads();
+		if (wid == 0) {
+			long long x = s_warp[lane];
+			for (int d = 1; d < 32; d <<= 1) { const long long t = __shfl_up_sync(FULL, x, d); if (lane >= d) x += t; }
+			s_warp[lane] = x;
+		}
+		__syncthreads();
+		const long long before = s_carry + (wid ? s_warp[wid - 1] : 0) + incl - v;
+		if (r < W.n_reads) W.mv_off[r] = before;
+		__syncthreads();
+		if (tid == 1023) s_carry = before + v;
+		__syncthreads();
+	}
+	if (tid == 0) { W.mv_off[W.n_reads] = s_carry; W.totals[0] = s_carry; }
+}
+
+__global__ void __launch_bounds__(256) k_sketch_pack(SketchWork W)
+{
+	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
+		const int n = W.n_mv[r];
+		const ulonglong2 *src = W.raw + W.seq_off[r];
+		ulonglong2 *dst = W.mv + W.mv_off[r];
+		for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+	}
+}
+
+inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
+
+struct Buf {
+	void *p = nullptr; size_t cap = 0; bool pinned = false;
+	int reserve(size_t bytes);
+	void release() { if (p) { if (pinned) cudaFreeHost(p); else cudaFree(p); } p = nullptr; cap = 0; }
+};
+
+int failf(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
+int failf(int code, const char *fmt, ...)
+{
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	return api_fail(code, buf);
+}
+#define CU_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+	return failf(MM2B200_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+int Buf::reserve(size_t bytes)
+{
+	if (p && bytes <= cap) return MM2B200_OK;
+	release();
+	const size_t want = bytes + bytes / 8 + 4096;
+	const cudaError_t e = pinned ? cudaHostAlloc(&p, want, cudaHostAllocDefault) : cudaMalloc(&p, want);
+	if (e != cudaSuccess) { cudaGetLastError(); p = nullptr; return failf(MM2B200_ERR_NOMEM, "%s(%zu bytes) failed in the sketching stage", pinned ? "cudaHostAlloc" : "cudaMalloc", want); }
+	cap = want;
+	return MM2B200_OK;
+}
+
+struct SketchState {
+	int device = 0;
+	std::mutex mu;
+	cudaStream_t stream = nullptr;
+	Buf d_raw, d_mv, d_small, d_in;
+	Buf h_off, h_mv, h_tot;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	double ms = 0; int64_t launches = 0;
+	SketchState() { h_off.pinned = h_mv.pinned = h_tot.pinned = true; }
+};
+
+void sketch_state_free(void *p)
+{
+	SketchState *s = (SketchState*)p;
+	cudaSetDevice(s->device);
+	if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+	for (Buf *b : { &s->d_raw, &s->d_mv, &s->d_small, &s->d_in, &s->h_off, &s->h_mv, &s->h_tot }) b->release();
+	if (s->ev0) cudaEventDestroy(s->ev0);
+	if (s->ev1) cudaEventDestroy(s->ev1);
+	delete s;
+}
+
+std::mutex g_state_mu;
+SketchState *sketch_state(mm2b200_ctx_t *ctx)
+{
+	std::lock_guard<std::mutex> lk(g_state_mu);
+	SketchState *s = (SketchState*)ctx_ext(ctx, 1);
+	if (!s) {
+		s = new SketchState();
+		s->device = ctx_device(ctx);
+		ctx_set_ext(ctx, 1, s, sketch_state_free);
+	}
+	return s;
+}
+
+int check_sketch(const mm2b200_sketch_params_t *prm)
+{
+	if (!prm) return failf(MM2B200_ERR_ARG, "sketching parameters are NULL");
+	if (prm->w <= 0 || prm->w >= 256 || prm->k <= 0 || prm->k > 28)            // the assert of sketch.c:84
+		return failf(MM2B200_ERR_ARG, "mm_sketch needs 0 < w < 256 and 0 < k <= 28 (w %d, k %d)", prm->w, prm->k);
+	return MM2B200_OK;
+}
+
+// kernels on `st`; waits once for the count; leaves the packing on the stream
+int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases,
+                       const int64_t *d_seq_off, const char *d_seq, const uint32_t *d_rid, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv)
+{
+	int rc;
+	const size_t R = (size_t)n_reads;
+	if ((rc = s->d_raw.reserve(16 * ((size_t)n_bases + 1))) || (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256)) ||
+	    (rc = s->h_tot.reserve(64))) return rc;
+	SketchWork W;
+	memset(&W, 0, sizeof(W));
+	W.seq = (const uint8_t*)d_seq; W.seq_off = d_seq_off; W.rid = d_rid;
+	W.n_reads = (int32_t)n_reads; W.w = prm->w; W.k = prm->k; W.is_hpc = prm->is_hpc ? 1 : 0;
+	W.raw = (ulonglong2*)s->d_raw.p;
+	char *cur = (char*)s->d_small.p;
+	W.n_mv = (int32_t*)cur; cur += up256(4 * (R + 1));
+	W.mv_off = (int64_t*)cur; cur += up256(8 * (R + 2));
+	W.totals = (int64_t*)cur;
+	const bool prof = ctx_profile(ctx) != 0;
+	if (prof) {
+		if (!s->ev0) { CU_TRY(cudaEventCreate(&s->ev0)); CU_TRY(cudaEventCreate(&s->ev1)); }
+		CU_TRY(cudaEventRecord(s->ev0, st));
+	}
+	int64_t total = 0;
+	int launches = 0;
+	if (n_reads > 0) {
+		const int sm = ctx_sm_count(ctx);
+		int grid = (int)(n_reads < (int64_t)sm * 4 ? n_reads : (int64_t)sm * 4);
+		k_sketch<<<grid, SK_T, 0, st>>>(W);
+		k_sketch_scan<<<1, 1024, 0, st>>>(W);
+		CU_TRY(cudaGetLastError());
+		CU_TRY(cudaMemcpyAsync(s->h_tot.p, W.totals, 8, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaStreamSynchronize(st));
+		total = *(int64_t*)s->h_tot.p;
+		if ((rc = s->d_mv.reserve(16 * ((size_t)total + 1)))) return rc;
+		W.mv = (ulonglong2*)s->d_mv.p;
+		k_sketch_pack<<<grid, 256, 0, st>>>(W);
+		CU_TRY(cudaGetLastError());
+		launches = 3;
+	} else {
+		if ((rc = s->d_mv.reserve(16))) return rc;
+		CU_TRY(cudaMemsetAsync(W.mv_off, 0, 8, st));
+		CU_TRY(cudaMemsetAsync(W.totals, 0, 64, st));
+	}
+	if (prof) CU_TRY(cudaEventRecord(s->ev1, st));
+	s->launches += launches;
+	ctx_add_launches(ctx, launches);
+	out->d_mv_off = W.mv_off; out->d_mv = (const mm128_t*)s->d_mv.p; out->d_totals = W.totals;
+	if (n_mv) *n_mv = total;
+	return MM2B200_OK;
+}
+
+void sketch_account(mm2b200_ctx_t *ctx, SketchState *s)
+{
+	if (ctx_profile(ctx) && s->ev0) {
+		float t = 0;
+		if (cudaEventElapsedTime(&t, s->ev0, s->ev1) == cudaSuccess) s->ms += t;
+		cudaGetLastError();
+	}
+}
+
+} // namespace
+
+extern "C" int mm2b200_sketch_device(mm2b200_ctx_t *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
+                                     const char *d_seq, const uint32_t *d_rid, void *stream, mm2b200_dev_sketch_t *out, int64_t *n_mv)
+{
+	int rc;
+	if (!ctx || !out) return failf(MM2B200_ERR_ARG, "NULL ctx or result");
+	if ((rc = check_sketch(prm))) return rc;
+	if (n_reads < 0 || n_bases < 0 || !d_seq_off || (n_bases && !d_seq)) return failf(MM2B200_ERR_ARG, "bad sketching arguments");
+	SketchState *s = sketch_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	CU_TRY(cudaSetDevice(s->device));
+	return sketch_device_impl(ctx, s, prm, n_reads, n_bases, d_seq_off, d_seq, d_rid, (cudaStream_t)stream, out, n_mv);
+}
+
+extern "C" int mm2b200_sketch_stage_ms(mm2b200_ctx_t *ctx, double *ms, int64_t *launches)
+{
+	if (!ctx) return failf(MM2B200_ERR_ARG, "NULL context");
+	SketchState *s = sketch_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	if (ms) *ms = s->ms;
+	if (launches) *launches = s->launches;
+	return MM2B200_OK;
+}
+
+extern "C" int mm2b200_sketch_batch(mm2b200_ctx_t *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, const int64_t *seq_off,
+                                    const char *seq, const uint32_t *rid, mm2b200_sketch_result_t *res)
+{
+	int rc;
+	if (!ctx || !res) return failf(MM2B200_ERR_ARG, "NULL ctx or result");
+	if ((rc = check_sketch(prm))) return rc;
+	if (n_reads < 0 || (n_reads && !seq_off)) return failf(MM2B200_ERR_ARG, "bad batch arguments");
+	for (int64_t r = 0; r < n_reads; ++r) {
+		if (seq_off[r + 1] < seq_off[r]) return failf(MM2B200_ERR_ARG, "seq_off is not non-decreasing at read %lld", (long long)r);
+		if (seq_off[r + 1] - seq_off[r] >= ((int64_t)1 << 31) - 1) return failf(MM2B200_ERR_ARG, "read %lld is longer than mm_sketch's int length", (long long)r);
+	}
+	const int64_t b0 = n_reads ? seq_off[0] : 0, B = n_reads ? seq_off[n_reads] - b0 : 0;
+	if (B && !seq) return failf(MM2B200_ERR_ARG, "NULL sequence array");
+	SketchState *s = sketch_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	memset(res, 0, sizeof(*res));
+	CU_TRY(cudaSetDevice(s->device));
+	if (!s->stream) CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+	cudaStream_t st = s->stream;
+	const size_t R = (size_t)n_reads;
+	if ((rc = s->d_in.reserve(up256((size_t)B + 16) + up256(8 * (R + 1)) + up256(4 * (R + 1)))) || (rc = s->h_off.reserve(16 * (R + 1) + 64))) return rc;
+	char *cur = (char*)s->d_in.p;
+	char *d_seq = cur; cur += up256((size_t)B + 16);
+	int64_t *d_off = (int64_t*)cur; cur += up256(8 * (R + 1));
+	uint32_t *d_rid = rid ? (uint32_t*)cur : nullptr;
+	int64_t *h_off = (int64_t*)s->h_off.p;
+	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? seq_off[r] - b0 : 0;
+	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	if (B) CU_TRY(cudaMemcpyAsync(d_seq, seq + b0, (size_t)B, cudaMemcpyHostToDevice, st));
+	if (rid && R) CU_TRY(cudaMemcpyAsync(d_rid, rid, 4 * R, cudaMemcpyHostToDevice, st));
+	mm2b200_dev_sketch_t dev;
+	int64_t total = 0;
+	if ((rc = sketch_device_impl(ctx, s, prm, n_reads, B, d_off, d_seq, d_rid, st, &dev, &total))) return rc;
+	if ((rc = s->h_mv.reserve(16 * ((size_t)total + 1)))) return rc;
+	int64_t *h_mv_off = h_off + (R + 1);
+	CU_TRY(cudaMemcpyAsync(h_mv_off, dev.d_mv_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	if (total) CU_TRY(cudaMemcpyAsync(s->h_mv.p, dev.d_mv, 16 * (size_t)total, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	sketch_account(ctx, s);
+	res->n_reads = n_reads; res->mv_off = h_mv_off; res->mv = (const mm128_t*)s->h_mv.p;
+	return MM2B200_OK;
+}

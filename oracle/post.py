@@ -90,6 +90,16 @@ def ref_sketch(seq: bytes, w: int, k: int, rid: int = 0, is_hpc: bool = False) -
     return out[:n].copy()
 
 
+def sketch(seq: bytes, w: int, k: int, rid: int = 0, is_hpc: bool = False) -> np.ndarray:
+    """mm_sketch from the restatement (sketch_oracle.c)"""
+    L = oracle_lib()
+    L.orc_sketch.restype = C.c_int64
+    L.orc_sketch.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_int, C.c_void_p]
+    out = np.zeros((len(seq) + 1, 2), np.uint64)
+    n = L.orc_sketch(seq, len(seq), w, k, rid, int(is_hpc), out.ctypes.data)
+    return out[:n].copy()
+
+
 def ref_preset(name: str = "") -> Preset:
     p = Preset()
     if ref_lib().ref_preset(name.encode(), C.byref(p)) != 0:

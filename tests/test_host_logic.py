@@ -50,6 +50,15 @@ def test_library_exports_every_post_processing_symbol():
     assert C.sizeof(post.PostParams) == 36 and post.REG_DTYPE.itemsize == 80
 
 
+def test_library_exports_every_sketching_symbol():
+    from minimap2_chaindp_b200 import sketch
+    names = _declared_symbols("mm2sketch_b200.h")
+    L = api.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mm2sketch_b200.h but not exported"
+    assert sorted(sketch.EXPORTED_SYMBOLS) == names
+
+
 def test_library_exports_every_driver_symbol():
     """include/mm2fpgadrv_b200.h: the 11 symbols the fork's objects expect from libfpgadrv.a (fpga.h:37-62)"""
     from minimap2_chaindp_b200 import fpgadrv
