@@ -39,7 +39,7 @@ def _stale(target: str, sources) -> bool:
 
 CU_SOURCES = ("chain_kernels.cu", "chain_api.cu", "seed_kernels.cu", "seed_api.cu", "fpgadrv_shim.cu", "post.cu", "sketch.cu")
 CU_HEADERS = ("chain_internal.h", "seed_internal.h", "sort_exact.cuh", "packet_format.h")
-API_HEADERS = ("mm2chain_b200.h", "mm2seed_b200.h", "mm2fpgadrv_b200.h", "mm2post_b200.h", "mm2sketch_b200.h")
+API_HEADERS = ("mm2chain_b200.h", "mm2seed_b200.h", "mm2fpgadrv_b200.h", "mm2post_b200.h", "mm2sketch_b200.h", "mm2map_b200.h")
 OBJ_DIR = os.path.join(PKG, "_obj")
 
 

@@ -15,6 +15,7 @@
 #include <vector>
 #include "seed_internal.h"
 #include "packet_format.h"
+#include "mm2map_b200.h"
 
 using namespace mm2b200;
 
@@ -91,6 +92,8 @@ struct mm2b200_index {
 	DevBuf d_in, d_work, d_anchor;
 	PinBuf h_stage, h_totals, h_rep, h_mini_off, h_mini, h_a_off, h_a;
 	PinBuf h_n_u, h_u_off, h_b_off, h_u, h_b, h_rec_off, h_rec;
+	DevBuf d_reads;                        // mm2b200_map_regs_batch: bases, offsets, bid, hash, qlen
+	PinBuf h_reg_off, h_regs;
 	int64_t launches = 0;
 	cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
 	double ms[3] = { 0, 0, 0 };
@@ -121,7 +124,8 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	cudaSetDevice(ix->device);
 	if (ix->stream) cudaStreamSynchronize(ix->stream);
 	for (auto &b : ix->d_stream) b.release();
-	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release();
+	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release(); ix->d_reads.release();
+	ix->h_reg_off.release(); ix->h_regs.release();
 	for (PinBuf *b : { &ix->h_stage, &ix->h_totals, &ix->h_rep, &ix->h_mini_off, &ix->h_mini, &ix->h_a_off, &ix->h_a,
 	                   &ix->h_n_u, &ix->h_u_off, &ix->h_b_off, &ix->h_u, &ix->h_b, &ix->h_rec_off, &ix->h_rec }) b->release();
 	for (auto &e : ix->ev) if (e) cudaEventDestroy(e);
@@ -222,19 +226,23 @@ int check_seed_args(const mm2b200_index *ix, const mm2b200_seed_params_t *prm, i
 
 // uploads the batch, runs lookup -> (sync for the anchor count) -> expand -> sort on ix->stream.  On return the sorted
 // anchors and their offsets are in HBM (out.w.a, out.w.a_off) and the stream holds the remaining work.
+// dev_n_mv < 0: mv_off / mv / bid / qlen are host arrays (uploaded here).  dev_n_mv >= 0: they are DEVICE arrays holding
+// dev_n_mv minimizers with mv_off[0] = 0 (the sketching stage left them in HBM); host_meta = false then also skips the
+// download of rep_len / mini_pos / offsets (the caller takes what it needs from out.w).
 int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_reads, const int64_t *mv_off, const mm128_t *mv,
-               const uint32_t *bid, const int32_t *qlen, SeedOut &out)
+               const uint32_t *bid, const int32_t *qlen, SeedOut &out, int64_t dev_n_mv = -1, bool host_meta = true)
 {
 	int rc;
 	CU_TRY(cudaSetDevice(ix->device));
 	cudaStream_t st = ix->stream;
-	const int64_t m_base = n_reads ? mv_off[0] : 0;
-	const int64_t n_mv = n_reads ? mv_off[n_reads] - m_base : 0;
+	const bool on_device = dev_n_mv >= 0;
+	const int64_t m_base = on_device ? 0 : (n_reads ? mv_off[0] : 0);
+	const int64_t n_mv = on_device ? dev_n_mv : (n_reads ? mv_off[n_reads] - m_base : 0);
 	const size_t R = (size_t)n_reads, M = (size_t)n_mv;
 	SeedWork &w = out.w;
 	// inputs
-	ulonglong2 *d_mv; int64_t *d_mv_off; uint32_t *d_bid; int32_t *d_qlen;
-	{
+	ulonglong2 *d_mv = nullptr; int64_t *d_mv_off = nullptr; uint32_t *d_bid = nullptr; int32_t *d_qlen = nullptr;
+	if (!on_device) {
 		Carver c;
 		c.add(&d_mv, 16 * (M + 1)); c.add(&d_mv_off, 8 * (R + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
 		if ((rc = ix->d_in.reserve(c.total()))) return rc;
@@ -249,17 +257,21 @@ int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_re
 		if ((rc = ix->d_work.reserve(c.total()))) return rc;
 		c.place(ix->d_work.p);
 	}
-	// offsets relative to the first minimizer of the batch, staged in pinned memory together with bid / qlen
-	if ((rc = ix->h_stage.reserve(8 * (R + 1) + 8 * (R + 1)))) return rc;
-	int64_t *h_off = ix->h_stage.as<int64_t>();
-	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? mv_off[r] - m_base : 0;
-	CU_TRY(cudaMemcpyAsync(d_mv_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
-	if (R) {
-		CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
-		CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
+	if (on_device) {
+		w.mv = (const ulonglong2*)mv; w.mv_off = mv_off; w.bid = bid; w.qlen = qlen;
+	} else {
+		// offsets relative to the first minimizer of the batch, staged in pinned memory together with bid / qlen
+		if ((rc = ix->h_stage.reserve(8 * (R + 1) + 8 * (R + 1)))) return rc;
+		int64_t *h_off = ix->h_stage.as<int64_t>();
+		for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? mv_off[r] - m_base : 0;
+		CU_TRY(cudaMemcpyAsync(d_mv_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+		if (R) {
+			CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
+			CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
+		}
+		if (M) CU_TRY(cudaMemcpyAsync(d_mv, mv + m_base, 16 * M, cudaMemcpyHostToDevice, st));
+		w.mv = d_mv; w.mv_off = d_mv_off; w.bid = d_bid; w.qlen = d_qlen;
 	}
-	if (M) CU_TRY(cudaMemcpyAsync(d_mv, mv + m_base, 16 * M, cudaMemcpyHostToDevice, st));
-	w.mv = d_mv; w.mv_off = d_mv_off; w.bid = d_bid; w.qlen = d_qlen;
 	w.n_reads = (int32_t)n_reads; w.n_mv = n_mv;
 	w.flag = prm->flag; w.max_occ = prm->max_occ;
 	const bool prof = ctx_profile(ix->ctx) != 0;
@@ -291,6 +303,7 @@ int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_re
 		if (prof) CU_TRY(cudaEventRecord(ix->ev[3], st));
 	}
 	CU_TRY(cudaGetLastError());
+	if (!host_meta) return MM2B200_OK;
 	// what the host always gets from this stage: rep_len, mini_pos, anchor offsets
 	if ((rc = ix->h_rep.reserve(4 * (R + 1))) || (rc = ix->h_mini_off.reserve(8 * (R + 1))) || (rc = ix->h_a_off.reserve(8 * (R + 1))) ||
 	    (rc = ix->h_mini.reserve(8 * ((size_t)out.n_mini + 1)))) return rc;
@@ -510,5 +523,78 @@ extern "C" int mm2b200_seed_work(mm2b200_index_t *ix, const mm2b200_seed_params_
 		o += mini_b;
 	}
 	*resp_size = need;
+	return MM2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// bases in, regions out: sketching -> seeding -> chaining DP -> region post-processing, all in HBM (include/mm2map_b200.h)
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_params_t *sk, const mm2b200_seed_params_t *prm,
+                                      const mm2b200_post_params_t *post, int64_t n_reads, const int64_t *seq_off, const char *seq,
+                                      const uint32_t *bid, const uint32_t *hash, mm2b200_map_result_t *res)
+{
+	int rc;
+	if (!ix || !sk || !prm || !post || !res) return failf(MM2B200_ERR_ARG, "NULL argument");
+	if (!ix->committed) return failf(MM2B200_ERR_STATE, "index not committed (mm2b200_index_commit)");
+	if (n_reads < 0 || n_reads >= ((int64_t)1 << 31) - 1 || (n_reads && (!seq_off || !bid || !hash))) return failf(MM2B200_ERR_ARG, "bad batch arguments");
+	if (prm->chain.n_segs > 1) return failf(MM2B200_ERR_ARG, "multi-segment reads (n_segs = %d) are outside this path", prm->chain.n_segs);
+	for (int64_t r = 0; r < n_reads; ++r) {
+		if (seq_off[r + 1] < seq_off[r]) return failf(MM2B200_ERR_ARG, "seq_off is not non-decreasing at read %lld", (long long)r);
+		if (seq_off[r + 1] - seq_off[r] >= ((int64_t)1 << 31) - 1) return failf(MM2B200_ERR_ARG, "read %lld is longer than mm_sketch's int length", (long long)r);
+	}
+	const int64_t b0 = n_reads ? seq_off[0] : 0, B = n_reads ? seq_off[n_reads] - b0 : 0;
+	if (B && !seq) return failf(MM2B200_ERR_ARG, "NULL sequence array");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	memset(res, 0, sizeof(*res));
+	CU_TRY(cudaSetDevice(ix->device));
+	cudaStream_t st = ix->stream;
+	const size_t R = (size_t)n_reads;
+	char *d_seq; int64_t *d_off; uint32_t *d_bid, *d_hash; int32_t *d_qlen;
+	{
+		Carver c;
+		c.add(&d_seq, (size_t)B + 16); c.add(&d_off, 8 * (R + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_hash, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
+		if ((rc = ix->d_reads.reserve(c.total()))) return rc;
+		c.place(ix->d_reads.p);
+	}
+	if ((rc = ix->h_stage.reserve(8 * (R + 1) + 4 * (R + 1)))) return rc;
+	int64_t *h_off = ix->h_stage.as<int64_t>();
+	int32_t *h_qlen = (int32_t*)(h_off + (R + 1));
+	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? seq_off[r] - b0 : 0;
+	for (size_t r = 0; r < R; ++r) h_qlen[r] = (int32_t)(seq_off[r + 1] - seq_off[r]);      // qlen_sum of a single-segment read (map.c:340-341)
+	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	if (R) {
+		CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, st));
+		CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
+		CU_TRY(cudaMemcpyAsync(d_hash, hash, 4 * R, cudaMemcpyHostToDevice, st));
+	}
+	if (B) CU_TRY(cudaMemcpyAsync(d_seq, seq + b0, (size_t)B, cudaMemcpyHostToDevice, st));
+	// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0
+	mm2b200_dev_sketch_t dsk;
+	int64_t n_mv = 0;
+	if ((rc = mm2b200_sketch_device(ix->ctx, sk, n_reads, B, d_off, d_seq, nullptr, st, &dsk, &n_mv))) return rc;
+	// collect_seed_hits (map.c:187-236) on the minimizers where the sketch left them
+	SeedOut so;
+	if ((rc = seed_stage(ix, prm, n_reads, dsk.d_mv_off, dsk.d_mv, d_bid, d_qlen, so, n_mv, false))) return rc;
+	// mm_chain_dp, then mm_gen_regs + chain_post (map.c:837-866)
+	mm2b200_dev_result_t dev;
+	if ((rc = mm2b200_chain_device(ix->ctx, &prm->chain, n_reads, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
+	const int64_t cap = so.n_anchors / (prm->chain.min_cnt > 1 ? prm->chain.min_cnt : 1) + 1;
+	mm2b200_dev_regs_t dr;
+	if ((rc = mm2b200_post_device(ix->ctx, post, n_reads, &dev, cap, d_hash, d_qlen, st, &dr))) return rc;
+	int64_t *tot = ix->h_totals.as<int64_t>() + ST_TOTALS;
+	if ((rc = ix->h_reg_off.reserve(8 * (R + 1))) || (rc = ix->h_rep.reserve(4 * (R + 1)))) return rc;
+	CU_TRY(cudaMemcpyAsync(tot, dr.d_totals, 8, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(tot + 1, dev.d_totals, 16, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(ix->h_reg_off.p, dr.d_reg_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	if (R) CU_TRY(cudaMemcpyAsync(ix->h_rep.p, so.w.rep_len, 4 * R, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	const size_t n_regs = (size_t)tot[0];
+	if ((rc = ix->h_regs.reserve(sizeof(mm2b200_reg_t) * (n_regs + 1)))) return rc;
+	if (n_regs) CU_TRY(cudaMemcpyAsync(ix->h_regs.p, dr.d_regs, sizeof(mm2b200_reg_t) * n_regs, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaStreamSynchronize(st));
+	seed_finish(ix, so);
+	res->n_reads = n_reads; res->reg_off = ix->h_reg_off.as<int64_t>(); res->regs = (const mm2b200_reg_t*)ix->h_regs.p;
+	res->rep_len = ix->h_rep.as<int32_t>();
+	res->n_minimizers = n_mv; res->n_anchors = so.n_anchors; res->n_chains = tot[1];
 	return MM2B200_OK;
 }

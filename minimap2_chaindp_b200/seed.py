@@ -28,6 +28,8 @@ EXPORTED_SYMBOLS = (
     "mm2b200_seed_chain_batch", "mm2b200_seed_fill_batch", "mm2b200_seed_work",
     "mm2b200_seed_launch_count", "mm2b200_seed_stage_ms",
 )
+# include/mm2map_b200.h
+MAP_EXPORTED_SYMBOLS = ("mm2b200_map_regs_batch",)
 
 
 class SeedParams(C.Structure):
@@ -43,6 +45,21 @@ class _SeedResult(C.Structure):
 class _SeedRecords(C.Structure):
     _fields_ = [("n_anchors", C.c_int64), ("rec_off", C.c_void_p), ("rec", C.c_void_p), ("rep_len", C.c_void_p),
                 ("mini_off", C.c_void_p), ("mini_pos", C.c_void_p)]
+
+
+class _MapResult(C.Structure):
+    _fields_ = [("n_reads", C.c_int64), ("reg_off", C.c_void_p), ("regs", C.c_void_p), ("rep_len", C.c_void_p),
+                ("n_minimizers", C.c_int64), ("n_anchors", C.c_int64), ("n_chains", C.c_int64)]
+
+
+@dataclass
+class MapBatch:
+    reg_off: np.ndarray
+    regs: np.ndarray
+    rep_len: np.ndarray
+    n_minimizers: int
+    n_anchors: int
+    n_chains: int
 
 
 _bound = False
@@ -65,6 +82,7 @@ def _lib():
         L.mm2b200_seed_launch_count.argtypes = [vp]
         L.mm2b200_seed_launch_count.restype = i64
         L.mm2b200_seed_stage_ms.argtypes = [vp] + [C.POINTER(C.c_double)] * 3
+        L.mm2b200_map_regs_batch.argtypes = [vp, vp, C.POINTER(SeedParams), vp, i64, vp, vp, vp, vp, C.POINTER(_MapResult)]
         _bound = True
     return L
 
@@ -187,6 +205,24 @@ class SeedIndex:
         n = C.c_int64()
         _check(_lib().mm2b200_seed_work(self._h, C.byref(prm), req.ctypes.data, req.size, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value].tobytes()
+
+    def map_regs_batch(self, sketch_prm, prm: SeedParams, post_prm, seq_off, seq, bid, hash_) -> MapBatch:
+        """bases in, regions out (include/mm2map_b200.h): mm_sketch -> collect_seed_hits -> mm_chain_dp -> mm_gen_regs + chain_post.
+        ``sketch_prm`` / ``post_prm`` are sketch.SketchParams / post.PostParams; ``raw_call`` of the same is used by bench.py."""
+        from .post import REG_DTYPE
+        seq_off = np.ascontiguousarray(seq_off, np.int64)
+        seq = np.ascontiguousarray(seq, np.uint8)
+        nr = seq_off.shape[0] - 1
+        bid = np.ascontiguousarray(np.asarray(bid, dtype=np.int64) & 0xffffffff, dtype=np.uint32)
+        hash_ = np.ascontiguousarray(np.asarray(hash_, dtype=np.int64) & 0xffffffff, dtype=np.uint32)
+        assert bid.shape[0] == nr and hash_.shape[0] == nr
+        res = _MapResult()
+        _check(_lib().mm2b200_map_regs_batch(self._h, C.byref(sketch_prm), C.byref(prm), C.byref(post_prm), nr, seq_off.ctypes.data,
+                                             seq.ctypes.data if seq.size else None, bid.ctypes.data, hash_.ctypes.data, C.byref(res)))
+        reg_off = _view(res.reg_off, nr + 1, np.int64)
+        return MapBatch(reg_off=reg_off, regs=_view(res.regs, int(reg_off[-1]) if reg_off.size else 0, REG_DTYPE),
+                        rep_len=_view(res.rep_len, nr, np.int32), n_minimizers=int(res.n_minimizers), n_anchors=int(res.n_anchors),
+                        n_chains=int(res.n_chains))
 
     def launch_count(self) -> int:
         return int(_lib().mm2b200_seed_launch_count(self._h))

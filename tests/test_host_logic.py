@@ -59,6 +59,14 @@ def test_library_exports_every_sketching_symbol():
     assert sorted(sketch.EXPORTED_SYMBOLS) == names
 
 
+def test_library_exports_the_composed_entry():
+    from minimap2_chaindp_b200 import seed
+    names = _declared_symbols("mm2map_b200.h")
+    assert names == sorted(seed.MAP_EXPORTED_SYMBOLS)
+    for n in names:
+        assert hasattr(api.lib(), n)
+
+
 def test_library_exports_every_driver_symbol():
     """include/mm2fpgadrv_b200.h: the 11 symbols the fork's objects expect from libfpgadrv.a (fpga.h:37-62)"""
     from minimap2_chaindp_b200 import fpgadrv
