@@ -68,6 +68,8 @@ void wls_free(wls_t *w)
 	free(w->hash); free(w->pos); free(w->B); free(w->H); free(w->V); free(w->P); free(w);
 }
 
+static void wls_layout(wls_t *w);
+
 wls_t *wls_build(const wls_spec_t *sp)
 {
 	const int64_t N = sp->n_sites;
@@ -93,7 +95,17 @@ wls_t *wls_build(const wls_spec_t *sp)
 		}
 	}
 	free(hot);
-	/* 2. group by (bucket, key): sort by (hash with the bucket bits on top) so that buckets come out in order */
+	wls_layout(w);
+	return w;
+}
+
+/* 2. the four streams from w->hash[] / w->pos[] */
+static void wls_layout(wls_t *w)
+{
+	const wls_spec_t *sp = &w->sp;
+	const int64_t N = sp->n_sites;
+	int64_t i;
+	/* group by (bucket, key): sort by (hash with the bucket bits on top) so that buckets come out in order */
 	hs_t *hs = (hs_t*)malloc(sizeof(hs_t) * (size_t)(N + 1));
 	const uint64_t bmask = (1ULL << sp->b) - 1;
 	for (i = 0; i < N; ++i) { const uint64_t h = w->hash[i]; hs[i].h = (h & bmask) << (64 - sp->b) | h >> sp->b; hs[i].i = i; }
@@ -167,6 +179,20 @@ wls_t *wls_build(const wls_spec_t *sp)
 		memcpy(w->B + 16 * k, rec, 16);
 	}
 	free(hs); free(bk_beg); free(slot0); free(p0); free(nbk);
+}
+
+/* An index over caller-supplied sites (hash = minimizer value, pos = packed position): what mm_idx_gen would build from the
+ * sketch of a reference (index.c:340-416), laid out like above.  Takes copies. */
+wls_t *wls_build_sites(int32_t b, int32_t hash_bits, int64_t n_sites, const uint64_t *hash, const uint64_t *pos)
+{
+	wls_t *w = (wls_t*)calloc(1, sizeof(wls_t));
+	if (!w) return 0;
+	w->sp.n_sites = n_sites; w->sp.b = b; w->sp.hash_bits = hash_bits;
+	w->hash = (uint64_t*)malloc(8 * (size_t)(n_sites + 1));
+	w->pos = (uint64_t*)malloc(8 * (size_t)(n_sites + 1));
+	memcpy(w->hash, hash, 8 * (size_t)n_sites);
+	memcpy(w->pos, pos, 8 * (size_t)n_sites);
+	wls_layout(w);
 	return w;
 }
 
@@ -240,4 +266,83 @@ void wls_reads_fill(const wls_t *w, const wls_reads_t *rs, int64_t first, int64_
 {
 	#pragma omp parallel for schedule(dynamic, 64)
 	for (int64_t r = 0; r < n_reads; ++r) wls_one(w, rs, first + r, mv + 2 * mv_off[r], 0, 0);
+}
+
+
+/* ---- "G-seq": a synthetic genome and reads sampled from it, as BASES (rows f4 + f1 + DP + f3 composed) ------------------ */
+typedef struct {
+	uint64_t seed;
+	int32_t n_contigs, contig_len;      /* contig_len < 2^21 (the fork packs refpos in 21 bits) */
+	double  p_repeat;                   /* share of the genome overwritten by copies of earlier 2-6 kb segments */
+	int32_t read_len;                   /* bases taken from the genome per read, before errors */
+	double  err;                        /* per-base error rate, one third each substitution / insertion / deletion */
+} wlg_spec_t;
+
+/* genome[n_contigs * contig_len], contig c at c * contig_len */
+void wlg_genome(const wlg_spec_t *sp, char *genome)
+{
+	const int64_t G = (int64_t)sp->n_contigs * sp->contig_len;
+	#pragma omp parallel for schedule(static)
+	for (int64_t c = 0; c < sp->n_contigs; ++c) {
+		uint64_t rng = sp->seed ^ (0x6E0ULL + (uint64_t)c) * 0x9E3779B97F4A7C15ULL;
+		char *g = genome + c * sp->contig_len;
+		for (int32_t i = 0; i < sp->contig_len; i += 32) {
+			uint64_t v = sm64(&rng);
+			for (int32_t j = 0; j < 32 && i + j < sp->contig_len; ++j, v >>= 2) g[i + j] = "ACGT"[v & 3];
+		}
+	}
+	{	/* repeats: serial, so that a copy can itself be copied */
+		uint64_t rng = sp->seed ^ 0x4E9EA7ULL;
+		int64_t todo = (int64_t)(sp->p_repeat * (double)G);
+		while (todo > 0) {
+			const int64_t len = 2000 + (int64_t)smbelow(&rng, 4000);
+			const int64_t cs = (int64_t)smbelow(&rng, (uint64_t)sp->n_contigs), cd = (int64_t)smbelow(&rng, (uint64_t)sp->n_contigs);
+			if (len + 1 >= sp->contig_len) break;
+			const int64_t ps = (int64_t)smbelow(&rng, (uint64_t)(sp->contig_len - len)), pd = (int64_t)smbelow(&rng, (uint64_t)(sp->contig_len - len));
+			memmove(genome + cd * sp->contig_len + pd, genome + cs * sp->contig_len + ps, (size_t)len);
+			todo -= len;
+		}
+	}
+}
+
+/* one read; returns its length; writes the bases if out != NULL */
+static int64_t wlg_one(const wlg_spec_t *sp, const char *genome, int64_t read_id, char *out, uint32_t *bid)
+{
+	uint64_t rng = sp->seed ^ (uint64_t)(read_id + 1) * 0xD1B54A32D192ED03ULL;
+	const int64_t c = (int64_t)smbelow(&rng, (uint64_t)sp->n_contigs);
+	const int64_t L = sp->read_len < sp->contig_len ? sp->read_len : sp->contig_len;
+	const int64_t p = (int64_t)smbelow(&rng, (uint64_t)(sp->contig_len - L + 1));
+	const int rev = (int)(sm64(&rng) & 1);
+	const char *g = genome + c * sp->contig_len + p;
+	const double e3 = sp->err / 3.0;
+	int64_t n = 0;
+	if (bid) *bid = (uint32_t)((c + 1 + (int64_t)smbelow(&rng, 7)) % (sp->n_contigs > 1 ? sp->n_contigs : 1));
+	else (void)smbelow(&rng, 7);
+	for (int64_t i = 0; i < L; ++i) {
+		const int64_t src = rev ? L - 1 - i : i;
+		char ch = g[src];
+		if (rev) ch = ch == 'A' ? 'T' : ch == 'C' ? 'G' : ch == 'G' ? 'C' : 'A';
+		const double u = sm01(&rng);
+		if (u < e3) continue;                                                   /* deletion */
+		if (u < 2 * e3) ch = "ACGT"[sm64(&rng) & 3];                             /* substitution (may be silent) */
+		else if (u < 3 * e3) { if (out) out[n] = "ACGT"[sm64(&rng) & 3]; ++n; } /* insertion in front */
+		if (out) out[n] = ch;
+		++n;
+	}
+	return n;
+}
+
+int64_t wlg_reads_count(const wlg_spec_t *sp, const char *genome, int64_t first, int64_t n_reads, int64_t *seq_off, uint32_t *bid)
+{
+	#pragma omp parallel for schedule(static, 64)
+	for (int64_t r = 0; r < n_reads; ++r) seq_off[r + 1] = wlg_one(sp, genome, first + r, 0, bid ? bid + r : 0);
+	seq_off[0] = 0;
+	for (int64_t r = 0; r < n_reads; ++r) seq_off[r + 1] += seq_off[r];
+	return seq_off[n_reads];
+}
+
+void wlg_reads_fill(const wlg_spec_t *sp, const char *genome, int64_t first, int64_t n_reads, const int64_t *seq_off, char *seq)
+{
+	#pragma omp parallel for schedule(dynamic, 64)
+	for (int64_t r = 0; r < n_reads; ++r) wlg_one(sp, genome, first + r, seq + seq_off[r], 0);
 }

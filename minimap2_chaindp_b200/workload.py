@@ -222,3 +222,113 @@ class SeedWorkload:
             self.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------------------------------------
+# "G-seq": a synthetic genome and reads as BASES, for the composed pipeline (csrc/workload_seed.c, wlg_*)
+# ---------------------------------------------------------------------------------------------------------
+class _GenomeSpec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n_contigs", C.c_int32), ("contig_len", C.c_int32), ("p_repeat", C.c_double),
+                ("read_len", C.c_int32), ("err", C.c_double)]
+
+
+@dataclass(frozen=True)
+class SeqWorkloadSpec:
+    name: str
+    preset: str
+    n_reads: int
+    seed: int
+    n_contigs: int            # contigs of <= 1 Mb (the fork's index limit)
+    contig_len: int
+    read_len: int
+    err: float = 0.10
+    p_repeat: float = 0.03
+    max_occ: int = 50         # opt->mid_occ
+    flag: int = 0
+    b: int = 14               # mi->b
+
+
+SEQ_CONFIGS = {
+    # BASELINE.json configs[1] as sequences: 100k x 10 kb reads at 10 % error against 100 x 1 Mb of synthetic reference
+    "map-ont-100k-seq": SeqWorkloadSpec("map-ont-100k-seq", "map-ont", 100_000, _SEED + 21, 100, 1_000_000, 10_000),
+    "map-ont-small-seq": SeqWorkloadSpec("map-ont-small-seq", "map-ont", 2_000, _SEED + 22, 6, 300_000, 10_000),
+}
+
+
+class SeqWorkload:
+    """The genome (bytes), a sampler of reads, and -- given the genome's minimizers -- its index streams."""
+
+    def __init__(self, spec: SeqWorkloadSpec):
+        L = lib()
+        if not hasattr(L, "_seq_bound"):
+            L.wlg_genome.argtypes = [C.POINTER(_GenomeSpec), C.c_void_p]
+            L.wlg_genome.restype = None
+            L.wlg_reads_count.restype = C.c_int64
+            L.wlg_reads_count.argtypes = [C.POINTER(_GenomeSpec), C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+            L.wlg_reads_fill.restype = None
+            L.wlg_reads_fill.argtypes = [C.POINTER(_GenomeSpec), C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+            L.wls_build_sites.restype = C.c_void_p
+            L.wls_build_sites.argtypes = [C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]
+            L.wls_free.argtypes = [C.c_void_p]
+            L.wls_free.restype = None
+            L.wls_streams.argtypes = [C.c_void_p] + [C.POINTER(C.c_void_p), C.POINTER(C.c_int64)] * 4 + [C.POINTER(C.c_int64)] * 2
+            L.wls_streams.restype = None
+            L._seq_bound = True
+        self.spec = spec
+        self._cs = _GenomeSpec(spec.seed, spec.n_contigs, spec.contig_len, spec.p_repeat, spec.read_len, spec.err)
+        self.genome = np.zeros(spec.n_contigs * spec.contig_len, np.uint8)
+        L.wlg_genome(C.byref(self._cs), self.genome.ctypes.data)
+        self._idx = None
+        self.streams = []
+
+    def contig_offsets(self) -> np.ndarray:
+        return np.arange(self.spec.n_contigs + 1, dtype=np.int64) * self.spec.contig_len
+
+    def build_index(self, mv_off: np.ndarray, mv: np.ndarray, k: int):
+        """Index streams from the genome's minimizers (mm_sketch of contig c with rid = c, as mm_idx_gen does, index.c:340-416):
+        key = x >> 8, position packed refid 21 | lastpos 21 | strand 1 | rank 21 with rank = the contig's own number."""
+        x, y = mv[:, 0], mv[:, 1]
+        rid = (y >> np.uint64(32)) & np.uint64(0x1fffff)
+        pos = (rid << np.uint64(43)) | (((y & np.uint64(0xffffffff)) >> np.uint64(1)) & np.uint64(0x1fffff)) << np.uint64(22) | \
+              (y & np.uint64(1)) << np.uint64(21) | rid
+        key = np.ascontiguousarray(x >> np.uint64(8))
+        pos = np.ascontiguousarray(pos)
+        L = lib()
+        self._idx = L.wls_build_sites(self.spec.b, 2 * k, key.shape[0], key.ctypes.data, pos.ctypes.data)
+        if not self._idx:
+            raise MemoryError("wls_build_sites failed")
+        ptr = [C.c_void_p() for _ in range(4)]
+        size = [C.c_int64() for _ in range(4)]
+        nk, mo = C.c_int64(), C.c_int64()
+        args = []
+        for p, s in zip(ptr, size):
+            args += [C.byref(p), C.byref(s)]
+        L.wls_streams(self._idx, *args, C.byref(nk), C.byref(mo))
+        self.streams = []
+        for p, s in zip(ptr, size):
+            n = int(s.value)
+            self.streams.append(np.frombuffer((C.c_char * max(n, 1)).from_address(p.value), np.uint8, n) if n else np.zeros(0, np.uint8))
+        self.n_keys, self.max_occ_seen = int(nk.value), int(mo.value)
+        return self.streams
+
+    def reads_count(self, first: int, n_reads: int):
+        off = np.zeros(n_reads + 1, np.int64)
+        bid = np.zeros(max(n_reads, 1), np.uint32)
+        lib().wlg_reads_count(C.byref(self._cs), self.genome.ctypes.data, first, n_reads, off.ctypes.data, bid.ctypes.data)
+        return off, bid[:n_reads]
+
+    def reads_fill(self, first: int, off: np.ndarray, out: np.ndarray) -> None:
+        assert out.dtype == np.uint8 and out.size >= int(off[-1])
+        lib().wlg_reads_fill(C.byref(self._cs), self.genome.ctypes.data, first, off.shape[0] - 1, off.ctypes.data, out.ctypes.data)
+
+    def close(self):
+        if self._idx:
+            self.streams = []
+            lib().wls_free(self._idx)
+            self._idx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
