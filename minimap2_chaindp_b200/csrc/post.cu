@@ -608,6 +608,20 @@ extern "C" int mm2b200_post_device(mm2b200_ctx_t *ctx, const mm2b200_post_params
 	return post_device_impl(ctx, s, post, n_reads, chains, n_chains_cap, d_hash, d_qlen, (cudaStream_t)stream, out);
 }
 
+// after the caller has synchronised the stream: add the events' span to the stage time (the composed path, seed_api.cu)
+namespace mm2b200 {
+void post_stage_account(mm2b200_ctx *ctx)
+{
+	PostState *s = post_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	if (ctx_profile(ctx) && s->ev0) {
+		float t = 0;
+		if (cudaEventElapsedTime(&t, s->ev0, s->ev1) == cudaSuccess) s->ms += t;
+		cudaGetLastError();
+	}
+}
+}
+
 extern "C" int mm2b200_post_stage_ms(mm2b200_ctx_t *ctx, double *ms, int64_t *launches)
 {
 	if (!ctx) return failf(MM2B200_ERR_ARG, "NULL context");

@@ -593,6 +593,8 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	if (n_regs) CU_TRY(cudaMemcpyAsync(ix->h_regs.p, dr.d_regs, sizeof(mm2b200_reg_t) * n_regs, cudaMemcpyDeviceToHost, st));
 	CU_TRY(cudaStreamSynchronize(st));
 	seed_finish(ix, so);
+	sketch_stage_account(ix->ctx);
+	post_stage_account(ix->ctx);
 	res->n_reads = n_reads; res->reg_off = ix->h_reg_off.as<int64_t>(); res->regs = (const mm2b200_reg_t*)ix->h_regs.p;
 	res->rep_len = ix->h_rep.as<int32_t>();
 	res->n_minimizers = n_mv; res->n_anchors = so.n_anchors; res->n_chains = tot[1];

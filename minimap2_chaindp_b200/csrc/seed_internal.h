@@ -60,6 +60,8 @@ int ctx_sm_count(const mm2b200_ctx *ctx);
 void *ctx_ext(const mm2b200_ctx *ctx, int k);
 void ctx_set_ext(mm2b200_ctx *ctx, int k, void *p, void (*free_fn)(void*));
 void ctx_add_launches(mm2b200_ctx *ctx, int64_t n);
+void sketch_stage_account(mm2b200_ctx *ctx);   // sketch.cu / post.cu: fold the last call's event span into the stage time
+void post_stage_account(mm2b200_ctx *ctx);
 
 // launchers; each returns the number of kernels it enqueued
 int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cudaStream_t s);   // + scans over reads, totals, mini_pos packing

@@ -57,31 +57,52 @@ __device__ __forceinline__ int nt4(uint8_t ch)                               // 
 	return u == 'a' ? 0 : u == 'c' ? 1 : u == 'g' ? 2 : (u == 't' || u == 'u') ? 3 : 4;
 }
 
-// inclusive block scan (sum) of a 64-bit value holding up to four 16-bit counters
-__device__ __forceinline__ unsigned long long block_scan(unsigned long long v, unsigned long long *s_warp, int tid)
+// the same function in 32-bit arithmetic: every step is exact modulo 2^(2k), so for 2k <= 32 the low word is all there is
+__device__ __forceinline__ uint32_t hash32m(uint32_t key, uint32_t mask)
+{
+	key = (~key + (key << 21)) & mask;
+	key = key ^ key >> 24;
+	key = ((key + (key << 3)) + (key << 8)) & mask;
+	key = key ^ key >> 14;
+	key = ((key + (key << 2)) + (key << 4)) & mask;
+	key = key ^ key >> 28;
+	key = (key + (key << 31)) & mask;
+	return key;
+}
+
+// inclusive block scan (sum) of a 32-bit value holding up to three 10-bit counters (a tile has 512 positions)
+__device__ __forceinline__ uint32_t block_scan(uint32_t v, uint32_t *s_warp, int tid)
 {
 	const int lane = tid & 31, wid = tid >> 5;
-	for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(FULL, v, d); if (lane >= d) v += t; }
+	for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, v, d); if (lane >= d) v += t; }
 	__syncthreads();                       // s_warp may still be read from the previous scan
 	if (lane == 31) s_warp[wid] = v;
 	__syncthreads();
 	if (wid == 0) {
-		unsigned long long x = lane < SK_T / 32 ? s_warp[lane] : 0;
-		for (int d = 1; d < 32; d <<= 1) { const unsigned long long t = __shfl_up_sync(FULL, x, d); if (lane >= d) x += t; }
+		uint32_t x = lane < SK_T / 32 ? s_warp[lane] : 0;
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, x, d); if (lane >= d) x += t; }
 		if (lane < SK_T / 32) s_warp[lane] = x;
 	}
 	__syncthreads();
 	return v + (wid ? s_warp[wid - 1] : 0);
 }
 
+// the 2-bit groups of x in reverse order (group g <-> group 31 - g)
+__device__ __forceinline__ uint64_t rev2(uint64_t x)
+{
+	const uint64_t y = __brevll(x);
+	return (y & 0x5555555555555555ull) << 1 | (y >> 1 & 0x5555555555555555ull);
+}
+
 __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 {
 	__shared__ unsigned long long sx[SK_HALO + SK_T], sy[SK_HALO + SK_T];
 	__shared__ int sl[SK_HALO + SK_T];
-	__shared__ uint8_t vcode[SK_KH + SK_T];
+	__shared__ __align__(16) uint8_t vcode[SK_KH + SK_T];
 	__shared__ uint16_t vskip[SK_KH + SK_T];
 	__shared__ uint16_t recV[SK_T], recS[SK_T];          // per ambiguous token of the tile: valid / non-symmetric tokens up to it
-	__shared__ unsigned long long s_warp[SK_T / 32];
+	__shared__ uint32_t s_warp[SK_T / 32];
+	__shared__ uint32_t vpack[(SK_KH + SK_T) / 16 + 2];    // vcode, 16 two-bit codes per word
 	__shared__ int c_V0, c_VN0, c_L0, c_E0;                // carried: valid tokens so far (saturated), valid / non-symmetric since the last ambiguous base, emitted
 	const int tid = threadIdx.x;
 	const int w = W.w, k = W.k, hpc = W.is_hpc;
@@ -111,12 +132,24 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 				if (is_tok) while (skip_len < 256 && p - skip_len >= 0 && nt4(str[p - skip_len]) == c) ++skip_len;   // 256+ can never be a real entry (span < 256)
 			}
 			const bool valid = is_tok && c < 4, isN = is_tok && c >= 4;
-			const unsigned long long a_in = (unsigned long long)is_tok | (unsigned long long)valid << 16 | (unsigned long long)isN << 32;
-			const unsigned long long a_sc = block_scan(a_in, s_warp, tid);
-			const int valid_incl = (int)(a_sc >> 16 & 0xffff), nN_incl = (int)(a_sc >> 32 & 0xffff);
+			const uint32_t a_sc = block_scan((uint32_t)is_tok | (uint32_t)valid << 10 | (uint32_t)isN << 20, s_warp, tid);
+			const int valid_incl = (int)(a_sc >> 10 & 0x3ff), nN_incl = (int)(a_sc >> 20 & 0x3ff);
 			const int vr = valid_incl - (valid ? 1 : 0);
 			if (valid) { vcode[SK_KH + vr] = (uint8_t)c; vskip[SK_KH + vr] = (uint16_t)skip_len; }
 			if (isN) recV[nN_incl - 1] = (uint16_t)valid_incl;
+			__syncthreads();
+			if (tid < (SK_KH + SK_T) / 16 + 2) {                 // 16 codes -> one word (stale codes behind the tile's last valid token are never read)
+				uint32_t word = 0;
+				if (tid < (SK_KH + SK_T) / 16) {
+					const uint32_t *src = (const uint32_t*)vcode + 4 * tid;
+					#pragma unroll
+					for (int q = 0; q < 4; ++q) {
+						const uint32_t v = src[q];
+						word |= ((v & 3) | (v >> 6 & 0xc) | (v >> 12 & 0x30) | (v >> 18 & 0xc0)) << 8 * q;
+					}
+				}
+				vpack[tid] = word;
+			}
 			__syncthreads();
 			// ---- k-mers of the valid tokens
 			const int V0 = c_V0, VN0 = c_VN0, L0 = c_L0, E0 = c_E0;
@@ -124,20 +157,24 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 			int span_hpc = 0;
 			bool nonsym = false;
 			if (valid) {
-				const int before = V0 + vr;                  // valid tokens before this one (saturated, only compared with j < 28)
-				const int sinceN = nN_incl > 0 ? valid_incl - (int)recV[nN_incl - 1] : VN0 + valid_incl;
-				const int nsum = sinceN < k ? sinceN : k;
-				for (int j = 0; j < k; ++j) {
-					const uint64_t code = vcode[SK_KH + vr - j];
-					kmer0 |= code << 2 * j;                  // tokens before the first one are zero here like in the reference's zero-initialised k-mer
-					if (j <= before) kmer1 |= (3ULL ^ code) << (shift1 - 2 * j);
-					if (j < nsum) span_hpc += vskip[SK_KH + vr - j];
+				const int before = V0 + vr;                  // valid tokens before this one (saturated, only compared with k <= 28)
+				const int q = SK_KH + vr;                    // this token in vcode[]; the 32 codes up to it as one word, oldest lowest
+				const int wi = (q - 31) >> 4, sh = 2 * ((q - 31) & 15);
+				const uint32_t w0 = vpack[wi], w1 = vpack[wi + 1], w2 = vpack[wi + 2];
+				const uint64_t S = (uint64_t)__funnelshift_r(w1, w2, sh) << 32 | __funnelshift_r(w0, w1, sh);
+				kmer0 = rev2(S) & mask;                      // newest token lowest; tokens before the read's first one are zero like the reference's initial k-mer
+				kmer1 = ~S >> (64 - 2 * k);                  // complement, newest token highest
+				if (before < k - 1) kmer1 &= ~((1ULL << 2 * (k - 1 - before)) - 1);     // ... and absent from the reverse k-mer
+				if (hpc) {
+					const int sinceN = nN_incl > 0 ? valid_incl - (int)recV[nN_incl - 1] : VN0 + valid_incl;
+					const int nsum = sinceN < k ? sinceN : k;
+					for (int j = 0; j < nsum; ++j) span_hpc += vskip[q - j];
 				}
 				nonsym = kmer0 != kmer1;
 			}
 			const bool step = isN || nonsym;
-			const unsigned long long b_sc = block_scan((unsigned long long)nonsym | (unsigned long long)step << 16, s_warp, tid);
-			const int nonsym_incl = (int)(b_sc & 0xffff), step_incl = (int)(b_sc >> 16 & 0xffff);
+			const uint32_t b_sc = block_scan((uint32_t)nonsym | (uint32_t)step << 10, s_warp, tid);
+			const int nonsym_incl = (int)(b_sc & 0x3ff), step_incl = (int)(b_sc >> 10 & 0x3ff);
 			if (isN) recS[nN_incl - 1] = (uint16_t)nonsym_incl;
 			__syncthreads();
 			if (step) {
@@ -148,7 +185,8 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 					const int span = hpc ? span_hpc : (l < k ? l : k);
 					if (l >= k && span < 256) {
 						const int z = kmer0 < kmer1 ? 0 : 1;
-						ix = hash64m(z ? kmer1 : kmer0, mask) << 8 | (uint64_t)span;
+						const uint64_t km = z ? kmer1 : kmer0;
+						ix = (k <= 16 ? (uint64_t)hash32m((uint32_t)km, (uint32_t)mask) : hash64m(km, mask)) << 8 | (uint64_t)span;
 						iy = (uint64_t)rid << 32 | (uint64_t)((uint32_t)p << 1) | (uint64_t)z;
 					}
 				}
@@ -168,29 +206,32 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 				s = SK_HALO + tid;
 				l = sl[s];
 				const uint64_t info_x = sx[s];
-				prev_i = s - w;
-				prev_x = sx[s - w];
-				for (int i = s - w + 1; i < s; ++i) { const uint64_t x = sx[i]; if (x <= prev_x) { prev_x = x; prev_i = i; } }   // newest minimum of [s-w, s-1]
-				if (l == w + k - 1 && prev_x != NONE) {
-					emitA = true;
-					for (int i = s - w + 1; i < s; ++i) cnt += (sx[i] == prev_x && i != prev_i);
+				// one pass over the entries both windows share, [s-w+1, s-1]: their newest minimum and how many entries equal it
+				uint64_t cm = NONE;
+				int ci = s - w, eq = 0;
+				for (int i = s - w + 1; i < s; ++i) {
+					const uint64_t x = sx[i];
+					if (x < cm) { cm = x; ci = i; eq = 1; }
+					else if (x == cm) { ci = i; ++eq; }
 				}
+				const uint64_t old_x = sx[s - w];
+				const bool old_min = old_x < cm;             // the entry that just left wins only when strictly smaller than everything newer
+				prev_x = old_min ? old_x : cm;
+				prev_i = old_min ? s - w : ci;
+				if (l == w + k - 1 && prev_x != NONE && !old_min && eq > 1) { emitA = true; cnt += eq - 1; }
 				if (info_x <= prev_x) {                      // the minimum is replaced
 					if (l >= w + k && prev_x != NONE) { emitPrev = true; ++cnt; }
-				} else if (prev_i == s - w) {                // the minimum has left the window: rescan
+				} else if (old_min) {                        // the minimum has left the window: the new one is the newest minimum of [s-w+1, s]
 					if (l >= w + k - 1 && prev_x != NONE) { emitPrev = true; ++cnt; }
-					uint64_t cur_x = NONE;
-					cur_i = s;
-					for (int i = s - w + 1; i <= s; ++i) { const uint64_t x = sx[i]; if (x <= cur_x) { cur_x = x; cur_i = i; } }
-					if (l >= w + k - 1 && cur_x != NONE) {
-						emitDup = true;
-						for (int i = s - w + 1; i <= s; ++i) cnt += (sx[i] == cur_x && i != cur_i);
-					}
+					const bool take = info_x <= cm;
+					cur_i = take ? s : ci;
+					const int ndup = take ? (info_x == cm ? eq : 0) : eq - 1;
+					if (l >= w + k - 1 && (take ? info_x : cm) != NONE && ndup > 0) { emitDup = true; cnt += ndup; }
 				}
 			}
-			const unsigned long long e_sc = block_scan((unsigned long long)cnt, s_warp, tid);
+			const uint32_t e_sc = block_scan((uint32_t)cnt, s_warp, tid);
 			if (cnt) {
-				ulonglong2 *o = out + E0 + (int)(e_sc - (unsigned long long)cnt);
+				ulonglong2 *o = out + E0 + (int)(e_sc - (uint32_t)cnt);
 				if (emitA) for (int i = s - w + 1; i < s; ++i) if (sx[i] == prev_x && i != prev_i) *o++ = make_ulonglong2(sx[i], sy[i]);
 				if (emitPrev) *o++ = make_ulonglong2(prev_x, sy[prev_i]);
 				if (emitDup) { const uint64_t cur_x = sx[cur_i]; for (int i = s - w + 1; i <= s; ++i) if (sx[i] == cur_x && i != cur_i) *o++ = make_ulonglong2(sx[i], sy[i]); }
@@ -400,6 +441,9 @@ void sketch_account(mm2b200_ctx_t *ctx, SketchState *s)
 }
 
 } // namespace
+
+// after the caller has synchronised the stream: add the events' span to the stage time (the composed path, seed_api.cu)
+namespace mm2b200 { void sketch_stage_account(mm2b200_ctx *ctx) { SketchState *s = sketch_state(ctx); std::lock_guard<std::mutex> lk(s->mu); sketch_account(ctx, s); } }
 
 extern "C" int mm2b200_sketch_device(mm2b200_ctx_t *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
                                      const char *d_seq, const uint32_t *d_rid, void *stream, mm2b200_dev_sketch_t *out, int64_t *n_mv)
