@@ -62,6 +62,18 @@ struct PinBuf {
 		cap = want;
 		return MM2B200_OK;
 	}
+	// grows like reserve but keeps the first `keep` bytes (the caller has synchronised everything that touches the buffer)
+	int reserve_keep(size_t bytes, size_t keep)
+	{
+		if (bytes <= cap && p) return MM2B200_OK;
+		const size_t want = bytes + bytes / 2 + 4096;
+		void *q = nullptr;
+		if (cudaHostAlloc(&q, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaHostAlloc(%zu bytes) failed in the seeding stage", want); }
+		if (p && keep) memcpy(q, p, keep);
+		if (p) cudaFreeHost(p);
+		p = q; cap = want;
+		return MM2B200_OK;
+	}
 	void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 	template <class T> T *as() { return (T*)p; }
 };
@@ -93,7 +105,9 @@ struct mm2b200_index {
 	PinBuf h_stage, h_totals, h_rep, h_mini_off, h_mini, h_a_off, h_a;
 	PinBuf h_n_u, h_u_off, h_b_off, h_u, h_b, h_rec_off, h_rec;
 	DevBuf d_reads;                        // mm2b200_map_regs_batch: bases, offsets, bid, hash, qlen
-	PinBuf h_reg_off, h_regs;
+	PinBuf h_reg_off, h_regs, h_chunk_off;
+	cudaStream_t copy_stream = nullptr;
+	std::vector<cudaEvent_t> ev_chunk;
 	int64_t launches = 0;
 	cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
 	double ms[3] = { 0, 0, 0 };
@@ -125,7 +139,9 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	if (ix->stream) cudaStreamSynchronize(ix->stream);
 	for (auto &b : ix->d_stream) b.release();
 	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release(); ix->d_reads.release();
-	ix->h_reg_off.release(); ix->h_regs.release();
+	ix->h_reg_off.release(); ix->h_regs.release(); ix->h_chunk_off.release();
+	if (ix->copy_stream) { cudaStreamSynchronize(ix->copy_stream); cudaStreamDestroy(ix->copy_stream); }
+	for (auto e : ix->ev_chunk) cudaEventDestroy(e);
 	for (PinBuf *b : { &ix->h_stage, &ix->h_totals, &ix->h_rep, &ix->h_mini_off, &ix->h_mini, &ix->h_a_off, &ix->h_a,
 	                   &ix->h_n_u, &ix->h_u_off, &ix->h_b_off, &ix->h_u, &ix->h_b, &ix->h_rec_off, &ix->h_rec }) b->release();
 	for (auto &e : ix->ev) if (e) cudaEventDestroy(e);
@@ -548,55 +564,89 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	memset(res, 0, sizeof(*res));
 	CU_TRY(cudaSetDevice(ix->device));
 	cudaStream_t st = ix->stream;
+	if (!ix->copy_stream) CU_TRY(cudaStreamCreateWithFlags(&ix->copy_stream, cudaStreamNonBlocking));
 	const size_t R = (size_t)n_reads;
+	// Chunks of whole reads (about MM2B200_MAP_CHUNK bases each, default 96 M): the bases of chunk c+1.. cross PCIe on a copy
+	// stream while chunk c runs through sketching, seeding, the DP and the post-processing on the compute stream.
+	static const int64_t chunk_bases = [] { const char *e = getenv("MM2B200_MAP_CHUNK"); const long long v = e ? atoll(e) : 0; return (int64_t)(v > 0 ? v : 96000000LL); }();
+	std::vector<int64_t> cut(1, 0);
+	for (int64_t r = 0; r < n_reads; ++r)
+		if (seq_off[r + 1] - seq_off[cut.back()] >= chunk_bases && r + 1 < n_reads) cut.push_back(r + 1);
+	cut.push_back(n_reads);
+	const size_t n_chunks = cut.size() - 1;
 	char *d_seq; int64_t *d_off; uint32_t *d_bid, *d_hash; int32_t *d_qlen;
 	{
 		Carver c;
-		c.add(&d_seq, (size_t)B + 16); c.add(&d_off, 8 * (R + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_hash, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
+		c.add(&d_seq, (size_t)B + 16); c.add(&d_off, 8 * (R + n_chunks + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_hash, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
 		if ((rc = ix->d_reads.reserve(c.total()))) return rc;
 		c.place(ix->d_reads.p);
 	}
-	if ((rc = ix->h_stage.reserve(8 * (R + 1) + 4 * (R + 1)))) return rc;
-	int64_t *h_off = ix->h_stage.as<int64_t>();
-	int32_t *h_qlen = (int32_t*)(h_off + (R + 1));
-	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? seq_off[r] - b0 : 0;
+	if ((rc = ix->h_stage.reserve(8 * (R + n_chunks + 1) + 4 * (R + 1)))) return rc;
+	int64_t *h_off = ix->h_stage.as<int64_t>();                       // chunk c's offsets, relative to its first base, at h_off + cut[c] + c
+	int32_t *h_qlen = (int32_t*)(h_off + (R + n_chunks + 1));
+	for (size_t c = 0; c < n_chunks; ++c)
+		for (int64_t r = cut[c]; r <= cut[c + 1]; ++r) h_off[r + (int64_t)c] = seq_off[r] - seq_off[cut[c]];
 	for (size_t r = 0; r < R; ++r) h_qlen[r] = (int32_t)(seq_off[r + 1] - seq_off[r]);      // qlen_sum of a single-segment read (map.c:340-341)
-	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, st));
 	if (R) {
 		CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, st));
 		CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
 		CU_TRY(cudaMemcpyAsync(d_hash, hash, 4 * R, cudaMemcpyHostToDevice, st));
 	}
-	if (B) CU_TRY(cudaMemcpyAsync(d_seq, seq + b0, (size_t)B, cudaMemcpyHostToDevice, st));
-	// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0
-	mm2b200_dev_sketch_t dsk;
-	int64_t n_mv = 0;
-	if ((rc = mm2b200_sketch_device(ix->ctx, sk, n_reads, B, d_off, d_seq, nullptr, st, &dsk, &n_mv))) return rc;
-	// collect_seed_hits (map.c:187-236) on the minimizers where the sketch left them
-	SeedOut so;
-	if ((rc = seed_stage(ix, prm, n_reads, dsk.d_mv_off, dsk.d_mv, d_bid, d_qlen, so, n_mv, false))) return rc;
-	// mm_chain_dp, then mm_gen_regs + chain_post (map.c:837-866)
-	mm2b200_dev_result_t dev;
-	if ((rc = mm2b200_chain_device(ix->ctx, &prm->chain, n_reads, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
-	const int64_t cap = so.n_anchors / (prm->chain.min_cnt > 1 ? prm->chain.min_cnt : 1) + 1;
-	mm2b200_dev_regs_t dr;
-	if ((rc = mm2b200_post_device(ix->ctx, post, n_reads, &dev, cap, d_hash, d_qlen, st, &dr))) return rc;
-	int64_t *tot = ix->h_totals.as<int64_t>() + ST_TOTALS;
-	if ((rc = ix->h_reg_off.reserve(8 * (R + 1))) || (rc = ix->h_rep.reserve(4 * (R + 1)))) return rc;
-	CU_TRY(cudaMemcpyAsync(tot, dr.d_totals, 8, cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaMemcpyAsync(tot + 1, dev.d_totals, 16, cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaMemcpyAsync(ix->h_reg_off.p, dr.d_reg_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
-	if (R) CU_TRY(cudaMemcpyAsync(ix->h_rep.p, so.w.rep_len, 4 * R, cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaStreamSynchronize(st));
-	const size_t n_regs = (size_t)tot[0];
-	if ((rc = ix->h_regs.reserve(sizeof(mm2b200_reg_t) * (n_regs + 1)))) return rc;
-	if (n_regs) CU_TRY(cudaMemcpyAsync(ix->h_regs.p, dr.d_regs, sizeof(mm2b200_reg_t) * n_regs, cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaStreamSynchronize(st));
-	seed_finish(ix, so);
-	sketch_stage_account(ix->ctx);
-	post_stage_account(ix->ctx);
+	while (ix->ev_chunk.size() < n_chunks) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+		ix->ev_chunk.push_back(e);
+	}
+	for (size_t c = 0; c < n_chunks; ++c) {                             // every chunk's bases, queued now, arriving in order
+		const int64_t lo = seq_off[cut[c]] - b0, nb = seq_off[cut[c + 1]] - seq_off[cut[c]];
+		if (nb) CU_TRY(cudaMemcpyAsync(d_seq + lo, seq + b0 + lo, (size_t)nb, cudaMemcpyHostToDevice, ix->copy_stream));
+		CU_TRY(cudaEventRecord(ix->ev_chunk[c], ix->copy_stream));
+	}
+	if ((rc = ix->h_reg_off.reserve(8 * (R + 1))) || (rc = ix->h_rep.reserve(4 * (R + 1))) || (rc = ix->h_chunk_off.reserve(8 * (R + n_chunks + 1))) ||
+	    (rc = ix->h_regs.reserve(sizeof(mm2b200_reg_t) * (2 * R + 64)))) return rc;
+	int64_t *h_reg_off = ix->h_reg_off.as<int64_t>();
+	int64_t tot_regs = 0, tot_mv = 0, tot_anchors = 0, tot_chains = 0;
+	for (size_t c = 0; c < n_chunks; ++c) {
+		const int64_t r0 = cut[c], nr = cut[c + 1] - cut[c], lo = seq_off[r0] - b0, nb = seq_off[cut[c + 1]] - seq_off[r0];
+		const int64_t *d_off_c = d_off + r0 + (int64_t)c;
+		CU_TRY(cudaStreamWaitEvent(st, ix->ev_chunk[c], 0));
+		// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0
+		mm2b200_dev_sketch_t dsk;
+		int64_t n_mv = 0;
+		if ((rc = mm2b200_sketch_device(ix->ctx, sk, nr, nb, d_off_c, d_seq + lo, nullptr, st, &dsk, &n_mv))) return rc;
+		// collect_seed_hits (map.c:187-236) on the minimizers where the sketch left them
+		SeedOut so;
+		if ((rc = seed_stage(ix, prm, nr, dsk.d_mv_off, dsk.d_mv, d_bid + r0, d_qlen + r0, so, n_mv, false))) return rc;
+		// mm_chain_dp, then mm_gen_regs + chain_post (map.c:837-866)
+		mm2b200_dev_result_t dev;
+		if ((rc = mm2b200_chain_device(ix->ctx, &prm->chain, nr, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
+		const int64_t cap = so.n_anchors / (prm->chain.min_cnt > 1 ? prm->chain.min_cnt : 1) + 1;
+		mm2b200_dev_regs_t dr;
+		if ((rc = mm2b200_post_device(ix->ctx, post, nr, &dev, cap, d_hash + r0, d_qlen + r0, st, &dr))) return rc;
+		int64_t *tot = ix->h_totals.as<int64_t>() + ST_TOTALS;
+		int64_t *h_co = ix->h_chunk_off.as<int64_t>() + r0 + (int64_t)c;
+		CU_TRY(cudaMemcpyAsync(tot, dr.d_totals, 8, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaMemcpyAsync(tot + 1, dev.d_totals, 16, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaMemcpyAsync(h_co, dr.d_reg_off, 8 * ((size_t)nr + 1), cudaMemcpyDeviceToHost, st));
+		if (nr) CU_TRY(cudaMemcpyAsync(ix->h_rep.as<int32_t>() + r0, so.w.rep_len, 4 * (size_t)nr, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaStreamSynchronize(st));
+		const int64_t n_regs = tot[0];
+		if ((rc = ix->h_regs.reserve_keep(sizeof(mm2b200_reg_t) * (size_t)(tot_regs + n_regs + 1), sizeof(mm2b200_reg_t) * (size_t)tot_regs))) return rc;
+		if (n_regs) CU_TRY(cudaMemcpyAsync((mm2b200_reg_t*)ix->h_regs.p + tot_regs, dr.d_regs, sizeof(mm2b200_reg_t) * (size_t)n_regs, cudaMemcpyDeviceToHost, st));
+		for (int64_t r = 0; r < nr; ++r) h_reg_off[r0 + r] = tot_regs + h_co[r];
+		seed_finish(ix, so);
+		tot_regs += n_regs; tot_mv += n_mv; tot_anchors += so.n_anchors; tot_chains += tot[1];
+		{                                          // the regions must be off the device before the next chunk reuses the buffers
+			CU_TRY(cudaStreamSynchronize(st));
+			sketch_stage_account(ix->ctx);
+			post_stage_account(ix->ctx);
+		}
+	}
+	h_reg_off[R] = tot_regs;
+	CU_TRY(cudaStreamSynchronize(ix->copy_stream));
 	res->n_reads = n_reads; res->reg_off = ix->h_reg_off.as<int64_t>(); res->regs = (const mm2b200_reg_t*)ix->h_regs.p;
 	res->rep_len = ix->h_rep.as<int32_t>();
-	res->n_minimizers = n_mv; res->n_anchors = so.n_anchors; res->n_chains = tot[1];
+	res->n_minimizers = tot_mv; res->n_anchors = tot_anchors; res->n_chains = tot_chains;
 	return MM2B200_OK;
 }
