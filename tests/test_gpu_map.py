@@ -10,8 +10,15 @@ from post_util import read_hash
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("preset,flag,max_occ", [("map-ont", 0, 50), ("map-pb", 0, 50), ("ava-ont", 0x1 | 0x2 | 0x400 | 0x800000, 30), ("asm5", 0, 10)])
-def test_bases_in_regions_out(preset, flag, max_occ):
+@pytest.mark.parametrize("preset,flag,max_occ,chunk", [("map-ont", 0, 50, 0), ("map-ont", 0, 50, 20000), ("map-pb", 0, 50, 0), ("map-pb", 0, 50, 1),
+                                                        ("ava-ont", 0x1 | 0x2 | 0x400 | 0x800000, 30, 50000), ("asm5", 0, 10, 0)])
+def test_bases_in_regions_out(preset, flag, max_occ, chunk, monkeypatch):
+    """chunk > 0: MM2B200_MAP_CHUNK bases per pipeline chunk (1 = every read its own chunk), so that the call runs as many
+    chunks whose uploads overlap the computation of the chunks before them"""
+    if chunk:
+        monkeypatch.setenv("MM2B200_MAP_CHUNK", str(chunk))
+    else:
+        monkeypatch.delenv("MM2B200_MAP_CHUNK", raising=False)
     import oracle
     from oracle import post as opost, seed as oseed
     from minimap2_chaindp_b200 import api, post, seed, sketch
