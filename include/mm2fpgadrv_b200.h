@@ -8,9 +8,11 @@
  * collection, sort, the DP fill and the compaction run on the device (what map.c:484-575 models on the CPU), and the
  * response packets (new_seed[] + mini_pos[], map.c:533-565) come back through fpga_get_retbuf.
  *
- * Behind the boundary (not the FPGA's structure): submitted packets are queued; one worker thread per GPU takes EVERYTHING
- * that is waiting (bounded by MM2B200_SHIM_BATCH_MV minimizers), turns it into one device batch, and cuts the results back
- * into one response packet per request packet.  While a batch computes, the fork's worker threads keep submitting, so the
+ * Behind the boundary (not the FPGA's structure): submitted packets are queued; a worker thread (MM2B200_SHIM_WORKERS per GPU,
+ * default 2, each with its own context and copy of the index streams, so that one copies packets while the other's batch is
+ * on the device) takes EVERYTHING that is waiting (bounded by MM2B200_SHIM_BATCH_MV minimizers), turns it into one device
+ * batch, and cuts the results back into one response packet per request packet.  Request and response buffers are recycled
+ * through size-classed free lists.  While a batch computes, the fork's worker threads keep submitting, so the
  * batch size adapts to the load without a timer.  With several GPUs (MM2B200_DEVICES=0,1,... or all visible devices with
  * MM2B200_DEVICES=all; default: $MM2B200_DEVICE or 0) the index is replicated and the packets are shared out; reads are
  * independent, there is no collective.

@@ -40,6 +40,10 @@ int mm2b200_index_load(mm2b200_index_t *idx, const void *addr, int64_t size, int
  * starts a new index. */
 int mm2b200_index_commit(mm2b200_index_t *idx);
 
+/* Forgets the stream chunks loaded since the last commit and the committed index: the next mm2b200_index_load starts from
+ * nothing.  (The driver shim calls it when a new index begins on an object that never served a packet of the old one.) */
+int mm2b200_index_reset(mm2b200_index_t *idx);
+
 /* log2(number of buckets) (mi->b) and the bytes resident in HBM, after commit */
 int mm2b200_index_info(const mm2b200_index_t *idx, int32_t *b, int64_t *bytes);
 

@@ -81,7 +81,7 @@ def build_cuda(force: bool = False, verbose: bool = False, extra=()) -> str:
 def build_workload(force: bool = False) -> str:
     srcs = [os.path.join(CSRC, "workload.c"), os.path.join(CSRC, "workload_seed.c")]
     if force or _stale(WL_LIB, srcs):
-        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fopenmp", "-Wall", "-o", WL_LIB, *srcs, "-lm"], check=True)
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-fopenmp", "-Wall", "-o", WL_LIB, *srcs, "-lm", "-lpthread"], check=True)
     return WL_LIB
 
 

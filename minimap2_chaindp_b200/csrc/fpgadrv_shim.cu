@@ -53,12 +53,59 @@ struct Shim {
 	int busy = 0;                      // workers inside a batch
 	bool exit_block = false, stop = false;
 	bool have_params = false, have_index = false;
+	bool index_open = false;           // stream chunks are arriving; closed by fpga_set_params or the first packet
 	mm2b200_seed_params_t prm{};
 	std::vector<std::unique_ptr<ShimDevice>> dev;
 	int64_t max_bytes = (int64_t)1 << 30;
 	int64_t batch_mv = (int64_t)8 << 20;
 	std::atomic<int64_t> n_packets{0}, n_reads{0}, n_batches{0}, n_err{0};
 };
+
+// Packet buffers (requests and responses, a few hundred KB each) come from size-classed free lists: a fresh malloc of that
+// size is an mmap whose pages fault in on first touch -- measured, that cost more than the device batch itself.
+struct BufPool {
+	static const int N_CLASS = 24;                 // 4 KB << c
+	std::mutex mu;
+	std::vector<void*> free_list[N_CLASS];
+	int64_t pooled = 0, cap = (int64_t)2 << 30;
+	static int cls(size_t n) { int c = 0; while (((size_t)4096 << c) < n + 16 && c < N_CLASS - 1) ++c; return c; }
+	void *get(size_t n)
+	{
+		const int c = cls(n);
+		if (((size_t)4096 << c) < n + 16) {            // larger than the largest class: plain malloc, class -1
+			char *q = (char*)malloc(n + 16);
+			if (!q) return nullptr;
+			*(int64_t*)q = -1;
+			return q + 16;
+		}
+		{
+			std::lock_guard<std::mutex> lk(mu);
+			if (!free_list[c].empty()) { void *q = free_list[c].back(); free_list[c].pop_back(); pooled -= (int64_t)4096 << c; return (char*)q + 16; }
+		}
+		char *q = (char*)malloc((size_t)4096 << c);
+		if (!q) return nullptr;
+		*(int64_t*)q = c;
+		return q + 16;
+	}
+	void put(void *user)
+	{
+		if (!user) return;
+		char *q = (char*)user - 16;
+		const int64_t c = *(int64_t*)q;
+		if (c >= 0) {
+			std::lock_guard<std::mutex> lk(mu);
+			if (pooled + ((int64_t)4096 << c) <= cap) { free_list[c].push_back(q); pooled += (int64_t)4096 << c; return; }
+		}
+		free(q);
+	}
+	void drain()
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		for (auto &l : free_list) { for (void *q : l) free(q); l.clear(); }
+		pooled = 0;
+	}
+};
+BufPool g_pool;
 
 Shim *g_shim = nullptr;
 std::mutex g_shim_mu;                  // guards creation / destruction of g_shim
@@ -277,7 +324,7 @@ void process_batch(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &base, co
 			if (!r.err) need += pkt_up64(r.n_rec * (int64_t)sizeof(struct new_seed)) + pkt_up64(r.n_mini * 8);
 		}
 		if (need > 0x7fffffffLL) shim_fatal("response", "a response packet exceeds 2 GiB (fpga_get_retbuf reports its size as int)");
-		char *o = (char*)calloc(1, (size_t)need);
+		char *o = (char*)g_pool.get((size_t)need);
 		if (!o) shim_fatal("response", "out of host memory");
 		PktHead oh;
 		memset(&oh, 0, sizeof(oh));
@@ -301,9 +348,12 @@ void process_batch(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &base, co
 			pr.sub_size = (uint32_t)(sizeof(PktResult) + rec_b + mini_b);
 			memcpy(w, &pr, sizeof(pr));
 			w += sizeof(pr);
-			if (r.n_rec) memcpy(w, r.rec, (size_t)r.n_rec * sizeof(struct new_seed));
+			const size_t rec_n = (size_t)r.n_rec * sizeof(struct new_seed), mini_n = (size_t)r.n_mini * 8;
+			if (rec_n) memcpy(w, r.rec, rec_n);
+			memset(w + rec_n, 0, (size_t)rec_b - rec_n);               // padding to 64 bytes is zero (the buffer is recycled)
 			w += rec_b;
-			if (r.n_mini) memcpy(w, r.mini, (size_t)r.n_mini * 8);
+			if (mini_n) memcpy(w, r.mini, mini_n);
+			memset(w + mini_n, 0, (size_t)mini_b - mini_n);
 			w += mini_b;
 		}
 		out.push_back(Packet{o, (uint32_t)need});
@@ -337,7 +387,7 @@ void worker_main(Shim *S, ShimDevice *d)
 		out.clear();
 		process_batch(*S, *d, prm, take, out);
 		int64_t bytes = 0;
-		for (const Packet &p : take) { bytes += p.size; free(p.buf); }
+		for (const Packet &p : take) { bytes += p.size; g_pool.put(p.buf); }
 		{
 			std::lock_guard<std::mutex> lk(S->mu);
 			for (const Packet &p : out) S->done.push_back(p);
@@ -362,7 +412,10 @@ extern "C" int fpga_init(int flag)
 	std::unique_ptr<Shim> S(new Shim());
 	S->max_bytes = env_i64("MM2B200_SHIM_MAX_BYTES", S->max_bytes);
 	S->batch_mv = env_i64("MM2B200_SHIM_BATCH_MV", S->batch_mv);
-	for (int ord : shim_devices()) {
+	// two workers per GPU by default (each with its own context and copy of the index streams): while one batch is on the
+	// device the other worker copies packets into staging / cuts responses
+	const int per_dev = (int)env_i64("MM2B200_SHIM_WORKERS", 2);
+	for (int ord : shim_devices()) for (int rep = 0; rep < per_dev; ++rep) {
 		std::unique_ptr<ShimDevice> d(new ShimDevice());
 		d->ordinal = ord;
 		mm2b200_config_t cfg;
@@ -394,7 +447,9 @@ extern "C" void fpga_finalize()
 		if (d->idx) mm2b200_index_destroy(d->idx);
 		if (d->ctx) mm2b200_destroy(d->ctx);
 	}
-	for (const Packet &p : S->done) free(p.buf);
+	for (const Packet &p : S->done) g_pool.put(p.buf);
+	for (const Packet &p : S->pending) g_pool.put(p.buf);
+	g_pool.drain();
 	g_shim = nullptr;
 	delete S;
 }
@@ -410,6 +465,7 @@ extern "C" void fpga_set_params(int bw, int is_cdna, int max_skip, int min_sc, i
 	S->prm.chain.n_segs = 1; S->prm.chain.max_iter = 0;
 	S->prm.flag = flag; S->prm.max_occ = max_occ;
 	S->have_params = true;
+	S->index_open = false;
 }
 
 extern "C" void fpga_load_index(void *addr, int size, int type)
@@ -419,6 +475,10 @@ extern "C" void fpga_load_index(void *addr, int size, int type)
 	std::unique_lock<std::mutex> lk(S->mu);
 	// a new index part replaces the old one: everything submitted against the old one must be through
 	S->cv_idle.wait(lk, [&] { return S->pending.empty() && S->busy == 0; });
+	if (!S->index_open) {              // the first chunk of a new index: nothing of the old one may linger, served or not
+		for (auto &d : S->dev) if (mm2b200_index_reset(d->idx) != MM2B200_OK) shim_fatal("fpga_load_index", mm2b200_last_error());
+		S->index_open = true;
+	}
 	for (auto &d : S->dev) {
 		if (mm2b200_index_load(d->idx, addr, size, type) != MM2B200_OK) shim_fatal("fpga_load_index", mm2b200_last_error());
 		d->index_dirty = true;
@@ -436,7 +496,7 @@ extern "C" void *fpga_get_writebuf_thread(unsigned long size, BUF_TYPE type, int
 		if (S->pending_bytes > 0 && S->pending_bytes + (int64_t)size > S->max_bytes) return nullptr;   // back-pressure: the caller sleeps and retries
 		S->pending_bytes += (int64_t)size;
 	}
-	void *p = malloc(size ? size : 1);
+	void *p = g_pool.get(size ? size : 1);
 	if (!p) { std::lock_guard<std::mutex> lk(S->mu); S->pending_bytes -= (int64_t)size; }
 	return p;
 }
@@ -450,6 +510,7 @@ extern "C" int fpga_writebuf_submit(void *addr, unsigned int size, unsigned int 
 	if (!S || !addr) return -1;
 	{
 		std::lock_guard<std::mutex> lk(S->mu);
+		S->index_open = false;
 		S->pending.push_back(Packet{addr, size});
 	}
 	S->cv_work.notify_one();
@@ -471,7 +532,7 @@ extern "C" void *fpga_get_retbuf(int *len, RET_TYPE type)
 	return p.buf;
 }
 
-extern "C" int fpga_release_retbuf(void *addr) { free(addr); return 0; }
+extern "C" int fpga_release_retbuf(void *addr) { g_pool.put(addr); return 0; }
 
 extern "C" void fpga_exit_block()
 {

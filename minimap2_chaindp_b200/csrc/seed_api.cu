@@ -165,6 +165,15 @@ extern "C" int mm2b200_index_load(mm2b200_index_t *ix, const void *addr, int64_t
 	return MM2B200_OK;
 }
 
+extern "C" int mm2b200_index_reset(mm2b200_index_t *ix)
+{
+	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	ix->committed = false;
+	for (auto &h : ix->host) std::vector<uint8_t>().swap(h);
+	return MM2B200_OK;
+}
+
 extern "C" int mm2b200_index_commit(mm2b200_index_t *ix)
 {
 	if (!ix) return failf(MM2B200_ERR_ARG, "NULL index");

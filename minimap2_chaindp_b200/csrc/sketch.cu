@@ -107,7 +107,6 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 	const int tid = threadIdx.x;
 	const int w = W.w, k = W.k, hpc = W.is_hpc;
 	const uint64_t mask = (1ULL << 2 * k) - 1;
-	const int shift1 = 2 * (k - 1);
 	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
 		const int64_t s0 = W.seq_off[r];
 		const int len = (int)(W.seq_off[r + 1] - s0);

@@ -177,3 +177,72 @@ void wl_fill(const wl_spec_t *sp, int64_t first, int64_t n_reads, const int64_t 
 #pragma omp parallel for schedule(dynamic, 64)
 	for (r = 0; r < n_reads; ++r) gen_read(sp, first + r, a + offs[r]);
 }
+
+/* ---- driver-boundary pump (bench.py, row f2): what the fork's worker / receiver threads do with the driver symbols --------
+ * n_threads submitters each take every n_threads-th packet: fpga_get_writebuf_thread (sleeping 50 us while it returns NULL,
+ * map.c:439-441), memcpy, fpga_writebuf_submit; one receiver loops over fpga_get_retbuf / fpga_release_retbuf
+ * (fpga_chaindp.c:241-262) until every packet is answered.  The symbols come in as function pointers so that this
+ * generator library does not link the product.  Returns the wall time in seconds; *resp_bytes = bytes received. */
+#include <pthread.h>
+#include <time.h>
+#include <unistd.h>
+
+typedef void *(*wl_get_wbuf_t)(unsigned long, int, int);
+typedef int (*wl_submit_t)(void*, unsigned int, unsigned int);
+typedef void *(*wl_get_rbuf_t)(int*, int);
+typedef int (*wl_release_t)(void*);
+
+typedef struct {
+	int tid, n_threads;
+	int64_t n_packets;
+	const int64_t *pkt_off;
+	const char *pkts;
+	wl_get_wbuf_t get_wbuf; wl_submit_t submit; wl_get_rbuf_t get_rbuf; wl_release_t release;
+	int64_t got_bytes;
+} wl_pump_t;
+
+static void *wl_pump_send(void *arg)
+{
+	wl_pump_t *p = (wl_pump_t*)arg;
+	for (int64_t i = p->tid; i < p->n_packets; i += p->n_threads) {
+		const int64_t n = p->pkt_off[i + 1] - p->pkt_off[i];
+		void *buf;
+		while ((buf = p->get_wbuf((unsigned long)n, 0, p->tid)) == 0) usleep(50);
+		memcpy(buf, p->pkts + p->pkt_off[i], (size_t)n);
+		p->submit(buf, (unsigned int)n, 1);
+	}
+	return 0;
+}
+
+static void *wl_pump_recv(void *arg)
+{
+	wl_pump_t *p = (wl_pump_t*)arg;
+	for (int64_t i = 0; i < p->n_packets; ++i) {
+		int len = 0;
+		void *buf = p->get_rbuf(&len, 3);
+		if (len == 0) break;
+		p->got_bytes += len;
+		p->release(buf);
+	}
+	return 0;
+}
+
+double wl_shim_pump(int n_threads, int64_t n_packets, const int64_t *pkt_off, const char *pkts,
+                    wl_get_wbuf_t get_wbuf, wl_submit_t submit, wl_get_rbuf_t get_rbuf, wl_release_t release, int64_t *resp_bytes)
+{
+	pthread_t th[65];
+	wl_pump_t ctx[65];
+	struct timespec t0, t1;
+	if (n_threads < 1) n_threads = 1;
+	if (n_threads > 64) n_threads = 64;
+	clock_gettime(CLOCK_MONOTONIC, &t0);
+	for (int t = 0; t <= n_threads; ++t) {
+		wl_pump_t c = { t, n_threads, n_packets, pkt_off, pkts, get_wbuf, submit, get_rbuf, release, 0 };
+		ctx[t] = c;
+		pthread_create(&th[t], 0, t < n_threads ? wl_pump_send : wl_pump_recv, &ctx[t]);
+	}
+	for (int t = 0; t <= n_threads; ++t) pthread_join(th[t], 0);
+	clock_gettime(CLOCK_MONOTONIC, &t1);
+	if (resp_bytes) *resp_bytes = ctx[n_threads].got_bytes;
+	return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}

@@ -24,7 +24,7 @@ INDEX_B, INDEX_H, INDEX_V, INDEX_P = 4, 5, 6, 7
 
 # every symbol include/mm2seed_b200.h declares
 EXPORTED_SYMBOLS = (
-    "mm2b200_index_create", "mm2b200_index_destroy", "mm2b200_index_load", "mm2b200_index_commit", "mm2b200_index_info",
+    "mm2b200_index_create", "mm2b200_index_destroy", "mm2b200_index_load", "mm2b200_index_commit", "mm2b200_index_reset", "mm2b200_index_info",
     "mm2b200_seed_chain_batch", "mm2b200_seed_fill_batch", "mm2b200_seed_work",
     "mm2b200_seed_launch_count", "mm2b200_seed_stage_ms",
 )
@@ -75,6 +75,7 @@ def _lib():
         L.mm2b200_index_destroy.restype = None
         L.mm2b200_index_load.argtypes = [vp, vp, i64, C.c_int]
         L.mm2b200_index_commit.argtypes = [vp]
+        L.mm2b200_index_reset.argtypes = [vp]
         L.mm2b200_index_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i64)]
         L.mm2b200_seed_chain_batch.argtypes = [vp, C.POINTER(SeedParams), i64, vp, vp, vp, vp, C.c_int, C.POINTER(_SeedResult)]
         L.mm2b200_seed_fill_batch.argtypes = [vp, C.POINTER(SeedParams), i64, vp, vp, vp, vp, C.POINTER(_SeedRecords)]
