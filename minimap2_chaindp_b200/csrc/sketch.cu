@@ -70,21 +70,22 @@ __device__ __forceinline__ uint32_t hash32m(uint32_t key, uint32_t mask)
 	return key;
 }
 
-// inclusive block scan (sum) of a 32-bit value holding up to three 10-bit counters (a tile has 512 positions)
-__device__ __forceinline__ uint32_t block_scan(uint32_t v, uint32_t *s_warp, int tid)
+// inclusive block scan (sum) of a 32-bit value holding up to three 10-bit counters (a tile has 512 positions).  Every scan of
+// a tile has its own buf[]: nothing reads it between this call's first write and the previous tile's last read but barriers,
+// and buf[SK_T / 32 - 1] keeps the block total until the same scan of the next tile.
+__device__ __forceinline__ uint32_t block_scan(uint32_t v, uint32_t *buf, int tid)
 {
 	const int lane = tid & 31, wid = tid >> 5;
 	for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, v, d); if (lane >= d) v += t; }
-	__syncthreads();                       // s_warp may still be read from the previous scan
-	if (lane == 31) s_warp[wid] = v;
+	if (lane == 31) buf[wid] = v;
 	__syncthreads();
 	if (wid == 0) {
-		uint32_t x = lane < SK_T / 32 ? s_warp[lane] : 0;
+		uint32_t x = lane < SK_T / 32 ? buf[lane] : 0;
 		for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, x, d); if (lane >= d) x += t; }
-		if (lane < SK_T / 32) s_warp[lane] = x;
+		if (lane < SK_T / 32) buf[lane] = x;
 	}
 	__syncthreads();
-	return v + (wid ? s_warp[wid - 1] : 0);
+	return v + (wid ? buf[wid - 1] : 0);
 }
 
 // the 2-bit groups of x in reverse order (group g <-> group 31 - g)
@@ -101,12 +102,14 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 	__shared__ __align__(16) uint8_t vcode[SK_KH + SK_T];
 	__shared__ uint16_t vskip[SK_KH + SK_T];
 	__shared__ uint16_t recV[SK_T], recS[SK_T];          // per ambiguous token of the tile: valid / non-symmetric tokens up to it
-	__shared__ uint32_t s_warp[SK_T / 32];
+	__shared__ uint32_t s_wA[SK_T / 32], s_wB[SK_T / 32], s_wE[SK_T / 32];   // one per scan of a tile (block_scan)
+	__shared__ uint32_t sk[SK_HALO + SK_T];               // 32-bit image of sx[] >> 8 (the hash) for the fast window pass
 	__shared__ uint32_t vpack[(SK_KH + SK_T) / 16 + 2];    // vcode, 16 two-bit codes per word
 	__shared__ int c_V0, c_VN0, c_L0, c_E0;                // carried: valid tokens so far (saturated), valid / non-symmetric since the last ambiguous base, emitted
 	const int tid = threadIdx.x;
 	const int w = W.w, k = W.k, hpc = W.is_hpc;
 	const uint64_t mask = (1ULL << 2 * k) - 1;
+	const bool fast = !hpc && 2 * k < 32;
 	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
 		const int64_t s0 = W.seq_off[r];
 		const int len = (int)(W.seq_off[r + 1] - s0);
@@ -114,7 +117,7 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 		ulonglong2 *out = W.raw + s0;
 		const uint32_t rid = W.rid ? W.rid[r] : 0;
 		__syncthreads();
-		if (tid < SK_HALO) { sx[tid] = NONE; sy[tid] = NONE; sl[tid] = 0; }
+		if (tid < SK_HALO) { sx[tid] = NONE; sy[tid] = NONE; sl[tid] = 0; sk[tid] = 0xffffffffu; }
 		if (tid < SK_KH) { vcode[tid] = 0; vskip[tid] = 0; }
 		if (tid == 0) { c_V0 = 0; c_VN0 = 0; c_L0 = 0; c_E0 = 0; }
 		__syncthreads();
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 				if (is_tok) while (skip_len < 256 && p - skip_len >= 0 && nt4(str[p - skip_len]) == c) ++skip_len;   // 256+ can never be a real entry (span < 256)
 			}
 			const bool valid = is_tok && c < 4, isN = is_tok && c >= 4;
-			const uint32_t a_sc = block_scan((uint32_t)is_tok | (uint32_t)valid << 10 | (uint32_t)isN << 20, s_warp, tid);
+			const uint32_t a_sc = block_scan((uint32_t)is_tok | (uint32_t)valid << 10 | (uint32_t)isN << 20, s_wA, tid);
 			const int valid_incl = (int)(a_sc >> 10 & 0x3ff), nN_incl = (int)(a_sc >> 20 & 0x3ff);
 			const int vr = valid_incl - (valid ? 1 : 0);
 			if (valid) { vcode[SK_KH + vr] = (uint8_t)c; vskip[SK_KH + vr] = (uint16_t)skip_len; }
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 				nonsym = kmer0 != kmer1;
 			}
 			const bool step = isN || nonsym;
-			const uint32_t b_sc = block_scan((uint32_t)nonsym | (uint32_t)step << 10, s_warp, tid);
+			const uint32_t b_sc = block_scan((uint32_t)nonsym | (uint32_t)step << 10, s_wB, tid);
 			const int nonsym_incl = (int)(b_sc & 0x3ff), step_incl = (int)(b_sc >> 10 & 0x3ff);
 			if (isN) recS[nN_incl - 1] = (uint16_t)nonsym_incl;
 			__syncthreads();
@@ -190,14 +193,12 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 					}
 				}
 				const int si = SK_HALO + step_incl - 1;
-				sx[si] = ix; sy[si] = iy; sl[si] = l;
+				sx[si] = ix; sy[si] = iy; sl[si] = l; sk[si] = ix == NONE ? 0xffffffffu : (uint32_t)(ix >> 8);
 			}
 			__syncthreads();
 			// ---- what each step pushes (sketch.c:118-137)
-			__shared__ int s_tot[5];                         // tile totals: valid, ambiguous, non-symmetric tokens, steps, emissions
-			if (tid == SK_T - 1) { s_tot[0] = valid_incl; s_tot[1] = nN_incl; s_tot[2] = nonsym_incl; s_tot[3] = step_incl; }
-			__syncthreads();
-			const int n_steps = s_tot[3];
+			const uint32_t totA = s_wA[SK_T / 32 - 1], totB = s_wB[SK_T / 32 - 1];      // tile totals, left behind by the scans
+			const int tv = (int)(totA >> 10 & 0x3ff), tn = (int)(totA >> 20 & 0x3ff), ts = (int)(totB & 0x3ff), n_steps = (int)(totB >> 10 & 0x3ff);
 			int cnt = 0, s = 0, l = 0, prev_i = 0, cur_i = 0;
 			uint64_t prev_x = NONE;
 			bool emitA = false, emitPrev = false, emitDup = false;
@@ -205,15 +206,29 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 				s = SK_HALO + tid;
 				l = sl[s];
 				const uint64_t info_x = sx[s];
-				// one pass over the entries both windows share, [s-w+1, s-1]: their newest minimum and how many entries equal it
-				uint64_t cm = NONE;
+				// one pass over the entries both windows share, [s-w+1, s-1]: their newest minimum and how many entries equal it.
+				// Without HPC every real entry has span k, so x compares like its hash: a 32-bit pass when the hash leaves
+				// 0xffffffff free for the empty entry (2k < 32).
+				uint64_t cm = NONE, old_x;
 				int ci = s - w, eq = 0;
-				for (int i = s - w + 1; i < s; ++i) {
-					const uint64_t x = sx[i];
-					if (x < cm) { cm = x; ci = i; eq = 1; }
-					else if (x == cm) { ci = i; ++eq; }
+				if (fast) {
+					uint32_t m32 = 0xffffffffu;
+					for (int i = s - w + 1; i < s; ++i) {
+						const uint32_t x = sk[i];
+						if (x < m32) { m32 = x; ci = i; eq = 1; }
+						else if (x == m32) { ci = i; ++eq; }
+					}
+					cm = m32 == 0xffffffffu ? NONE : (uint64_t)m32 << 8 | (uint64_t)k;
+					const uint32_t o32 = sk[s - w];
+					old_x = o32 == 0xffffffffu ? NONE : (uint64_t)o32 << 8 | (uint64_t)k;
+				} else {
+					for (int i = s - w + 1; i < s; ++i) {
+						const uint64_t x = sx[i];
+						if (x < cm) { cm = x; ci = i; eq = 1; }
+						else if (x == cm) { ci = i; ++eq; }
+					}
+					old_x = sx[s - w];
 				}
-				const uint64_t old_x = sx[s - w];
 				const bool old_min = old_x < cm;             // the entry that just left wins only when strictly smaller than everything newer
 				prev_x = old_min ? old_x : cm;
 				prev_i = old_min ? s - w : ci;
@@ -228,22 +243,20 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 					if (l >= w + k - 1 && (take ? info_x : cm) != NONE && ndup > 0) { emitDup = true; cnt += ndup; }
 				}
 			}
-			const uint32_t e_sc = block_scan((uint32_t)cnt, s_warp, tid);
+			const uint32_t e_sc = block_scan((uint32_t)cnt, s_wE, tid);
 			if (cnt) {
 				ulonglong2 *o = out + E0 + (int)(e_sc - (uint32_t)cnt);
 				if (emitA) for (int i = s - w + 1; i < s; ++i) if (sx[i] == prev_x && i != prev_i) *o++ = make_ulonglong2(sx[i], sy[i]);
 				if (emitPrev) *o++ = make_ulonglong2(prev_x, sy[prev_i]);
 				if (emitDup) { const uint64_t cur_x = sx[cur_i]; for (int i = s - w + 1; i <= s; ++i) if (sx[i] == cur_x && i != cur_i) *o++ = make_ulonglong2(sx[i], sy[i]); }
 			}
-			if (tid == SK_T - 1) s_tot[4] = (int)e_sc;
-			__syncthreads();
 			// ---- carry to the next tile: the last SK_HALO ring entries, the last SK_KH valid tokens, the counters
-			const int tv = s_tot[0], tn = s_tot[1], ts = s_tot[2], te = s_tot[4];
-			unsigned long long hx = 0, hy = 0; int hl = 0; uint8_t hc = 0; uint16_t hs = 0;
-			if (tid < SK_HALO) { hx = sx[n_steps + tid]; hy = sy[n_steps + tid]; hl = sl[n_steps + tid]; }
+			const int te = (int)s_wE[SK_T / 32 - 1];
+			unsigned long long hx = 0, hy = 0; int hl = 0; uint8_t hc = 0; uint16_t hs = 0; uint32_t hk = 0;
+			if (tid < SK_HALO) { hx = sx[n_steps + tid]; hy = sy[n_steps + tid]; hl = sl[n_steps + tid]; hk = sk[n_steps + tid]; }
 			if (tid < SK_KH) { hc = vcode[tv + tid]; hs = vskip[tv + tid]; }
 			__syncthreads();
-			if (tid < SK_HALO) { sx[tid] = hx; sy[tid] = hy; sl[tid] = hl; }
+			if (tid < SK_HALO) { sx[tid] = hx; sy[tid] = hy; sl[tid] = hl; sk[tid] = hk; }
 			if (tid < SK_KH) { vcode[tid] = hc; vskip[tid] = hs; }
 			if (tid == 0) {
 				c_V0 = V0 + tv > 64 ? 64 : V0 + tv;
