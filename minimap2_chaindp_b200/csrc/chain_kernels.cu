@@ -560,6 +560,9 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 // nothing, and a few scored lanes are stepped through the reference's state machine one by one, in visit order, with
 // warp-uniform scalar code (two shuffles per scored lane).  Returns 0 = scan goes on, 1 = anchor finished,
 // 2 = too many scored lanes, nothing was changed: run the dense routine on this chunk.
+#ifndef DEEP_BATCH
+#define DEEP_BATCH 4      // chunks of a deep window requested together (k_fill_fast, RING >= 256)
+#endif
 #define SPARSE_MAX 4
 // a mark on anchor pj while anchor i is scanned (chain.c:87): in the ring's tag word while pj is still in the ring
 template <int RING>
@@ -576,7 +579,7 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
                                                          const unsigned xi, const int qi, const int span,
                                                          const unsigned mdx, const unsigned dr_max, const unsigned dq_max, const int bw,
                                                          const int B0, const unsigned tab_w, const double avg,
-                                                         int32_t *t, const int32_t *vg, const unsigned ring_w)
+                                                         int32_t *t, const int32_t *vg, const unsigned ring_w, bool &pub)
 {
 	const int j = jb - lane;
 	const unsigned dr = xi - (unsigned)rj.x;
@@ -622,7 +625,7 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 		if (pjL >= 0) {                                   // chain.c:87
 			const unsigned kt = (unsigned)(jb - pjL);
 			if (kt < 32u) lm |= 1u << kt;
-			else if (lane == 0) publish_mark<RING>(pjL, i, ring_w, t);
+			else { pub = true; if (lane == 0) publish_mark<RING>(pjL, i, ring_w, t); }    // pub: warp-uniform "a mark left this chunk"
 		}
 	} while (live);
 	return done;
@@ -732,15 +735,11 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 				if (__any_sync(FULL, far)) { if (far) publish_mark<RING>(rj.w, i, ring_w, t); }
 				// one chunk beyond the first: records and marks from the ring (chunks 1 .. RING/32-1) or from global memory
 				// (the records flushed there in 32-anchor blocks; L1/L2 hits)
-				auto deeper = [&](const bool in_ring, const unsigned ra, const int jb) -> int {
-					__syncwarp();                                     // marks published by the previous chunk are visible
-					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo are masked (j >= jlo in the scan routines)
-					int4 rk; bool mg;
-					if (in_ring) { rk = lds128<0>(ra); mg = lds32<SM::comp + 4>(ra) == i; }
-					else { rk = wrec[jc]; mg = t[jc] == i; }
+				// one chunk beyond the first, records rk and memory marks mg already loaded; pub reports marks that left the chunk
+				auto process = [&](const bool in_ring, const unsigned ra, const int jb, const int jc, const int4 rk, const bool mg, bool &pub) -> int {
 					if (FULLV) ++n_chunks;
 					int dn = scan_chunk_sparse<TABLE, FULLV, WIDE, RING>(max_f, max_j, vbest, budget, visited, i, jb, jlo, lane, rk, mg,
-					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg, ring_w);
+					                                       xi, qi, span, mdx, dr_max, dq_max, bw, B0, tab_w, avg, t, vg, ring_w, pub);
 					if (dn == 2) {                                    // many scored lanes: warp-wide replay
 						const int vk = in_ring ? lds32<SM::comp>(ra) : vg[jc];
 						const int ddk = abs((int)(xi - (unsigned)rk.x) - (qi - rk.y));
@@ -748,9 +747,21 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 						bool fk;
 						dn = scan_chunk_fast<FULLV, WIDE>(max_f, max_j, vbest, budget, visited, fk, jb, jlo, lane, rk, vk, mg,
 						                                   xi, qi, span, mdx, dr_max, dq_max, bw, ddk, ck, B0, max_skip, one);
-						if (!dn && fk) publish_mark<RING>(rk.w, i, ring_w, t);   // (the scalar path publishes its own)
+						if (!dn) {                                    // (the scalar path publishes its own)
+							if (__any_sync(FULL, fk)) pub = true;
+							if (fk) publish_mark<RING>(rk.w, i, ring_w, t);
+						}
 					}
 					return dn;
+				};
+				auto deeper = [&](const bool in_ring, const unsigned ra, const int jb) -> int {
+					__syncwarp();                                     // marks published by the previous chunk are visible
+					const int jc = max(jb - lane, jlo);               // clamped: lanes below jlo are masked (j >= jlo in the scan routines)
+					int4 rk; bool mg;
+					if (in_ring) { rk = lds128<0>(ra); mg = lds32<SM::comp + 4>(ra) == i; }
+					else { rk = wrec[jc]; mg = t[jc] == i; }
+					bool pub = false;
+					return process(in_ring, ra, jb, jc, rk, mg, pub);
 				};
 				unsigned ra = ring_w | (addi_fma<-512>(raddr, one) & SM::mask);
 				done = deeper(true, ra, i - 33);                      // chunk 1 is always in the ring
@@ -762,8 +773,38 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 						done = deeper(true, ra, jb);
 					}
 				}
+				if (RING >= 256) {
+					// Long reads: most of the scan is out here, one L2 / HBM round trip per chunk (ncu, map-pb: 57 % of the stall
+					// samples on these two loads, L2 hit rate 49 %).  While at least DEEP_BATCH whole chunks of the window remain, their
+					// records and marks are requested together and worked off in order; a mark that one of them publishes may be
+					// missing from the early load of the later ones, so those reload their marks (rare: the deep part of a window
+					// is mostly off the diagonal).  An early exit wastes at most DEEP_BATCH - 1 chunk loads.
 #pragma unroll 1
-				for (; !done && jb >= jlo; jb -= 32) done = deeper(false, 0u, jb);
+					while (!done && jb >= jlo) {
+						if (jb - (32 * DEEP_BATCH - 1) >= jlo) {
+							__syncwarp();
+							int4 rk[DEEP_BATCH]; int tk[DEEP_BATCH];
+#pragma unroll
+							for (int c = 0; c < DEEP_BATCH; ++c) { rk[c] = wrec[jb - 32 * c - lane]; tk[c] = t[jb - 32 * c - lane]; }
+							bool pub = false;
+#pragma unroll
+							for (int c = 0; c < DEEP_BATCH; ++c) {
+								if (!done) {
+									const int jc = jb - 32 * c - lane;
+									if (c) { __syncwarp(); if (pub) tk[c] = t[jc]; }
+									done = process(false, 0u, jb - 32 * c, jc, rk[c], tk[c] == i, pub);
+								}
+							}
+							jb -= 32 * DEEP_BATCH;
+						} else {
+							done = deeper(false, 0u, jb);
+							jb -= 32;
+						}
+					}
+				} else {
+#pragma unroll 1
+					for (; !done && jb >= jlo; jb -= 32) done = deeper(false, 0u, jb);
+				}
 			}
 			// chain.c:89-90: every lane holds the same result; all write it to the ring (same address, same data)
 			sts128<0>(waddr, make_int4((int)xi, qi, max_f, max_j));
