@@ -60,7 +60,7 @@ BYTES_PER_ANCHOR = 40          # 16 B anchor in + 16 B anchor ou
 # the other BASELINE.json configs: reads per chunk (bounds pinned + device memory) and reads in the parity sample
 CONFIG_BLOCK = {
     "ava-ont-50k": dict(chunk_reads=8000, parity_reads=2000),
-    "map-pb-ul-20k": dict(chunk_reads=2000, parity_reads=2000),
+    "map-pb-ul-20k": dict(chunk_reads=6000, parity_reads=2000),
     "asm5-50mb": dict(chunk_reads=8, parity_reads=8),
 }
 

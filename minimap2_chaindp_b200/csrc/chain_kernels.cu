@@ -561,7 +561,7 @@ static __device__ __forceinline__ int scan_chunk_fast(int &max_f, int &max_j, in
 // warp-uniform scalar code (two shuffles per scored lane).  Returns 0 = scan goes on, 1 = anchor finished,
 // 2 = too many scored lanes, nothing was changed: run the dense routine on this chunk.
 #ifndef DEEP_BATCH
-#define DEEP_BATCH 4      // chunks of a deep window requested together (k_fill_fast, RING >= 256)
+#define DEEP_BATCH 4      // chunks of a deep window requested together (k_fill_fast<.., DEEP = true>)
 #endif
 #define SPARSE_MAX 4
 // a mark on anchor pj while anchor i is scanned (chain.c:87): in the ring's tag word while pj is still in the ring
@@ -633,7 +633,7 @@ static __device__ __forceinline__ int scan_chunk_sparse(int &max_f, int &max_j, 
 
 // FULL = instrumented / extended variant: counts visited pairs and honours max_iter; the plain variant does neither
 // (register caps were tried: 40 registers / 12 CTAs per SM 5.70 ms, 32 / 16 CTAs 6.09 ms, 67 / 7 CTAs 5.07 ms, default 48 / 10 CTAs 4.89 ms)
-template <bool TABLE, bool FULLV, bool WIDE, int RING>
+template <bool TABLE, bool FULLV, bool WIDE, int RING, bool DEEP>
 __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b200_params_t prm, int tab_entries)
 {
 	extern __shared__ int4 smem4[];
@@ -773,7 +773,7 @@ __global__ void __launch_bounds__(FILL_WARPS * 32) k_fill_fast(Workspace w, mm2b
 						done = deeper(true, ra, jb);
 					}
 				}
-				if (RING >= 256) {
+				if (DEEP) {
 					// Long reads: most of the scan is out here, one L2 / HBM round trip per chunk (ncu, map-pb: 57 % of the stall
 					// samples on these two loads, L2 hit rate 49 %).  While at least DEEP_BATCH whole chunks of the window remain, their
 					// records and marks are requested together and worked off in order; a mark that one of them publishes may be
@@ -1443,11 +1443,11 @@ static int cached_occupancy(OccCache &oc, K kern, int threads, int smem)
 	return oc.occ;
 }
 
-template <bool TABLE, bool FULLV, bool WIDE, int RING>
+template <bool TABLE, bool FULLV, bool WIDE, int RING, bool DEEP>
 static void launch_fill_ring(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, cudaStream_t s)
 {
 	const int smem = fill_smem_bytes<RING>(tab_entries);
-	auto kern = k_fill_fast<TABLE, FULLV, WIDE, RING>;
+	auto kern = k_fill_fast<TABLE, FULLV, WIDE, RING, DEEP>;
 	static thread_local OccCache oc;   // one cache per template instance
 	const int occ = cached_occupancy(oc, kern, FILL_WARPS * 32, smem);
 	const int per_sm = (g_fill_ctas_cap > 0 && g_fill_ctas_cap < occ) ? g_fill_ctas_cap : occ;
@@ -1456,9 +1456,12 @@ static void launch_fill_ring(const Workspace &w, const mm2b200_params_t &prm, in
 template <bool TABLE, bool FULLV, bool WIDE>
 static void launch_fill_fast(const Workspace &w, const mm2b200_params_t &prm, int sms, int tab_entries, int ring, cudaStream_t s)
 {
-	if (ring >= 256) launch_fill_ring<TABLE, FULLV, WIDE, 256>(w, prm, sms, tab_entries, s);
-	else if (ring >= 128) launch_fill_ring<TABLE, FULLV, WIDE, 128>(w, prm, sms, tab_entries, s);
-	else launch_fill_ring<TABLE, FULLV, WIDE, 64>(w, prm, sms, tab_entries, s);
+	// ring < 0: the long-read variant of the 64-anchor ring (DEEP: the global part of a window four chunks at a time; 64
+	// registers, 8 CTAs per SM).  Deeper rings exist for experiments (MM2B200_RING) and always use the batched loads.
+	if (ring >= 256) launch_fill_ring<TABLE, FULLV, WIDE, 256, true>(w, prm, sms, tab_entries, s);
+	else if (ring >= 128) launch_fill_ring<TABLE, FULLV, WIDE, 128, true>(w, prm, sms, tab_entries, s);
+	else if (ring < 0) launch_fill_ring<TABLE, FULLV, WIDE, 64, true>(w, prm, sms, tab_entries, s);
+	else launch_fill_ring<TABLE, FULLV, WIDE, 64, false>(w, prm, sms, tab_entries, s);
 }
 
 void query_launch_cfg(LaunchCfg *cfg)
@@ -1494,9 +1497,14 @@ int launch_fill(const Workspace &w, const mm2b200_params_t &prm, const LaunchCfg
 	if (!host_generic) {
 		const int te = fill_tab_entries(prm);
 		const bool full = cfg.count_visited || prm.max_iter > 0;   // instrumented / max_iter-aware variant
-		// ring depth: long reads (thousands of anchors per read: map-pb, asm5) scan hundreds of predecessors per anchor, which
-		// the 256-anchor ring keeps in shared memory; ordinary reads rarely leave the first two chunks and keep the occupancy
-		const int ring = cfg.fill_ring ? cfg.fill_ring : (w.n_reads > 0 && w.n_anchors / w.n_reads >= 4096 ? 256 : 64);
+		// Long reads (thousands of anchors per read: map-pb, asm5, ava) scan hundreds of predecessors per anchor, far beyond the
+		// first chunks, and every chunk out of the ring is an L2 / HBM round trip: those sub-batches run the variants with the
+		// batched deep loads.  Which ring depth depends on how full the GPU gets (measured, tools/ring_sweep.sh): with fewer
+		// runs than resident warps (<= 2048 reads) the 256-anchor ring wins (fewer trips, occupancy is not the limit); with
+		// more, the 64-anchor ring (8 CTAs per SM instead of 5).  Ordinary reads rarely leave the first two chunks and keep
+		// the lean 64-anchor variant (48 registers, 10 CTAs per SM).
+		const bool long_reads = w.n_reads > 0 && w.n_anchors / w.n_reads >= 4096;
+		const int ring = cfg.fill_ring ? cfg.fill_ring : (long_reads ? (w.n_reads <= 2048 ? 256 : -1) : 64);
 		if (prm.max_dist_x >= (1 << 26)) {                         // per-lane window test not exact (33 gaps could wrap 2^32): general chunk routine only
 			if (te) launch_fill_fast<true, true, true>(w, prm, cfg.sm_count, te, ring, s); else launch_fill_fast<false, true, true>(w, prm, cfg.sm_count, 0, ring, s);
 		} else if (te) { if (full) launch_fill_fast<true, true, false>(w, prm, cfg.sm_count, te, ring, s); else launch_fill_fast<true, false, false>(w, prm, cfg.sm_count, te, ring, s); }

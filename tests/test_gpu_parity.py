@@ -66,13 +66,15 @@ def test_deep_windows(ctx, seed):
         assert_same(got, want, f"deep seed {seed} {over}")
 
 
-@pytest.mark.parametrize("ring", [64, 128, 256])
+@pytest.mark.parametrize("ring", [64, -1, 128, 256])
 def test_ring_depths(ring, monkeypatch):
-    """The fill kernel's ring depth (MM2B200_RING; 256 is what sub-batches of long reads get): chunks 1..RING/32-1 come from
-    shared memory with their marks in the ring's tag words, deeper ones from global memory with marks in t[].  Dense and
+    """The fill kernel's ring depth (MM2B200_RING; -1 = the 64-anchor ring with the batched loads of deep windows, what
+    sub-batches of long reads get; 128 / 256 use them too): chunks 1..RING/32-1 come from
+    shared memory with their marks in the ring's tag words, deeper ones from global memory with marks in t[] -- four chunks
+    at a time in the batched variants, with the marks reloaded when an earlier chunk of the batch let a mark leave.  Dense and
     sparse windows, break budgets that cross several chunks, and the visited-pair counter, all against the oracle."""
     monkeypatch.setenv("MM2B200_RING", str(ring))
-    rng = np.random.default_rng(7700 + ring)
+    rng = np.random.default_rng(7700 + abs(ring))
     reads = [random_colinear(rng, int(n), noise=float(rng.random()) * 0.6, step=int(rng.integers(1, 6))) for n in rng.integers(2, 2500, 20)]
     reads += [interleaved_diagonals(rng, int(n), k, step=int(rng.integers(1, 4))) for k in (3, 9, 40) for n in rng.integers(200, 3000, 4)]
     offs, a = concat_reads(reads)
@@ -87,7 +89,7 @@ def test_ring_depths(ring, monkeypatch):
 
 
 def test_long_reads_pick_the_deep_ring(ctx):
-    """A sub-batch of long reads (>= 4096 anchors per read on average) runs with the 256-anchor ring."""
+    """A sub-batch of long reads (>= 4096 anchors per read on average) runs the long-read variant of the fill (batched deep loads)."""
     spec = workload.CONFIGS["map-pb-ul-20k"]
     offs, a = workload.generate(spec, 5, 3)
     got = ctx.chain_batch(api.params(spec.preset), offs, a)

@@ -28,8 +28,8 @@ def test_fill_is_deterministic_under_every_residency(monkeypatch):
     prm, oprm = api.params("map-ont"), oracle.params("map-ont")
     want = _digest(oracle.chain_batch(oprm, offs, a))
     runs = 0
-    for ctas in (1, 2, 3, 5, 8, 0):
-        for ring in (64, 256):
+    for ctas in (1, 2, 5, 0):
+        for ring in (64, -1, 256):
             for slots, slot_anchors in ((1, 1 << 14), (2, 1 << 12), (32, 1 << 11)):
                 monkeypatch.setenv("MM2B200_FILL_CTAS", str(ctas))
                 monkeypatch.setenv("MM2B200_RING", str(ring))
