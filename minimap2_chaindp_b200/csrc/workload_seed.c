@@ -325,7 +325,7 @@ static int64_t wlg_one(const wlg_spec_t *sp, const char *genome, int64_t read_id
 		const double u = sm01(&rng);
 		if (u < e3) continue;                                                   /* deletion */
 		if (u < 2 * e3) ch = "ACGT"[sm64(&rng) & 3];                             /* substitution (may be silent) */
-		else if (u < 3 * e3) { if (out) out[n] = "ACGT"[sm64(&rng) & 3]; ++n; } /* insertion in front */
+		else if (u < 3 * e3) { const char ins = "ACGT"[sm64(&rng) & 3]; if (out) out[n] = ins; ++n; }   /* insertion in front (drawn in the counting pass too) */
 		if (out) out[n] = ch;
 		++n;
 	}
