@@ -96,7 +96,7 @@ struct mm2b200_index {
 	// upload
 	std::vector<uint8_t> host[4];          // B, H, V, P chunks appended until commit
 	bool committed = false;
-	DevBuf d_stream[4];
+	DevBuf d_stream[4], d_bloom;
 	DevIndex dix{};
 	int64_t resident_bytes = 0;
 	// per-batch state
@@ -138,6 +138,7 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	cudaSetDevice(ix->device);
 	if (ix->stream) cudaStreamSynchronize(ix->stream);
 	for (auto &b : ix->d_stream) b.release();
+	ix->d_bloom.release();
 	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release(); ix->d_reads.release();
 	ix->h_reg_off.release(); ix->h_regs.release(); ix->h_chunk_off.release();
 	if (ix->copy_stream) { cudaStreamSynchronize(ix->copy_stream); cudaStreamDestroy(ix->copy_stream); }
@@ -202,6 +203,26 @@ extern "C" int mm2b200_index_commit(mm2b200_index_t *ix)
 	ix->dix.b = b;
 	ix->dix.n_slots = (int64_t)(nV / 8);
 	ix->dix.n_pos = (int64_t)(nP / 8);
+	ix->dix.bloom = nullptr; ix->dix.bloom_mask = 0;
+	{	// presence filter over the live keys (seed_internal.h): >= 8 bits per hash slot, at least 2^20, at most 2^33 bits
+		const char *eb = getenv("MM2B200_SEED_BLOOM");
+		if (!(eb && atoi(eb) == 0) && ix->dix.n_slots > 0) {
+			uint64_t bits = (uint64_t)1 << 20;
+			while (bits < (uint64_t)ix->dix.n_slots * 8 && bits < ((uint64_t)1 << 33)) bits <<= 1;
+			int rc = ix->d_bloom.reserve(bits / 8 + 256);          // + a flag word behind the bits
+			if (rc) return rc;
+			CU_TRY(cudaMemsetAsync(ix->d_bloom.p, 0, bits / 8 + 256, ix->stream));
+			int32_t *d_bad = (int32_t*)((char*)ix->d_bloom.p + bits / 8), bad = 0;
+			ix->dix.bloom_mask = bits - 1;
+			ix->dix.bloom = (const uint32_t*)ix->d_bloom.p;
+			ix->launches += launch_seed_bloom(ix->dix, (uint32_t*)ix->d_bloom.p, d_bad, ix->stream);
+			CU_TRY(cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ix->stream));
+			CU_TRY(cudaStreamSynchronize(ix->stream));
+			CU_TRY(cudaGetLastError());
+			if (bad) { ix->dix.bloom = nullptr; ix->dix.bloom_mask = 0; }      // a bucket points outside H: the lookup will say so
+			else ix->resident_bytes += (int64_t)(bits / 8);
+		}
+	}
 	ix->committed = true;
 	return MM2B200_OK;
 }

@@ -15,7 +15,20 @@ struct DevIndex {
 	const uint64_t *P;     // [n_pos]
 	int32_t b;
 	int64_t n_slots, n_pos;
+	// Presence filter over the live keys, built once at commit (not part of the fork's streams): two bits per key in a
+	// power-of-two bit array of >= 8 bits per hash slot.  A minimizer with a clear bit is absent for sure and never touches
+	// B/H; in a noisy read most minimizers are (sequencing errors), and the array is small enough to live in L2.
+	const uint32_t *bloom;
+	uint64_t bloom_mask;       // number of bits - 1; 0 = no filter
 };
+
+__host__ __device__ __forceinline__ uint64_t bloom_bit(uint64_t minier, int which, uint64_t mask)
+{
+	uint64_t z = minier + (which ? 0x9E3779B97F4A7C15ULL : 0xD1B54A32D192ED03ULL);
+	z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+	z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+	return (z ^ (z >> 31)) & mask;
+}
 
 enum SeedTotal { ST_ANCHORS = 0, ST_MINI = 1, ST_ERROR = 2, ST_EXACT = 3, ST_MAX_READ = 4, ST_TOTALS = 8 };
 enum SeedError { SE_INDEX_RANGE = 1, SE_READ_TOO_LONG = 2 };
@@ -64,6 +77,7 @@ void sketch_stage_account(mm2b200_ctx *ctx);   // sketch.cu / post.cu: fold the 
 void post_stage_account(mm2b200_ctx *ctx);
 
 // launchers; each returns the number of kernels it enqueued
+int launch_seed_bloom(const DevIndex &ix, uint32_t *bloom, int32_t *bad, cudaStream_t s);     // fills ix.bloom from the live slots of H; *bad = 1: streams inconsistent
 int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cudaStream_t s);   // + scans over reads, totals, mini_pos packing
 int launch_seed_expand(const DevIndex &ix, const SeedWork &w, cudaStream_t s);
 int launch_seed_sort(const SeedWork &w, cudaStream_t s);

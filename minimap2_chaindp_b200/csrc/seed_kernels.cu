@@ -37,6 +37,10 @@ struct Hit { int t; int single; uint64_t v; };
 static __device__ __forceinline__ Hit idx_get(const DevIndex &ix, uint64_t minier, int64_t *err)
 {
 	Hit h; h.t = 0; h.single = 0; h.v = 0;
+	if (ix.bloom_mask) {                              // absent for sure when either bit is clear
+		const uint64_t b0 = bloom_bit(minier, 0, ix.bloom_mask), b1 = bloom_bit(minier, 1, ix.bloom_mask);
+		if (!((__ldg(ix.bloom + (b0 >> 5)) >> (b0 & 31)) & 1u) || !((__ldg(ix.bloom + (b1 >> 5)) >> (b1 & 31)) & 1u)) return h;
+	}
 	const uint4 rec = __ldg(ix.B + (minier & ((1ULL << ix.b) - 1)));
 	const uint64_t b0 = (uint64_t)rec.y << 32 | rec.x, b1 = (uint64_t)rec.w << 32 | rec.z;
 	const uint64_t h_off = b1 >> 28, p_off = (b1 & 0xfffffffULL) << 8 | b0 >> 56;
@@ -64,6 +68,39 @@ static __device__ __forceinline__ Hit idx_get(const DevIndex &ix, uint64_t minie
 		i = (i + (++step)) & m;
 		if (i == last) return h;
 	}
+}
+
+// one CTA per bucket: every live slot of its hash table sets the key's two bits
+__global__ void __launch_bounds__(256) k_seed_bloom(DevIndex ix, uint32_t *bloom, int32_t *bad)
+{
+	const int64_t n_bkt = (int64_t)1 << ix.b;
+	for (int64_t bk = blockIdx.x; bk < n_bkt; bk += gridDim.x) {
+		const uint4 rec = ix.B[bk];
+		const uint64_t b0 = (uint64_t)rec.y << 32 | rec.x, b1 = (uint64_t)rec.w << 32 | rec.z;
+		const uint64_t h_off = b1 >> 28;
+		const uint32_t n_buckets = (uint32_t)(b0 >> 24);
+		for (uint32_t i = threadIdx.x; i < n_buckets; i += blockDim.x) {
+			const uint64_t slot = h_off + i;
+			if (slot >= (uint64_t)ix.n_slots) { *bad = 1; break; }    // inconsistent streams: no filter, the lookup reports them
+			const uint8_t *grp = ix.H + 64 * (slot >> 3);
+			const uint32_t fl = (*(const uint32_t*)grp >> ((i & 0xfU) << 1)) & 3;
+			if (fl) continue;                                        // empty or deleted
+			const uint16_t *kp = (const uint16_t*)(grp + 4 + 6 * (slot & 7));
+			const uint64_t kk = (uint64_t)kp[0] | (uint64_t)kp[1] << 16 | (uint64_t)kp[2] << 32;
+			const uint64_t minier = (kk >> 1) << ix.b | (uint64_t)bk;
+			for (int wch = 0; wch < 2; ++wch) {
+				const uint64_t bit = bloom_bit(minier, wch, ix.bloom_mask);
+				atomicOr(bloom + (bit >> 5), 1u << (bit & 31));
+			}
+		}
+	}
+}
+
+int launch_seed_bloom(const DevIndex &ix, uint32_t *bloom, int32_t *bad, cudaStream_t s)
+{
+	const int64_t n_bkt = (int64_t)1 << ix.b;
+	k_seed_bloom<<<(int)(n_bkt < 65535 ? n_bkt : 65535), 256, 0, s>>>(ix, bloom, bad);
+	return 1;
 }
 
 // skip_seed (map.c:146-185).  Only bit 0 of flag opens the name-order block ("1 & flag & (...)", map.c:150).
