@@ -36,7 +36,8 @@ typedef struct {
 /* mm_sketch over n_reads sequences: read r owns seq[seq_off[r] .. seq_off[r+1]) (bytes as in the FASTA/FASTQ record: any case,
  * anything that is not A/C/G/T/U counts as ambiguous, sketch.c:8-25); rid[r] is mm_sketch's rid argument (NULL = 0 for every
  * read, what collect_minimizers passes for single-segment reads).  Empty reads are allowed and yield nothing.  Inputs are
- * host pointers and are not consumed. */
+ * host pointers and are not consumed.  Scratch: 16 bytes of HBM per base of the batch (MM2B200_ERR_NOMEM beyond what the
+ * device has: send fewer reads per call). */
 int mm2b200_sketch_batch(mm2b200_ctx_t *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, const int64_t *seq_off,
                          const char *seq, const uint32_t *rid, mm2b200_sketch_result_t *res);
 
