@@ -522,7 +522,8 @@ class Bench:
         h2d, wire_sub = ctx.upload_stats()      # bytes the last e2e step copied host -> device (counted by the library)
 
         # ---- e2e side legs (untimed for the headline): rank 0 alone, pageable input, the PCIe ceiling
-        solo_s = page_s = None
+        solo_s = page_s = regs_s = None
+        n_regs_out = 0
         self.cpu_barrier()
         if rank == 0:
             t0 = time.perf_counter()
@@ -537,6 +538,25 @@ class Bench:
             torch.cuda.synchronize()
             page_s = time.perf_counter() - t0
             del pageable
+            res = e2e_step()
+            # regions instead of chains (row f3): mm2b200_chain_regs_batch, same pinned anchors in, mm_reg1_t out
+            from minimap2_chaindp_b200 import post as mpost
+            hashes = ((np.arange(n_reads, dtype=np.uint64) * np.uint64(2654435761)) & np.uint64(0xffffffff)).astype(np.uint32)
+            qlens = np.full(n_reads, 12000, np.int32)
+            pp = mpost.post_params(spec.preset if spec.preset in mpost.POST_PRESETS else "map-ont")
+            rres = mpost._Regs()
+
+            def regs_step():
+                rc = mpost._lib().mm2b200_chain_regs_batch(ctx._h, C.byref(prm), C.byref(pp), n_reads, offs.ctypes.data, pin.ptr, hashes.ctypes.data,
+                                                           qlens.ctypes.data, 0, C.byref(rres))
+                if rc:
+                    raise api.ChainError(rc, api.last_error())
+            regs_step(); regs_step()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                regs_step()
+            regs_s = (time.perf_counter() - t0) / steps
+            n_regs_out = int(np.frombuffer((C.c_char * 8).from_address(rres.reg_off + 8 * n_reads), np.int64)[0])
             res = e2e_step()
         self.cpu_barrier()
         pcie_ms = self.pcie_ceiling_ms(pin, n_anchors, d2h)
@@ -595,7 +615,10 @@ class Bench:
                         "rank0_alone_ms_per_step": 1e3 * solo_s,
                         "scaling_efficiency": e2e_value / (world * solo_value),
                         "pageable_ms_per_step": 1e3 * page_s,
-                        "pageable_note": "anchors in ordinary host memory: the library stages every sub-batch through its own pinned buffer"},
+                        "pageable_note": "anchors in ordinary host memory: the library stages every sub-batch through its own pinned buffer",
+                        "regs": {"api": "mm2b200_chain_regs_batch (pinned host anchors in, mm_reg1_t out: mm_chain_dp + mm_gen_regs + chain_post on the device), rank 0 alone",
+                                 "ms_per_step": 1e3 * regs_s, "reads_per_s": n_reads / regs_s, "value": pairs_step / regs_s, "unit": UNIT,
+                                 "d2h_bytes_per_step": n_regs_out * 80 + (n_reads + 1) * 8, "regions": n_regs_out}},
                 "gpu_launches": int(launches),
                 "clocks": clocks,
                 "roofline": {"kernel": "k_fill", "bound": "int-issue", "achieved": int_achieved / 1e12, "peak": int_peak_mix / 1e12,

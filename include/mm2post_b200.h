@@ -67,7 +67,9 @@ typedef struct {
 } mm2b200_regs_t;
 
 /* mm_chain_dp + mm_gen_regs + chain_post over n_reads reads: read r owns a[offs[r] .. offs[r+1]) (sorted by x), hash[r] is
- * the read's name hash (map.c:347-349) and qlen[r] its length (qlen_sum).  Inputs are not consumed. */
+ * the read's name hash (map.c:347-349) and qlen[r] its length (qlen_sum).  Inputs are not consumed.  The batch runs as a
+ * pipeline of chunks of about 8 Mi anchors (MM2B200_REGS_CHUNK): the anchors of a chunk cross PCIe while the chunk before
+ * is chained and post-processed, and only the regions come back (page-locked a[] makes the upload a plain DMA). */
 int mm2b200_chain_regs_batch(mm2b200_ctx_t *ctx, const mm2b200_params_t *prm, const mm2b200_post_params_t *post,
                              int64_t n_reads, const int64_t *offs, const mm128_t *a, const uint32_t *hash, const int32_t *qlen,
                              int want_anchors, mm2b200_regs_t *res);

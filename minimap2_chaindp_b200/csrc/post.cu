@@ -14,8 +14,10 @@
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
+#include <vector>
 #include "mm2post_b200.h"
 #include "seed_internal.h"
 #include "sort_exact.cuh"
@@ -464,7 +466,8 @@ struct PostState {
 	void *d_block = nullptr; size_t cap_chains = 0, cap_reads = 0;
 	PostWork w{};
 	// host API
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr, copy_stream = nullptr;
+	cudaEvent_t ev_ready[2] = { nullptr, nullptr }, ev_free[2] = { nullptr, nullptr };
 	void *d_in = nullptr; size_t cap_in = 0;
 	void *h_regs = nullptr, *h_off = nullptr, *h_a = nullptr, *h_aoff = nullptr, *h_tot = nullptr;
 	size_t cap_h_regs = 0, cap_h_off = 0, cap_h_a = 0;
@@ -478,6 +481,8 @@ void post_state_free(void *p)
 	PostState *s = (PostState*)p;
 	cudaSetDevice(s->device);
 	if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+	if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
+	for (int k = 0; k < 2; ++k) { if (s->ev_ready[k]) cudaEventDestroy(s->ev_ready[k]); if (s->ev_free[k]) cudaEventDestroy(s->ev_free[k]); }
 	if (s->d_block) cudaFree(s->d_block);
 	if (s->d_in) cudaFree(s->d_in);
 	for (void *h : { s->h_regs, s->h_off, s->h_a, s->h_aoff, s->h_tot }) if (h) cudaFreeHost(h);
@@ -644,65 +649,117 @@ extern "C" int mm2b200_chain_regs_batch(mm2b200_ctx_t *ctx, const mm2b200_params
 	for (int64_t r = 0; r < n_reads; ++r) if (offs[r + 1] < offs[r]) return failf(MM2B200_ERR_ARG, "offs is not non-decreasing at read %lld", (long long)r);
 	const int64_t a0 = n_reads ? offs[0] : 0, A = n_reads ? offs[n_reads] - a0 : 0;
 	if (A && !a) return failf(MM2B200_ERR_ARG, "NULL anchor array");
-	if (A >= ((int64_t)1 << 31) - 64) return failf(MM2B200_ERR_ARG, "batch of %lld anchors exceeds the 2^31 index space of one device batch", (long long)A);
 	PostState *s = post_state(ctx);
 	std::lock_guard<std::mutex> lk(s->mu);
 	memset(res, 0, sizeof(*res));
 	CU_TRY(cudaSetDevice(s->device));
-	if (!s->stream) CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-	cudaStream_t st = s->stream;
+	if (!s->stream) {
+		CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+		CU_TRY(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+		for (int k = 0; k < 2; ++k) {
+			CU_TRY(cudaEventCreateWithFlags(&s->ev_ready[k], cudaEventDisableTiming));
+			CU_TRY(cudaEventCreateWithFlags(&s->ev_free[k], cudaEventDisableTiming));
+		}
+	}
+	cudaStream_t st = s->stream, cs = s->copy_stream;
 	const size_t R = (size_t)n_reads;
-	// inputs: anchors, offsets (rebased), hash, qlen
-	const size_t need = up256(16 * ((size_t)A + 1)) + up256(8 * (R + 1)) + 2 * up256(4 * (R + 1));
+	// Chunks of whole reads of about 8 Mi anchors: the anchors of chunk c+1 cross PCIe (copy stream, second input buffer) while
+	// chunk c is chained and post-processed; only the regions (80 B each) come back, so the bus carries little else.
+	int64_t chunk_anchors = (int64_t)8 << 20;
+	{ const char *e = getenv("MM2B200_REGS_CHUNK"); const long long v = e ? atoll(e) : 0; if (v > 0) chunk_anchors = (int64_t)v; }
+	std::vector<int64_t> cut(1, 0);
+	int64_t max_a = 1;
+	for (int64_t r = 0; r < n_reads; ++r)
+		if (offs[r + 1] - offs[cut.back()] >= chunk_anchors && r + 1 < n_reads) cut.push_back(r + 1);
+	cut.push_back(n_reads);
+	const size_t n_chunks = cut.size() - 1;
+	for (size_t c = 0; c < n_chunks; ++c) { const int64_t na = offs[cut[c + 1]] - offs[cut[c]]; if (na > max_a) max_a = na; }
+	if (max_a >= ((int64_t)1 << 31) - 64) return failf(MM2B200_ERR_ARG, "a read of %lld anchors exceeds the 2^31 index space of one device batch", (long long)max_a);
+	// device inputs: two anchor buffers, per-chunk offsets (rebased), hash, qlen
+	const size_t buf_b = up256(16 * ((size_t)max_a + 1));
+	const size_t need = 2 * buf_b + up256(8 * (R + n_chunks + 1)) + 2 * up256(4 * (R + 1));
 	if (need > s->cap_in) {
-		if (s->d_in) { CU_TRY(cudaStreamSynchronize(st)); cudaFree(s->d_in); s->d_in = nullptr; s->cap_in = 0; }
+		if (s->d_in) { CU_TRY(cudaDeviceSynchronize()); cudaFree(s->d_in); s->d_in = nullptr; s->cap_in = 0; }
 		const size_t want = need + need / 4;
-		if (cudaMalloc(&s->d_in, want) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaMalloc(%zu bytes) for a batch of %lld anchors failed", want, (long long)A); }
+		if (cudaMalloc(&s->d_in, want) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaMalloc(%zu bytes) for chunks of %lld anchors failed", want, (long long)max_a); }
 		s->cap_in = want;
 	}
 	char *cur = (char*)s->d_in;
-	mm128_t *d_a = (mm128_t*)cur; cur += up256(16 * ((size_t)A + 1));
-	int64_t *d_offs = (int64_t*)cur; cur += up256(8 * (R + 1));
+	mm128_t *d_a[2] = { (mm128_t*)cur, (mm128_t*)(cur + buf_b) }; cur += 2 * buf_b;
+	int64_t *d_offs = (int64_t*)cur; cur += up256(8 * (R + n_chunks + 1));
 	uint32_t *d_hash = (uint32_t*)cur; cur += up256(4 * (R + 1));
 	int32_t *d_qlen = (int32_t*)cur;
-	if ((rc = pin_reserve(&s->h_off, &s->cap_h_off, 8 * (R + 1) * 2 + 64))) return rc;
-	int64_t *h_off = (int64_t*)s->h_off;
-	for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? offs[r] - a0 : 0;
-	CU_TRY(cudaMemcpyAsync(d_offs, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	if ((rc = pin_reserve(&s->h_off, &s->cap_h_off, 8 * (R + n_chunks + 1) * 2 + 8 * (R + 1) + 64))) return rc;
+	int64_t *h_off = (int64_t*)s->h_off;                         // chunk c's offsets, relative to its first anchor, at h_off + cut[c] + c
+	int64_t *h_co = h_off + (R + n_chunks + 1);                  // per chunk: reg_off as the device wrote it
+	int64_t *h_roff = h_co + (R + n_chunks + 1);                 // reg_off of the whole batch
+	for (size_t c = 0; c < n_chunks; ++c)
+		for (int64_t r = cut[c]; r <= cut[c + 1]; ++r) h_off[r + (int64_t)c] = offs[r] - offs[cut[c]];
+	CU_TRY(cudaMemcpyAsync(d_offs, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, st));
 	if (R) {
 		CU_TRY(cudaMemcpyAsync(d_hash, hash, 4 * R, cudaMemcpyHostToDevice, st));
 		CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
 	}
-	if (A) CU_TRY(cudaMemcpyAsync(d_a, a + a0, 16 * (size_t)A, cudaMemcpyHostToDevice, st));
-	mm2b200_dev_result_t dev;
-	if ((rc = mm2b200_chain_device(ctx, prm, n_reads, A, d_offs, d_a, st, &dev))) return rc;
-	// every chain holds at least max(min_cnt, 1) anchors
-	const int64_t cap = A / (prm->min_cnt > 1 ? prm->min_cnt : 1) + 1;
-	mm2b200_dev_regs_t dr;
-	if ((rc = post_device_impl(ctx, s, post, n_reads, &dev, cap, d_hash, d_qlen, st, &dr))) return rc;
 	if (!s->h_tot) CU_TRY(cudaHostAlloc(&s->h_tot, 128, cudaHostAllocDefault));
 	int64_t *tot = (int64_t*)s->h_tot;
-	CU_TRY(cudaMemcpyAsync(tot, dr.d_totals, 64, cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaMemcpyAsync(tot + 8, dev.d_totals, 64, cudaMemcpyDeviceToHost, st));
-	int64_t *h_roff = h_off + (R + 1);
-	CU_TRY(cudaMemcpyAsync(h_roff, dr.d_reg_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
-	CU_TRY(cudaStreamSynchronize(st));
-	const size_t n_regs = (size_t)tot[0], n_b = (size_t)tot[8 + 1];
-	if ((rc = pin_reserve(&s->h_regs, &s->cap_h_regs, sizeof(Reg) * (n_regs + 1)))) return rc;
-	if (n_regs) CU_TRY(cudaMemcpyAsync(s->h_regs, dr.d_regs, sizeof(Reg) * n_regs, cudaMemcpyDeviceToHost, st));
+	if ((rc = pin_reserve(&s->h_regs, &s->cap_h_regs, sizeof(Reg) * (2 * R + 64)))) return rc;
+	int64_t *h_aoff = nullptr;
 	if (want_anchors) {
-		if ((rc = pin_reserve(&s->h_a, &s->cap_h_a, 16 * (n_b + 1) + 8 * (R + 1) + 256))) return rc;
-		if (n_b) CU_TRY(cudaMemcpyAsync(s->h_a, dev.d_b, 16 * n_b, cudaMemcpyDeviceToHost, st));
-		int64_t *h_aoff = (int64_t*)((char*)s->h_a + up256(16 * (n_b + 1)));
-		CU_TRY(cudaMemcpyAsync(h_aoff, dev.d_b_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+		if ((rc = pin_reserve(&s->h_a, &s->cap_h_a, up256(16 * ((size_t)A + 1)) + 8 * (R + 1) + 256))) return rc;
+		h_aoff = (int64_t*)((char*)s->h_a + up256(16 * ((size_t)A + 1)));
 		res->a = (const mm128_t*)s->h_a; res->a_off = h_aoff;
 	}
-	CU_TRY(cudaStreamSynchronize(st));
-	if (ctx_profile(ctx) && s->ev0) {
-		float t = 0;
-		if (cudaEventElapsedTime(&t, s->ev0, s->ev1) == cudaSuccess) s->ms += t;
-		cudaGetLastError();
+	auto upload = [&](size_t c) -> int {                          // chunk c's anchors into buffer c % 2, once its previous user is done
+		const int b = (int)(c & 1);
+		const int64_t lo = offs[cut[c]], na = offs[cut[c + 1]] - lo;
+		if (c >= 2) CU_TRY(cudaStreamWaitEvent(cs, s->ev_free[b], 0));
+		if (na) CU_TRY(cudaMemcpyAsync(d_a[b], a + lo, 16 * (size_t)na, cudaMemcpyHostToDevice, cs));
+		CU_TRY(cudaEventRecord(s->ev_ready[b], cs));
+		return MM2B200_OK;
+	};
+	int64_t tot_regs = 0, tot_chains = 0, tot_b = 0;
+	if ((rc = upload(0))) return rc;
+	for (size_t c = 0; c < n_chunks; ++c) {
+		const int b = (int)(c & 1);
+		const int64_t r0 = cut[c], nr = cut[c + 1] - cut[c], na = offs[cut[c + 1]] - offs[cut[c]];
+		CU_TRY(cudaStreamWaitEvent(st, s->ev_ready[b], 0));
+		mm2b200_dev_result_t dev;
+		if ((rc = mm2b200_chain_device(ctx, prm, nr, na, d_offs + r0 + (int64_t)c, d_a[b], st, &dev))) return rc;
+		const int64_t cap = na / (prm->min_cnt > 1 ? prm->min_cnt : 1) + 1;   // every chain holds at least max(min_cnt, 1) anchors
+		mm2b200_dev_regs_t dr;
+		if ((rc = post_device_impl(ctx, s, post, nr, &dev, cap, d_hash + r0, d_qlen + r0, st, &dr))) return rc;
+		CU_TRY(cudaEventRecord(s->ev_free[b], st));
+		CU_TRY(cudaMemcpyAsync(tot, dr.d_totals, 64, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaMemcpyAsync(tot + 8, dev.d_totals, 64, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaMemcpyAsync(h_co + r0 + (int64_t)c, dr.d_reg_off, 8 * ((size_t)nr + 1), cudaMemcpyDeviceToHost, st));
+		if (want_anchors) CU_TRY(cudaMemcpyAsync(h_aoff + r0, dev.d_b_off, 8 * ((size_t)nr + 1), cudaMemcpyDeviceToHost, st));
+		if (c + 1 < n_chunks && (rc = upload(c + 1))) return rc;  // the next chunk's upload is queued before this chunk is waited for
+		CU_TRY(cudaStreamSynchronize(st));
+		const int64_t n_regs = tot[0], n_b = tot[8 + 1];
+		if (sizeof(Reg) * (size_t)(tot_regs + n_regs + 1) > s->cap_h_regs) {        // grow, keeping what earlier chunks delivered
+			const size_t want = sizeof(Reg) * (size_t)(tot_regs + n_regs + 1) * 2;
+			void *q = nullptr;
+			if (cudaHostAlloc(&q, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return failf(MM2B200_ERR_NOMEM, "cudaHostAlloc(%zu bytes) for the regions failed", want); }
+			memcpy(q, s->h_regs, sizeof(Reg) * (size_t)tot_regs);
+			cudaFreeHost(s->h_regs);
+			s->h_regs = q; s->cap_h_regs = want;
+		}
+		if (n_regs) CU_TRY(cudaMemcpyAsync((Reg*)s->h_regs + tot_regs, dr.d_regs, sizeof(Reg) * (size_t)n_regs, cudaMemcpyDeviceToHost, st));
+		if (want_anchors && n_b) CU_TRY(cudaMemcpyAsync((mm128_t*)s->h_a + tot_b, dev.d_b, 16 * (size_t)n_b, cudaMemcpyDeviceToHost, st));
+		for (int64_t r = 0; r < nr; ++r) h_roff[r0 + r] = tot_regs + h_co[r0 + (int64_t)c + r];
+		if (want_anchors) for (int64_t r = 0; r < nr; ++r) h_aoff[r0 + r] += tot_b;
+		if (ctx_profile(ctx) && s->ev0) {
+			float t = 0;
+			if (cudaEventElapsedTime(&t, s->ev0, s->ev1) == cudaSuccess) s->ms += t;
+			cudaGetLastError();
+		}
+		tot_regs += n_regs; tot_chains += tot[8 + 0]; tot_b += n_b;
 	}
+	h_roff[R] = tot_regs;
+	if (want_anchors) h_aoff[R] = tot_b;
+	CU_TRY(cudaStreamSynchronize(st));
+	CU_TRY(cudaStreamSynchronize(cs));
+	tot[8 + 0] = tot_chains;
 	res->n_reads = n_reads; res->reg_off = h_roff; res->regs = (const mm2b200_reg_t*)s->h_regs; res->n_chains = tot[8 + 0];
 	return MM2B200_OK;
 }

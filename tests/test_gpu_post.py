@@ -29,6 +29,35 @@ def _oracle_regs(preset_post, over, offs, a, res, hashes, qlens):
     return regs, anchors
 
 
+@pytest.mark.parametrize("chunk", [0, 40000, 1])
+def test_batch_runs_as_a_pipeline_of_chunks(ctx, chunk, monkeypatch):
+    """MM2B200_REGS_CHUNK anchors per chunk (1 = every read its own chunk; default 8 Mi): uploads of later chunks overlap the
+    chaining of earlier ones, regions and anchors of all chunks come back in submission order"""
+    import oracle
+    from minimap2_chaindp_b200 import api, post, workload
+    if chunk:
+        monkeypatch.setenv("MM2B200_REGS_CHUNK", str(chunk))
+    else:
+        monkeypatch.delenv("MM2B200_REGS_CHUNK", raising=False)
+    n_reads = 400 if chunk != 1 else 60
+    spec = workload.CONFIGS["map-ont-100k"]
+    offs, a = workload.generate(spec, 7, n_reads)
+    offs = offs + 5                                         # absolute offsets into a larger array
+    a = np.concatenate([np.zeros((5, 2), np.uint64), a])
+    hashes = np.array([read_hash(r, 3) for r in range(n_reads)], np.uint32)
+    qlens = np.full(n_reads, 12000, np.int32)
+    want_chains = oracle.chain_batch(oracle.params(spec.preset), offs - 5, a[5:])
+    want, want_a = _oracle_regs("map-ont", {}, offs - 5, a[5:], want_chains, hashes, qlens)
+    got = post.chain_regs_batch(ctx, api.params(spec.preset), post.post_params("map-ont"), offs, a, hashes, qlens, want_anchors=True)
+    assert got.n_chains == int(want_chains.u_off[-1])
+    assert np.array_equal(np.diff(got.reg_off), [g.shape[0] for g in want]) and got.reg_off[0] == 0
+    assert np.array_equal(got.a_off, want_chains.b_off)
+    for r in range(n_reads):
+        assert got.regs[got.reg_off[r]:got.reg_off[r + 1]].tobytes() == want[r].tobytes(), f"chunk {chunk} read {r}"
+        a2, n_a = want_a[r]
+        assert np.array_equal(got.a[got.a_off[r]:got.a_off[r] + n_a], a2[:n_a])
+
+
 @pytest.mark.parametrize("name,preset_post,n_reads,over", [
     ("map-ont-100k", "map-ont", 3000, {}),
     ("map-ont-100k", "map-ont", 500, dict(pri_ratio=0.3, best_n=1)),
