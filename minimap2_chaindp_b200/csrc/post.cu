@@ -689,16 +689,21 @@ extern "C" int mm2b200_chain_regs_batch(mm2b200_ctx_t *ctx, const mm2b200_params
 	int64_t *d_offs = (int64_t*)cur; cur += up256(8 * (R + n_chunks + 1));
 	uint32_t *d_hash = (uint32_t*)cur; cur += up256(4 * (R + 1));
 	int32_t *d_qlen = (int32_t*)cur;
-	if ((rc = pin_reserve(&s->h_off, &s->cap_h_off, 8 * (R + n_chunks + 1) * 2 + 8 * (R + 1) + 64))) return rc;
+	if ((rc = pin_reserve(&s->h_off, &s->cap_h_off, 8 * (R + n_chunks + 1) * 2 + 16 * (R + 1) + 64))) return rc;
 	int64_t *h_off = (int64_t*)s->h_off;                         // chunk c's offsets, relative to its first anchor, at h_off + cut[c] + c
 	int64_t *h_co = h_off + (R + n_chunks + 1);                  // per chunk: reg_off as the device wrote it
 	int64_t *h_roff = h_co + (R + n_chunks + 1);                 // reg_off of the whole batch
 	for (size_t c = 0; c < n_chunks; ++c)
 		for (int64_t r = cut[c]; r <= cut[c + 1]; ++r) h_off[r + (int64_t)c] = offs[r] - offs[cut[c]];
-	CU_TRY(cudaMemcpyAsync(d_offs, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, st));
+	// the per-read arrays travel first on the copy stream, from page-locked memory: a copy from pageable memory queued on the
+	// compute stream can end up behind the anchor uploads on the copy engine and hold the first chunk's kernels back
+	uint32_t *h_hash = (uint32_t*)(h_roff + (R + 1));
+	int32_t *h_qlen = (int32_t*)(h_hash + (R + 1));
+	if (R) { memcpy(h_hash, hash, 4 * R); memcpy(h_qlen, qlen, 4 * R); }
+	CU_TRY(cudaMemcpyAsync(d_offs, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, cs));
 	if (R) {
-		CU_TRY(cudaMemcpyAsync(d_hash, hash, 4 * R, cudaMemcpyHostToDevice, st));
-		CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
+		CU_TRY(cudaMemcpyAsync(d_hash, h_hash, 4 * R, cudaMemcpyHostToDevice, cs));
+		CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, cs));
 	}
 	if (!s->h_tot) CU_TRY(cudaHostAlloc(&s->h_tot, 128, cudaHostAllocDefault));
 	int64_t *tot = (int64_t*)s->h_tot;

@@ -8,6 +8,8 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
+#include <time.h>
 #include <mutex>
 #include <new>
 #include <string>
@@ -17,6 +19,12 @@
 #include "packet_format.h"
 #include "mm2map_b200.h"
 
+namespace mm2b200 {
+// sketch.cu: mm2b200_sketch_device on bases that arrive in parts (reads [part_cut[k], part_cut[k+1]) are in HBM once part_ev[k] fired)
+int sketch_device_parts(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
+                        const char *d_seq, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv, int n_parts, const int64_t *part_cut,
+                        const cudaEvent_t *part_ev);
+}
 using namespace mm2b200;
 
 namespace {
@@ -36,6 +44,18 @@ int failf(int code, const char *fmt, ...)
 	return failf(MM2B200_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 
 inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
+
+// MM2B200_TRACE=1: host wall-clock marks of the composed path on stderr (ms since the call began)
+struct Trace {
+	bool on; struct timespec t0;
+	Trace() { const char *e = getenv("MM2B200_TRACE"); on = e && atoi(e); if (on) clock_gettime(CLOCK_MONOTONIC, &t0); }
+	void mark(const char *what) const
+	{
+		if (!on) return;
+		struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t);
+		fprintf(stderr, "[mm2b200 trace] %-28s %8.3f ms\n", what, 1e3 * (double)(t.tv_sec - t0.tv_sec) + 1e-6 * (double)(t.tv_nsec - t0.tv_nsec));
+	}
+};
 
 struct DevBuf {
 	void *p = nullptr; size_t cap = 0;
@@ -108,6 +128,7 @@ struct mm2b200_index {
 	PinBuf h_reg_off, h_regs, h_chunk_off;
 	cudaStream_t copy_stream = nullptr;
 	std::vector<cudaEvent_t> ev_chunk;
+	cudaEvent_t ev_small = nullptr;
 	int64_t launches = 0;
 	cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
 	double ms[3] = { 0, 0, 0 };
@@ -143,6 +164,7 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	ix->h_reg_off.release(); ix->h_regs.release(); ix->h_chunk_off.release();
 	if (ix->copy_stream) { cudaStreamSynchronize(ix->copy_stream); cudaStreamDestroy(ix->copy_stream); }
 	for (auto e : ix->ev_chunk) cudaEventDestroy(e);
+	if (ix->ev_small) cudaEventDestroy(ix->ev_small);
 	for (PinBuf *b : { &ix->h_stage, &ix->h_totals, &ix->h_rep, &ix->h_mini_off, &ix->h_mini, &ix->h_a_off, &ix->h_a,
 	                   &ix->h_n_u, &ix->h_u_off, &ix->h_b_off, &ix->h_u, &ix->h_b, &ix->h_rec_off, &ix->h_rec }) b->release();
 	for (auto &e : ix->ev) if (e) cudaEventDestroy(e);
@@ -591,6 +613,7 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	const int64_t b0 = n_reads ? seq_off[0] : 0, B = n_reads ? seq_off[n_reads] - b0 : 0;
 	if (B && !seq) return failf(MM2B200_ERR_ARG, "NULL sequence array");
 	std::lock_guard<std::mutex> lk(ix->mu);
+	const Trace tr;
 	memset(res, 0, sizeof(*res));
 	CU_TRY(cudaSetDevice(ix->device));
 	cudaStream_t st = ix->stream;
@@ -615,43 +638,74 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 		if ((rc = ix->d_reads.reserve(c.total()))) return rc;
 		c.place(ix->d_reads.p);
 	}
-	if ((rc = ix->h_stage.reserve(8 * (R + n_chunks + 1) + 4 * (R + 1)))) return rc;
+	if ((rc = ix->h_stage.reserve(8 * (R + n_chunks + 1) + 12 * (R + 1)))) return rc;
 	int64_t *h_off = ix->h_stage.as<int64_t>();                       // chunk c's offsets, relative to its first base, at h_off + cut[c] + c
 	int32_t *h_qlen = (int32_t*)(h_off + (R + n_chunks + 1));
+	uint32_t *h_bid = (uint32_t*)(h_qlen + (R + 1)), *h_hash = h_bid + (R + 1);
 	for (size_t c = 0; c < n_chunks; ++c)
 		for (int64_t r = cut[c]; r <= cut[c + 1]; ++r) h_off[r + (int64_t)c] = seq_off[r] - seq_off[cut[c]];
 	for (size_t r = 0; r < R; ++r) h_qlen[r] = (int32_t)(seq_off[r + 1] - seq_off[r]);      // qlen_sum of a single-segment read (map.c:340-341)
-	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, st));
+	// The per-read arrays go FIRST on the copy stream and from page-locked memory (bid / hash are staged: a copy from pageable
+	// memory on the compute stream was seen to run only after every queued upload of bases, which held the sketching back
+	// until the last base had crossed PCIe).
+	if (R) { memcpy(h_bid, bid, 4 * R); memcpy(h_hash, hash, 4 * R); }
+	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + n_chunks + 1), cudaMemcpyHostToDevice, ix->copy_stream));
 	if (R) {
-		CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, st));
-		CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
-		CU_TRY(cudaMemcpyAsync(d_hash, hash, 4 * R, cudaMemcpyHostToDevice, st));
+		CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, ix->copy_stream));
+		CU_TRY(cudaMemcpyAsync(d_bid, h_bid, 4 * R, cudaMemcpyHostToDevice, ix->copy_stream));
+		CU_TRY(cudaMemcpyAsync(d_hash, h_hash, 4 * R, cudaMemcpyHostToDevice, ix->copy_stream));
 	}
-	while (ix->ev_chunk.size() < n_chunks) {
+	if (!ix->ev_small) CU_TRY(cudaEventCreateWithFlags(&ix->ev_small, cudaEventDisableTiming));
+	CU_TRY(cudaEventRecord(ix->ev_small, ix->copy_stream));
+	CU_TRY(cudaStreamWaitEvent(st, ix->ev_small, 0));
+	// every chunk's bases are queued on the copy stream now, in parts of about MM2B200_MAP_PART bases (default 48 M) with an
+	// event behind each, so that the sketching of a part can start while the following parts are still on the bus
+	int64_t part_bases = 48000000;
+	{ const char *e = getenv("MM2B200_MAP_PART"); const long long v = e ? atoll(e) : 0; if (v > 0) part_bases = (int64_t)v; }
+	std::vector<int64_t> part_cut;                 // per chunk: read boundaries of its parts, relative to the chunk's first read
+	std::vector<size_t> part_first(n_chunks + 1, 0);
+	for (size_t c = 0; c < n_chunks; ++c) {
+		part_first[c] = part_cut.size();
+		part_cut.push_back(0);
+		int64_t last = cut[c];
+		for (int64_t r = cut[c]; r < cut[c + 1]; ++r)
+			if (seq_off[r + 1] - seq_off[last] >= part_bases && r + 1 < cut[c + 1]) { part_cut.push_back(r + 1 - cut[c]); last = r + 1; }
+		part_cut.push_back(cut[c + 1] - cut[c]);
+	}
+	part_first[n_chunks] = part_cut.size();
+	while (ix->ev_chunk.size() < part_cut.size()) {
 		cudaEvent_t e;
-		CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+		CU_TRY(cudaEventCreateWithFlags(&e, tr.on ? cudaEventDefault : cudaEventDisableTiming));   // timed only for the trace
 		ix->ev_chunk.push_back(e);
 	}
-	for (size_t c = 0; c < n_chunks; ++c) {                             // every chunk's bases, queued now, arriving in order
-		const int64_t lo = seq_off[cut[c]] - b0, nb = seq_off[cut[c + 1]] - seq_off[cut[c]];
-		if (nb) CU_TRY(cudaMemcpyAsync(d_seq + lo, seq + b0 + lo, (size_t)nb, cudaMemcpyHostToDevice, ix->copy_stream));
-		CU_TRY(cudaEventRecord(ix->ev_chunk[c], ix->copy_stream));
+	for (size_t c = 0; c < n_chunks; ++c) {
+		const size_t p0 = part_first[c], np = part_first[c + 1] - p0 - 1;       // parts k = 0 .. np-1 use events p0 + k
+		for (size_t k = 0; k < np; ++k) {
+			const int64_t ra = cut[c] + part_cut[p0 + k], rb = cut[c] + part_cut[p0 + k + 1];
+			const int64_t lo = seq_off[ra] - b0, nb = seq_off[rb] - seq_off[ra];
+			if (nb) CU_TRY(cudaMemcpyAsync(d_seq + lo, seq + b0 + lo, (size_t)nb, cudaMemcpyHostToDevice, ix->copy_stream));
+			CU_TRY(cudaEventRecord(ix->ev_chunk[p0 + k], ix->copy_stream));
+		}
 	}
 	if ((rc = ix->h_reg_off.reserve(8 * (R + 1))) || (rc = ix->h_rep.reserve(4 * (R + 1))) || (rc = ix->h_chunk_off.reserve(8 * (R + n_chunks + 1))) ||
 	    (rc = ix->h_regs.reserve(sizeof(mm2b200_reg_t) * (2 * R + 64)))) return rc;
 	int64_t *h_reg_off = ix->h_reg_off.as<int64_t>();
 	int64_t tot_regs = 0, tot_mv = 0, tot_anchors = 0, tot_chains = 0;
+	tr.mark("uploads queued");
+
 	for (size_t c = 0; c < n_chunks; ++c) {
 		const int64_t r0 = cut[c], nr = cut[c + 1] - cut[c], lo = seq_off[r0] - b0, nb = seq_off[cut[c + 1]] - seq_off[r0];
 		const int64_t *d_off_c = d_off + r0 + (int64_t)c;
-		CU_TRY(cudaStreamWaitEvent(st, ix->ev_chunk[c], 0));
-		// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0
+		// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0, part by part as the bases arrive
 		mm2b200_dev_sketch_t dsk;
 		int64_t n_mv = 0;
-		if ((rc = mm2b200_sketch_device(ix->ctx, sk, nr, nb, d_off_c, d_seq + lo, nullptr, st, &dsk, &n_mv))) return rc;
+		const size_t p0 = part_first[c], np = part_first[c + 1] - p0 - 1;
+		if ((rc = sketch_device_parts(ix->ctx, sk, nr, nb, d_off_c, d_seq + lo, st, &dsk, &n_mv, (int)np, part_cut.data() + p0, ix->ev_chunk.data() + p0))) return rc;
+		tr.mark("sketch counted");
 		// collect_seed_hits (map.c:187-236) on the minimizers where the sketch left them
 		SeedOut so;
 		if ((rc = seed_stage(ix, prm, nr, dsk.d_mv_off, dsk.d_mv, d_bid + r0, d_qlen + r0, so, n_mv, false))) return rc;
+		tr.mark("seeding queued");
 		// mm_chain_dp, then mm_gen_regs + chain_post (map.c:837-866)
 		mm2b200_dev_result_t dev;
 		if ((rc = mm2b200_chain_device(ix->ctx, &prm->chain, nr, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
@@ -665,6 +719,7 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 		CU_TRY(cudaMemcpyAsync(h_co, dr.d_reg_off, 8 * ((size_t)nr + 1), cudaMemcpyDeviceToHost, st));
 		if (nr) CU_TRY(cudaMemcpyAsync(ix->h_rep.as<int32_t>() + r0, so.w.rep_len, 4 * (size_t)nr, cudaMemcpyDeviceToHost, st));
 		CU_TRY(cudaStreamSynchronize(st));
+		tr.mark("chains + regions done");
 		const int64_t n_regs = tot[0];
 		if ((rc = ix->h_regs.reserve_keep(sizeof(mm2b200_reg_t) * (size_t)(tot_regs + n_regs + 1), sizeof(mm2b200_reg_t) * (size_t)tot_regs))) return rc;
 		if (n_regs) CU_TRY(cudaMemcpyAsync((mm2b200_reg_t*)ix->h_regs.p + tot_regs, dr.d_regs, sizeof(mm2b200_reg_t) * (size_t)n_regs, cudaMemcpyDeviceToHost, st));
@@ -679,6 +734,7 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	}
 	h_reg_off[R] = tot_regs;
 	CU_TRY(cudaStreamSynchronize(ix->copy_stream));
+	tr.mark("regions on the host");
 	res->n_reads = n_reads; res->reg_off = ix->h_reg_off.as<int64_t>(); res->regs = (const mm2b200_reg_t*)ix->h_regs.p;
 	res->rep_len = ix->h_rep.as<int32_t>();
 	res->n_minimizers = tot_mv; res->n_anchors = tot_anchors; res->n_chains = tot_chains;

@@ -12,6 +12,7 @@
 //           k-mers after a rescan, the first-window special case) is a function of the w+1 entries around it
 // One CTA per read walks it in tiles of 512 bases; three block scans per tile place tokens, steps and emitted minimizers.
 // A read's minimizers are first written to a slot of len entries (mm_sketch emits at most one per base), then packed.
+#include <vector>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -34,6 +35,7 @@ namespace {
 struct SketchWork {
 	const uint8_t *seq; const int64_t *seq_off; const uint32_t *rid;
 	int32_t n_reads, w, k, is_hpc;
+	int32_t r_begin, r_end;        // the reads this launch sketches (a batch may arrive in parts)
 	ulonglong2 *raw;               // slot of read r at seq_off[r]
 	int32_t *n_mv; int64_t *mv_off; ulonglong2 *mv; int64_t *totals;
 };
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 	const int w = W.w, k = W.k, hpc = W.is_hpc;
 	const uint64_t mask = (1ULL << 2 * k) - 1;
 	const bool fast = !hpc && 2 * k < 32;
-	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
+	for (int r = W.r_begin + blockIdx.x; r < W.r_end; r += gridDim.x) {
 		const int64_t s0 = W.seq_off[r];
 		const int len = (int)(W.seq_off[r + 1] - s0);
 		const uint8_t *str = W.seq + s0;
@@ -356,6 +358,7 @@ struct SketchState {
 	Buf d_raw, d_mv, d_small, d_in;
 	Buf h_off, h_mv, h_tot;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	std::vector<cudaEvent_t> ev_part;      // MM2B200_TRACE: one timing event behind every part of a part-wise sketch
 	double ms = 0; int64_t launches = 0;
 	SketchState() { h_off.pinned = h_mv.pinned = h_tot.pinned = true; }
 };
@@ -368,6 +371,7 @@ void sketch_state_free(void *p)
 	for (Buf *b : { &s->d_raw, &s->d_mv, &s->d_small, &s->d_in, &s->h_off, &s->h_mv, &s->h_tot }) b->release();
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
+	for (auto e : s->ev_part) cudaEventDestroy(e);
 	delete s;
 }
 
@@ -393,8 +397,11 @@ int check_sketch(const mm2b200_sketch_params_t *prm)
 }
 
 // kernels on `st`; waits once for the count; leaves the packing on the stream
+// n_parts > 0: the bases arrive in parts -- reads [part_cut[k], part_cut[k+1]) are in HBM once part_ev[k] has fired (the
+// composed path uploads them on a copy stream); each part is sketched as soon as it is there, the packing waits for all.
 int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases,
-                       const int64_t *d_seq_off, const char *d_seq, const uint32_t *d_rid, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv)
+                       const int64_t *d_seq_off, const char *d_seq, const uint32_t *d_rid, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv,
+                       int n_parts = 0, const int64_t *part_cut = nullptr, const cudaEvent_t *part_ev = nullptr)
 {
 	int rc;
 	const size_t R = (size_t)n_reads;
@@ -409,7 +416,7 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	W.n_mv = (int32_t*)cur; cur += up256(4 * (R + 1));
 	W.mv_off = (int64_t*)cur; cur += up256(8 * (R + 2));
 	W.totals = (int64_t*)cur;
-	const bool prof = ctx_profile(ctx) != 0;
+	const bool prof = ctx_profile(ctx) != 0, trace = prof && n_parts > 0 && getenv("MM2B200_TRACE") != nullptr;
 	if (prof) {
 		if (!s->ev0) { CU_TRY(cudaEventCreate(&s->ev0)); CU_TRY(cudaEventCreate(&s->ev1)); }
 		CU_TRY(cudaEventRecord(s->ev0, st));
@@ -419,17 +426,40 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	if (n_reads > 0) {
 		const int sm = ctx_sm_count(ctx);
 		int grid = (int)(n_reads < (int64_t)sm * 4 ? n_reads : (int64_t)sm * 4);
-		k_sketch<<<grid, SK_T, 0, st>>>(W);
+		if (n_parts <= 0) {
+			W.r_begin = 0; W.r_end = (int32_t)n_reads;
+			k_sketch<<<grid, SK_T, 0, st>>>(W);
+		} else {
+			for (int k = 0; k < n_parts; ++k) {
+				const int64_t nr = part_cut[k + 1] - part_cut[k];
+				CU_TRY(cudaStreamWaitEvent(st, part_ev[k], 0));
+				if (nr <= 0) continue;
+				W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1];
+				k_sketch<<<(int)(nr < (int64_t)sm * 4 ? nr : (int64_t)sm * 4), SK_T, 0, st>>>(W);
+				++launches;
+				if (trace) {
+					while ((int)s->ev_part.size() <= k) { cudaEvent_t e; CU_TRY(cudaEventCreate(&e)); s->ev_part.push_back(e); }
+					CU_TRY(cudaEventRecord(s->ev_part[k], st));
+				}
+			}
+			--launches;
+		}
 		k_sketch_scan<<<1, 1024, 0, st>>>(W);
 		CU_TRY(cudaGetLastError());
 		CU_TRY(cudaMemcpyAsync(s->h_tot.p, W.totals, 8, cudaMemcpyDeviceToHost, st));
 		CU_TRY(cudaStreamSynchronize(st));
+		if (trace) {
+			for (int k = 0; k < n_parts && k < (int)s->ev_part.size(); ++k) {
+				float t = 0, u = 0; cudaEventElapsedTime(&t, s->ev0, s->ev_part[k]); cudaEventElapsedTime(&u, s->ev0, part_ev[k]);
+				fprintf(stderr, "[mm2b200 trace] part %d: bases in HBM %.3f ms, sketched %.3f ms after the stage began\n", k, u, t);
+			}
+		}
 		total = *(int64_t*)s->h_tot.p;
 		if ((rc = s->d_mv.reserve(16 * ((size_t)total + 1)))) return rc;
 		W.mv = (ulonglong2*)s->d_mv.p;
 		k_sketch_pack<<<grid, 256, 0, st>>>(W);
 		CU_TRY(cudaGetLastError());
-		launches = 3;
+		launches += 3;
 	} else {
 		if ((rc = s->d_mv.reserve(16))) return rc;
 		CU_TRY(cudaMemsetAsync(W.mv_off, 0, 8, st));
@@ -453,6 +483,21 @@ void sketch_account(mm2b200_ctx_t *ctx, SketchState *s)
 }
 
 } // namespace
+
+// the composed path (seed_api.cu): mm2b200_sketch_device on bases that arrive in parts
+namespace mm2b200 {
+int sketch_device_parts(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
+                        const char *d_seq, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv, int n_parts, const int64_t *part_cut,
+                        const cudaEvent_t *part_ev)
+{
+	int rc;
+	if ((rc = check_sketch(prm))) return rc;
+	SketchState *s = sketch_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	CU_TRY(cudaSetDevice(s->device));
+	return sketch_device_impl(ctx, s, prm, n_reads, n_bases, d_seq_off, d_seq, nullptr, st, out, n_mv, n_parts, part_cut, part_ev);
+}
+}
 
 // after the caller has synchronised the stream: add the events' span to the stage time (the composed path, seed_api.cu)
 namespace mm2b200 { void sketch_stage_account(mm2b200_ctx *ctx) { SketchState *s = sketch_state(ctx); std::lock_guard<std::mutex> lk(s->mu); sketch_account(ctx, s); } }
