@@ -331,11 +331,14 @@ int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_re
 		// offsets relative to the first minimizer of the batch, staged in pinned memory together with bid / qlen
 		if ((rc = ix->h_stage.reserve(8 * (R + 1) + 8 * (R + 1)))) return rc;
 		int64_t *h_off = ix->h_stage.as<int64_t>();
+		uint32_t *h_bid = (uint32_t*)(h_off + (R + 1));
+		int32_t *h_qlen = (int32_t*)(h_bid + (R + 1));
 		for (size_t r = 0; r <= R; ++r) h_off[r] = n_reads ? mv_off[r] - m_base : 0;
+		if (R) { memcpy(h_bid, bid, 4 * R); memcpy(h_qlen, qlen, 4 * R); }
 		CU_TRY(cudaMemcpyAsync(d_mv_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
 		if (R) {
-			CU_TRY(cudaMemcpyAsync(d_bid, bid, 4 * R, cudaMemcpyHostToDevice, st));
-			CU_TRY(cudaMemcpyAsync(d_qlen, qlen, 4 * R, cudaMemcpyHostToDevice, st));
+			CU_TRY(cudaMemcpyAsync(d_bid, h_bid, 4 * R, cudaMemcpyHostToDevice, st));
+			CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, st));
 		}
 		if (M) CU_TRY(cudaMemcpyAsync(d_mv, mv + m_base, 16 * M, cudaMemcpyHostToDevice, st));
 		w.mv = d_mv; w.mv_off = d_mv_off; w.bid = d_bid; w.qlen = d_qlen;

@@ -279,6 +279,142 @@ __global__ void __launch_bounds__(SK_T) k_sketch(SketchWork W)
 	}
 }
 
+// ---- the common presets: no HPC, odd k <= 15 (map-ont, ava-ont: k = 15)
+// Three facts make this case much cheaper than the general kernel above:
+//  * a k-mer of odd length is never its own reverse complement (its middle base would have to be its own complement; a k-mer
+//    that is still filling up cannot be either: its forward image ends in zeros where the reverse image has a complemented
+//    base), so EVERY base is a step: the ring index of a base is its position, and the scans of tokens and steps fall away;
+//  * l = bases since the last ambiguous one, and an entry is real iff l >= k -- then its k-mer is the k bases up to it, read
+//    straight from the 2-bit image of the tile by position (what the k-mer holds while l < k never matters);
+//  * x = hash << 8 | k and y = rid << 32 | pos << 1 | strand follow from a 32-bit key and one strand bit per base.
+// The ring is a circular buffer of 1024 keys (a tile never looks back further than w < 256) whose first 256 slots are
+// mirrored behind its end, so a window is w + 1 consecutive words.  Four block barriers per tile of 512 bases.
+#define RK_N 1024
+#define RK_EMPTY 0xffffffffu
+
+__device__ __forceinline__ uint32_t rev2_32(uint32_t x)
+{
+	const uint32_t y = __brev(x);
+	return (y & 0x55555555u) << 1 | (y >> 1 & 0x55555555u);
+}
+
+template <int TW>                  // w at compile time (0: any w)
+__global__ void __launch_bounds__(SK_T, 3) k_sketch_odd(SketchWork W)
+{
+	__shared__ uint32_t rk[RK_N + SK_HALO];                // keys by position & 1023: the hash, or RK_EMPTY
+	__shared__ uint8_t rz[RK_N + SK_HALO];                 // strand of the entry
+	__shared__ __align__(8) uint32_t pw[64];               // 2-bit codes of the bases, 16 per word, by (position >> 4) & 63
+	__shared__ int s_lastN[SK_T / 32];
+	__shared__ uint32_t s_wE[SK_T / 32];
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	const int w = TW ? TW : W.w, k = W.k;
+	const uint32_t mask = (1u << 2 * k) - 1;
+	for (int r = W.r_begin + blockIdx.x; r < W.r_end; r += gridDim.x) {
+		const int64_t s0 = W.seq_off[r];
+		const int len = (int)(W.seq_off[r + 1] - s0);
+		const uint8_t *str = W.seq + s0;
+		ulonglong2 *out = W.raw + s0;
+		const uint64_t rid_hi = (uint64_t)(W.rid ? W.rid[r] : 0) << 32;
+		__syncthreads();
+		if (tid < SK_HALO) rk[RK_N - SK_HALO + tid] = RK_EMPTY;       // positions -256 .. -1
+		if (tid == 0) pw[63] = 0;
+		int carryN = -1, E0 = 0;                           // position of the last ambiguous base so far; minimizers emitted so far
+		for (int P0 = 0; P0 < len; P0 += SK_T) {
+			const int p = P0 + tid;
+			const bool active = p < len;
+			// ---- the base: 2-bit code, ambiguity (seq_nt4_table, sketch.c:8-25)
+			const uint32_t ch = active ? str[p] : 'N';
+			const uint32_t u = (ch | 0x20) - 'a';
+			const bool letter = u < 21 && (0x180045u >> u & 1);            // a c g t u
+			const bool valid = letter || ch < 4;
+			const uint32_t h = ch >> 1 & 3;
+			const uint32_t c = letter ? h ^ h >> 1 : ch & 3;               // A C T G -> 0 1 3 2
+			const bool isN = active && !valid;
+			const uint32_t nb = __ballot_sync(FULL, isN);
+			const uint32_t sh = 2 * (lane & 15);
+			const uint32_t lo = __reduce_or_sync(FULL, lane < 16 ? c << sh : 0u), hi = __reduce_or_sync(FULL, lane < 16 ? 0u : c << sh);
+			if (lane == 0) {
+				*(uint2*)&pw[(P0 >> 4 & 63) + 2 * wid] = make_uint2(lo, hi);
+				s_lastN[wid] = nb ? P0 + 32 * wid + 31 - __clz(nb) : -1;
+			}
+			const int anyN = __syncthreads_or(nb != 0);
+			int lastN = carryN;
+			if (anyN) {                                    // rare: a tile with ambiguous bases
+				const uint32_t mine = nb & (0xffffffffu >> (31 - lane));
+				int t = carryN;
+				for (int j = 0; j < SK_T / 32; ++j) { const int v = s_lastN[j]; if (j < wid && v > lastN) lastN = v; if (v > t) t = v; }
+				if (mine) lastN = P0 + 32 * wid + 31 - __clz(mine);
+				carryN = t;
+			}
+			// ---- k-mer, key, strand
+			uint32_t key = RK_EMPTY, z = 0;
+			const int l = valid ? p - lastN : 0;           // isN: lastN == p
+			if (active && l >= k) {
+				const int q = p - 15, a = q >> 4;
+				const uint32_t V = __funnelshift_r(pw[a & 63], pw[(a + 1) & 63], 2 * (q & 15));   // the 16 bases up to p, oldest lowest
+				const uint32_t kmer0 = rev2_32(V) & mask, kmer1 = ~V >> (32 - 2 * k);
+				z = kmer0 < kmer1 ? 0 : 1;
+				key = hash32m(z ? kmer1 : kmer0, mask);
+			}
+			const int slot = p & (RK_N - 1);
+			if (active) {
+				rk[slot] = key; rz[slot] = (uint8_t)z;
+				if (slot < SK_HALO) { rk[RK_N + slot] = key; rz[RK_N + slot] = (uint8_t)z; }
+			}
+			__syncthreads();
+			// ---- what the step pushes (sketch.c:118-137); entry j of the window is position p - w + j
+			const int base = (p - w) & (RK_N - 1);
+			const uint32_t *win = rk + base;
+			int cnt = 0, prev_j = 0, cur_j = 0;
+			uint32_t prev = RK_EMPTY, m = RK_EMPTY;
+			bool emitA = false, emitPrev = false, emitDup = false;
+			if (active) {
+				int cj = 0, eq = 0;
+				#pragma unroll
+				for (int j = 1; j < w; ++j) {
+					const uint32_t x = win[j];
+					if (x < m) { m = x; cj = j; eq = 1; }
+					else if (x == m) { cj = j; ++eq; }
+				}
+				const uint32_t old = win[0];
+				const bool old_min = old < m;
+				prev = old_min ? old : m;
+				prev_j = old_min ? 0 : cj;
+				if (l == w + k - 1 && prev != RK_EMPTY && !old_min && eq > 1) { emitA = true; cnt += eq - 1; }
+				if (key <= prev) {
+					if (l >= w + k && prev != RK_EMPTY) { emitPrev = true; ++cnt; }
+				} else if (old_min) {
+					if (l >= w + k - 1 && prev != RK_EMPTY) { emitPrev = true; ++cnt; }
+					const bool take = key <= m;
+					cur_j = take ? w : cj;
+					const int ndup = take ? (key == m ? eq : 0) : eq - 1;
+					if (l >= w + k - 1 && (take ? key : m) != RK_EMPTY && ndup > 0) { emitDup = true; cnt += ndup; }
+				}
+			}
+			const uint32_t e_sc = block_scan((uint32_t)cnt, s_wE, tid);
+			if (cnt) {
+				ulonglong2 *o = out + E0 + (int)(e_sc - (uint32_t)cnt);
+				const uint8_t *wz = rz + base;
+				auto y_of = [&](int j) { return rid_hi | (uint64_t)((uint32_t)(p - w + j) << 1) | (uint64_t)wz[j]; };
+				if (emitA) for (int j = 1; j < w; ++j) if (win[j] == prev && j != prev_j) *o++ = make_ulonglong2((uint64_t)prev << 8 | (uint64_t)k, y_of(j));
+				if (emitPrev) *o++ = make_ulonglong2((uint64_t)prev << 8 | (uint64_t)k, y_of(prev_j));
+				if (emitDup) {
+					const uint32_t cur = cur_j == w ? key : m;
+					for (int j = 1; j <= w; ++j) if (win[j] == cur && j != cur_j) *o++ = make_ulonglong2((uint64_t)cur << 8 | (uint64_t)k, y_of(j));
+				}
+			}
+			E0 += (int)s_wE[SK_T / 32 - 1];
+		}
+		// ---- the minimum that is still current at the end of the read (sketch.c:141-142)
+		if (tid == 0) {
+			uint32_t bx = RK_EMPTY; int bi = 0;
+			for (int i = len - w; i < len; ++i) { const uint32_t x = rk[i & (RK_N - 1)]; if (x <= bx) { bx = x; bi = i; } }
+			if (bx != RK_EMPTY && len > 0) out[E0++] = make_ulonglong2((uint64_t)bx << 8 | (uint64_t)k, rid_hi | (uint64_t)((uint32_t)bi << 1) | rz[bi & (RK_N - 1)]);
+			W.n_mv[r] = E0;
+		}
+	}
+}
+
 // exclusive scan of n_mv over the reads by one CTA
 __global__ void __launch_bounds__(1024) k_sketch_scan(SketchWork W)
 {
@@ -319,6 +455,7 @@ __global__ void __launch_bounds__(256) k_sketch_pack(SketchWork W)
 	}
 }
 
+inline bool getenv_off(const char *name) { const char *e = getenv(name); return e && e[0] == '0'; }
 inline size_t up256(size_t x) { return (x + 255) / 256 * 256; }
 
 struct Buf {
@@ -426,16 +563,24 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	if (n_reads > 0) {
 		const int sm = ctx_sm_count(ctx);
 		int grid = (int)(n_reads < (int64_t)sm * 4 ? n_reads : (int64_t)sm * 4);
+		// no HPC and an odd k <= 15: the specialised kernel (w = 5 and 10 unrolled: ava-ont, map-ont)
+		const bool odd = !W.is_hpc && (W.k & 1) && W.k <= 15 && !getenv_off("MM2B200_SKETCH_ODD");
+		auto launch = [&](int g) {
+			if (!odd) k_sketch<<<g, SK_T, 0, st>>>(W);
+			else if (W.w == 10) k_sketch_odd<10><<<g, SK_T, 0, st>>>(W);
+			else if (W.w == 5) k_sketch_odd<5><<<g, SK_T, 0, st>>>(W);
+			else k_sketch_odd<0><<<g, SK_T, 0, st>>>(W);
+		};
 		if (n_parts <= 0) {
 			W.r_begin = 0; W.r_end = (int32_t)n_reads;
-			k_sketch<<<grid, SK_T, 0, st>>>(W);
+			launch(grid);
 		} else {
 			for (int k = 0; k < n_parts; ++k) {
 				const int64_t nr = part_cut[k + 1] - part_cut[k];
 				CU_TRY(cudaStreamWaitEvent(st, part_ev[k], 0));
 				if (nr <= 0) continue;
 				W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1];
-				k_sketch<<<(int)(nr < (int64_t)sm * 4 ? nr : (int64_t)sm * 4), SK_T, 0, st>>>(W);
+				launch((int)(nr < (int64_t)sm * 4 ? nr : (int64_t)sm * 4));
 				++launches;
 				if (trace) {
 					while ((int)s->ev_part.size() <= k) { cudaEvent_t e; CU_TRY(cudaEventCreate(&e)); s->ev_part.push_back(e); }

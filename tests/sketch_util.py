@@ -2,7 +2,9 @@
 import numpy as np
 
 SETTINGS = [(10, 15, 0), (5, 15, 0), (10, 19, 1), (5, 19, 1), (19, 19, 0), (11, 21, 0), (3, 6, 0), (1, 4, 0), (4, 8, 1), (50, 28, 1),
-            (255, 11, 0), (16, 14, 0), (7, 2, 1)]       # (w, k, is_hpc); the presets use the first six
+            (255, 11, 0), (16, 14, 0), (7, 2, 1),
+            (3, 7, 0), (1, 5, 0), (19, 13, 0), (10, 1, 0), (200, 15, 0), (2, 3, 0)]   # (w, k, is_hpc); the presets use the first six;
+                                                        # no HPC with an odd k <= 15 runs the specialised kernel (k_sketch_odd)
 
 
 def sequences(rng, n=24, max_len=6000):

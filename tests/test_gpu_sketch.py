@@ -40,7 +40,7 @@ def test_every_branch_of_mm_sketch(ctx, w, k, hpc):
     assert _check(ctx, seqs, w, k, hpc, rid=np.arange(len(seqs)) % 7) > 0
 
 
-@pytest.mark.parametrize("w,k,hpc", SETTINGS[:6])
+@pytest.mark.parametrize("w,k,hpc", SETTINGS[:6] + [(200, 15, 0), (3, 7, 0), (255, 11, 0)])
 def test_reads_across_many_tiles(ctx, w, k, hpc):
     """10-60 kb reads (20-120 tiles of 512 bases): the carried ring, k-mer context and counters"""
     rng = np.random.default_rng(77 + w + k + hpc)
