@@ -38,6 +38,7 @@ struct SketchWork {
 	int32_t r_begin, r_end;        // the reads this launch sketches (a batch may arrive in parts)
 	ulonglong2 *raw;               // slot of read r at seq_off[r]
 	int32_t *n_mv; int64_t *mv_off; ulonglong2 *mv; int64_t *totals;
+	int *next_read;                // k_sketch_odd: the launch's work counter (starts at 0)
 };
 
 __device__ __forceinline__ uint64_t hash64m(uint64_t key, uint64_t mask)     // sketch.c:27-37
@@ -309,21 +310,28 @@ __global__ void __launch_bounds__(SK_T, 3) k_sketch_odd(SketchWork W)
 	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	const int w = TW ? TW : W.w, k = W.k;
 	const uint32_t mask = (1u << 2 * k) - 1;
-	for (int r = W.r_begin + blockIdx.x; r < W.r_end; r += gridDim.x) {
+	__shared__ int s_r;
+	for (;;) {
+		__syncthreads();
+		if (tid == 0) s_r = W.r_begin + atomicAdd(W.next_read, 1);     // reads are handed out one by one: they differ in length
+		__syncthreads();
+		const int r = s_r;
+		if (r >= W.r_end) break;
 		const int64_t s0 = W.seq_off[r];
 		const int len = (int)(W.seq_off[r + 1] - s0);
 		const uint8_t *str = W.seq + s0;
 		ulonglong2 *out = W.raw + s0;
 		const uint64_t rid_hi = (uint64_t)(W.rid ? W.rid[r] : 0) << 32;
-		__syncthreads();
 		if (tid < SK_HALO) rk[RK_N - SK_HALO + tid] = RK_EMPTY;       // positions -256 .. -1
 		if (tid == 0) pw[63] = 0;
 		int carryN = -1, E0 = 0;                           // position of the last ambiguous base so far; minimizers emitted so far
+		uint32_t ch_next = tid < len ? str[tid] : 'N';     // the tile's base is fetched one tile ahead
 		for (int P0 = 0; P0 < len; P0 += SK_T) {
 			const int p = P0 + tid;
 			const bool active = p < len;
 			// ---- the base: 2-bit code, ambiguity (seq_nt4_table, sketch.c:8-25)
-			const uint32_t ch = active ? str[p] : 'N';
+			const uint32_t ch = ch_next;
+			ch_next = p + SK_T < len ? str[p + SK_T] : 'N';
 			const uint32_t u = (ch | 0x20) - 'a';
 			const bool letter = u < 21 && (0x180045u >> u & 1);            // a c g t u
 			const bool valid = letter || ch < 4;
@@ -369,12 +377,21 @@ __global__ void __launch_bounds__(SK_T, 3) k_sketch_odd(SketchWork W)
 			uint32_t prev = RK_EMPTY, m = RK_EMPTY;
 			bool emitA = false, emitPrev = false, emitDup = false;
 			if (active) {
-				int cj = 0, eq = 0;
-				#pragma unroll
-				for (int j = 1; j < w; ++j) {
-					const uint32_t x = win[j];
-					if (x < m) { m = x; cj = j; eq = 1; }
-					else if (x == m) { cj = j; ++eq; }
+				int cj = 0, eq = 0;                        // newest entry that equals the minimum, and how many do
+				if (TW > 0 && TW <= 32) {                  // unrolled: the minimum first, then a bit mask of the entries equal to it
+					uint32_t x[TW > 0 ? TW : 1], em = 0;
+					#pragma unroll
+					for (int j = 1; j < TW; ++j) { x[j] = win[j]; m = x[j] < m ? x[j] : m; }
+					#pragma unroll
+					for (int j = 1; j < TW; ++j) if (x[j] == m) em |= 1u << j;
+					eq = __popc(em);
+					cj = em ? 31 - __clz(em) : 0;
+				} else {
+					for (int j = 1; j < w; ++j) {
+						const uint32_t x = win[j];
+						if (x < m) { m = x; cj = j; eq = 1; }
+						else if (x == m) { cj = j; ++eq; }
+					}
 				}
 				const uint32_t old = win[0];
 				const bool old_min = old < m;
@@ -542,7 +559,7 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 {
 	int rc;
 	const size_t R = (size_t)n_reads;
-	if ((rc = s->d_raw.reserve(16 * ((size_t)n_bases + 1))) || (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256)) ||
+	if ((rc = s->d_raw.reserve(16 * ((size_t)n_bases + 1))) || (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256 + up256(4 * ((size_t)(n_parts > 0 ? n_parts : 1) + 1)))) ||
 	    (rc = s->h_tot.reserve(64))) return rc;
 	SketchWork W;
 	memset(&W, 0, sizeof(W));
@@ -552,7 +569,8 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	char *cur = (char*)s->d_small.p;
 	W.n_mv = (int32_t*)cur; cur += up256(4 * (R + 1));
 	W.mv_off = (int64_t*)cur; cur += up256(8 * (R + 2));
-	W.totals = (int64_t*)cur;
+	W.totals = (int64_t*)cur; cur += 256;
+	int *counters = (int*)cur;                                         // one work counter per launch of k_sketch_odd
 	const bool prof = ctx_profile(ctx) != 0, trace = prof && n_parts > 0 && getenv("MM2B200_TRACE") != nullptr;
 	if (prof) {
 		if (!s->ev0) { CU_TRY(cudaEventCreate(&s->ev0)); CU_TRY(cudaEventCreate(&s->ev1)); }
@@ -562,7 +580,8 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	int launches = 0;
 	if (n_reads > 0) {
 		const int sm = ctx_sm_count(ctx);
-		int grid = (int)(n_reads < (int64_t)sm * 4 ? n_reads : (int64_t)sm * 4);
+		const int64_t resident = (int64_t)sm * 3;                       // both kernels: 512 threads of 40 registers
+		int grid = (int)(n_reads < resident ? n_reads : resident);
 		// no HPC and an odd k <= 15: the specialised kernel (w = 5 and 10 unrolled: ava-ont, map-ont)
 		const bool odd = !W.is_hpc && (W.k & 1) && W.k <= 15 && !getenv_off("MM2B200_SKETCH_ODD");
 		auto launch = [&](int g) {
@@ -571,6 +590,8 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 			else if (W.w == 5) k_sketch_odd<5><<<g, SK_T, 0, st>>>(W);
 			else k_sketch_odd<0><<<g, SK_T, 0, st>>>(W);
 		};
+		if (odd) CU_TRY(cudaMemsetAsync(counters, 0, 4 * ((size_t)(n_parts > 0 ? n_parts : 1)), st));
+		W.next_read = counters;
 		if (n_parts <= 0) {
 			W.r_begin = 0; W.r_end = (int32_t)n_reads;
 			launch(grid);
@@ -579,8 +600,8 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 				const int64_t nr = part_cut[k + 1] - part_cut[k];
 				CU_TRY(cudaStreamWaitEvent(st, part_ev[k], 0));
 				if (nr <= 0) continue;
-				W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1];
-				launch((int)(nr < (int64_t)sm * 4 ? nr : (int64_t)sm * 4));
+				W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1]; W.next_read = counters + k;
+				launch((int)(nr < resident ? nr : resident));
 				++launches;
 				if (trace) {
 					while ((int)s->ev_part.size() <= k) { cudaEvent_t e; CU_TRY(cudaEventCreate(&e)); s->ev_part.push_back(e); }
@@ -602,7 +623,7 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 		total = *(int64_t*)s->h_tot.p;
 		if ((rc = s->d_mv.reserve(16 * ((size_t)total + 1)))) return rc;
 		W.mv = (ulonglong2*)s->d_mv.p;
-		k_sketch_pack<<<grid, 256, 0, st>>>(W);
+		k_sketch_pack<<<(int)(n_reads < (int64_t)sm * 8 ? n_reads : (int64_t)sm * 8), 256, 0, st>>>(W);
 		CU_TRY(cudaGetLastError());
 		launches += 3;
 	} else {
