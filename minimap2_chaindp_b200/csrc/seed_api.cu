@@ -623,10 +623,9 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	if (!ix->copy_stream) CU_TRY(cudaStreamCreateWithFlags(&ix->copy_stream, cudaStreamNonBlocking));
 	const size_t R = (size_t)n_reads;
 	// Chunks of whole reads of about MM2B200_MAP_CHUNK bases (default 2 G: the sketching slots take 16 B per base, so a chunk
-	// stays below 32 GB of scratch).  The bases of later chunks cross PCIe on a copy stream while earlier chunks compute.
-	// Measured on a B200 (1 Gbase per call): smaller chunks do NOT pay -- every stage's tail (the single-thread replay of the
-	// reference's unstable sort for reads with tied anchors above all) is paid once per chunk: 75.7 ms in one chunk, 77.9 in
-	// two, 88.7 in six -- so the default keeps a batch whole unless memory says otherwise.
+	// stays below 32 GB of scratch).  A chunk is a memory bound, not a pipeline stage: inside a chunk the upload already hides
+	// behind the sketching (parts, below), the kernels of a 1-Gbase call add up to more than its upload, and every stage's tail
+	// is paid once per chunk -- so the default keeps a batch whole unless memory says otherwise.
 	int64_t chunk_bases = 2000000000;
 	{ const char *e = getenv("MM2B200_MAP_CHUNK"); const long long v = e ? atoll(e) : 0; if (v > 0) chunk_bases = (int64_t)v; }
 	std::vector<int64_t> cut(1, 0);
