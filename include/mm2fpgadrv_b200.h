@@ -9,13 +9,16 @@
  * response packets (new_seed[] + mini_pos[], map.c:533-565) come back through fpga_get_retbuf.
  *
  * Behind the boundary (not the FPGA's structure): submitted packets are queued; a worker thread (MM2B200_SHIM_WORKERS per GPU,
- * default 2, each with its own context and copy of the index streams, so that one copies packets while the other's batch is
- * on the device) takes EVERYTHING that is waiting (bounded by MM2B200_SHIM_BATCH_MV minimizers), turns it into one device
- * batch, and cuts the results back into one response packet per request packet.  Request and response buffers are recycled
- * through size-classed free lists.  While a batch computes, the fork's worker threads keep submitting, so the
- * batch size adapts to the load without a timer.  With several GPUs (MM2B200_DEVICES=0,1,... or all visible devices with
- * MM2B200_DEVICES=all; default: $MM2B200_DEVICE or 0) the index is replicated and the packets are shared out; reads are
- * independent, there is no collective.
+ * default 2, each with its own context and copy of the index streams, so that one batch's packets cross PCIe while the
+ * other's is computed) takes EVERYTHING that is waiting (bounded by MM2B200_SHIM_BATCH_MV minimizers) as one device batch.
+ * The buffers handed out by fpga_get_writebuf and fpga_get_retbuf are PAGE-LOCKED and recycled through size-classed free
+ * lists: a request packet is DMA'd to HBM as the fork wrote it and the minimizers are pulled out of the packet layout on the
+ * device; the response packets (headers, records, mini_pos, zero padding) are laid out in HBM and DMA'd into their
+ * buffers -- no host thread copies a packet.  (MM2B200_SHIM_ZEROCOPY=0, or a batch the device refuses as a whole, goes the
+ * careful way instead: staged and cut on the host, halved on refusal.)  While a batch computes, the fork's worker threads
+ * keep submitting, so the batch size adapts to the load without a timer.  With several GPUs (MM2B200_DEVICES=0,1,... or all
+ * visible devices with MM2B200_DEVICES=all; default: $MM2B200_DEVICE or 0) the index is replicated and the packets are
+ * shared out; reads are independent, there is no collective.
  *
  * No CPU fallback inside the library.  A read the device cannot take (more than 2^21 anchors, a batch of one read that does
  * not fit the GPU) is answered with collect_result_t.err_flag = 1, which is the fork's own protocol for "host, redo this read"

@@ -11,10 +11,12 @@
 // A batch the device refuses (allocation failure, anchor count beyond the index space) is halved and retried; a single read
 // that still fails is answered with err_flag = 1, the fork's own "host, redo this read" protocol (map.c:933-944).
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -58,34 +60,54 @@ struct Shim {
 	std::vector<std::unique_ptr<ShimDevice>> dev;
 	int64_t max_bytes = (int64_t)1 << 30;
 	int64_t batch_mv = (int64_t)8 << 20;
+	bool direct = true;                // packets are DMA'd as they are (MM2B200_SHIM_ZEROCOPY=0: staged and cut by the worker)
 	std::atomic<int64_t> n_packets{0}, n_reads{0}, n_batches{0}, n_err{0};
 };
 
 // Packet buffers (requests and responses, a few hundred KB each) come from size-classed free lists: a fresh malloc of that
-// size is an mmap whose pages fault in on first touch -- measured, that cost more than the device batch itself.
+// size is an mmap whose pages fault in on first touch -- measured, that cost more than the device batch itself.  The buffers
+// are PAGE-LOCKED (cudaHostAlloc, portable): the fork fills a request packet in place and the GPU's copy engine reads it
+// from there; response packets are written by the copy engine and handed to the fork as they are.  Ordinary memory is the
+// fallback when page-locked memory runs out (the copies then go through the driver's own staging) or with
+// MM2B200_SHIM_ZEROCOPY=0.
 struct BufPool {
 	static const int N_CLASS = 24;                 // 4 KB << c
 	std::mutex mu;
 	std::vector<void*> free_list[N_CLASS];
 	int64_t pooled = 0, cap = (int64_t)2 << 30;
+	int device = 0;
+	bool pin = true;
+	// 16-byte prefix: [0] size class (-1: larger than the largest class), [1] 1 = page-locked
 	static int cls(size_t n) { int c = 0; while (((size_t)4096 << c) < n + 16 && c < N_CLASS - 1) ++c; return c; }
+	char *raw_alloc(size_t bytes, int64_t c)
+	{
+		char *q = nullptr;
+		int64_t pinned = 0;
+		if (pin) {
+			int cur = -1;
+			if (cudaGetDevice(&cur) == cudaSuccess && cur != device) cudaSetDevice(device);
+			if (cudaHostAlloc((void**)&q, bytes, cudaHostAllocPortable) == cudaSuccess) pinned = 1;
+			else { cudaGetLastError(); q = nullptr; }
+		}
+		if (!q) q = (char*)malloc(bytes);
+		if (!q) return nullptr;
+		((int64_t*)q)[0] = c; ((int64_t*)q)[1] = pinned;
+		return q;
+	}
+	static void raw_free(char *q) { if (((int64_t*)q)[1]) cudaFreeHost(q); else free(q); }
 	void *get(size_t n)
 	{
 		const int c = cls(n);
-		if (((size_t)4096 << c) < n + 16) {            // larger than the largest class: plain malloc, class -1
-			char *q = (char*)malloc(n + 16);
-			if (!q) return nullptr;
-			*(int64_t*)q = -1;
-			return q + 16;
+		if (((size_t)4096 << c) < n + 16) {            // larger than the largest class: not recycled
+			char *q = raw_alloc(n + 16, -1);
+			return q ? q + 16 : nullptr;
 		}
 		{
 			std::lock_guard<std::mutex> lk(mu);
 			if (!free_list[c].empty()) { void *q = free_list[c].back(); free_list[c].pop_back(); pooled -= (int64_t)4096 << c; return (char*)q + 16; }
 		}
-		char *q = (char*)malloc((size_t)4096 << c);
-		if (!q) return nullptr;
-		*(int64_t*)q = c;
-		return q + 16;
+		char *q = raw_alloc((size_t)4096 << c, c);
+		return q ? q + 16 : nullptr;
 	}
 	void put(void *user)
 	{
@@ -96,12 +118,12 @@ struct BufPool {
 			std::lock_guard<std::mutex> lk(mu);
 			if (pooled + ((int64_t)4096 << c) <= cap) { free_list[c].push_back(q); pooled += (int64_t)4096 << c; return; }
 		}
-		free(q);
+		raw_free(q);
 	}
 	void drain()
 	{
 		std::lock_guard<std::mutex> lk(mu);
-		for (auto &l : free_list) { for (void *q : l) free(q); l.clear(); }
+		for (auto &l : free_list) { for (void *q : l) raw_free((char*)q); l.clear(); }
 		pooled = 0;
 	}
 };
@@ -268,6 +290,91 @@ void run_group(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &prm, std::ve
 	}
 }
 
+// The whole batch in one device call with no host copy of a packet (seed_internal.h: seed_packets_begin / _end): the request
+// packets are DMA'd as they are, the response packets are laid out in HBM and DMA'd into their buffers.  false = the device
+// refused the batch as a whole (the caller then goes the careful way: halves, err_flag for a single refused read).
+bool process_batch_direct(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &prm, const std::vector<Packet> &pkts, const std::vector<PktHead> &heads,
+                          const std::vector<std::pair<size_t, size_t>> &span, const std::vector<ReadRef> &reads, std::vector<Packet> &out)
+{
+	const size_t P = pkts.size(), R = reads.size();
+	static const bool trace = [] { const char *e = getenv("MM2B200_TRACE"); return e && atoi(e); }();
+	struct timespec t0, t1, t2, t3;
+	if (trace) clock_gettime(CLOCK_MONOTONIC, &t0);
+	std::vector<const void*> req(P);
+	std::vector<int64_t> req_size(P), base(P);
+	int64_t at = 0;
+	for (size_t p = 0; p < P; ++p) { req[p] = pkts[p].buf; req_size[p] = pkts[p].size; base[p] = at; at += pkt_up64(pkts[p].size); }
+	std::vector<int64_t> src16(R);
+	std::vector<int32_t> n_mv(R), qlen(R);
+	std::vector<uint32_t> bid(R);
+	for (size_t k = 0; k < R; ++k) {
+		const ReadRef &r = reads[k];
+		src16[k] = (base[(size_t)r.pkt] + (r.mv - (const char*)pkts[(size_t)r.pkt].buf)) / 16;
+		n_mv[k] = r.task.seednum; bid[k] = r.task.bid; qlen[k] = r.task.qlensum;
+	}
+	PacketCounts cnt;
+	int rc = seed_packets_begin(d.idx, &prm, (int)P, req.data(), req_size.data(), (int64_t)R, src16.data(), n_mv.data(), bid.data(), qlen.data(), &cnt);
+	if (rc != MM2B200_OK) {
+		if ((rc == MM2B200_ERR_CUDA || rc == MM2B200_ERR_STATE) && shim_abort_on_error()) shim_fatal("device batch failed", mm2b200_last_error());
+		return false;
+	}
+	if (trace) clock_gettime(CLOCK_MONOTONIC, &t1);
+	// response layout (map.c:495-501,533-565): chaindp_sndhdr_t, then per read collect_result_t + records + mini_pos
+	std::vector<int64_t> resp_size(P), rec_dst(R), mini_dst(R), hdr_dst;
+	std::vector<char> hdr;
+	hdr_dst.reserve(P + R); hdr.reserve(64 * (P + R));
+	int64_t o = 0;
+	for (size_t p = 0; p < P; ++p) {
+		const int64_t start = o;
+		PktHead oh;
+		memset(&oh, 0, sizeof(oh));
+		oh.magic = heads[p].magic; oh.tid = heads[p].tid; oh.num = heads[p].num; oh.type = heads[p].type; oh.lat = heads[p].lat;
+		const size_t head_at = hdr.size();
+		hdr_dst.push_back(o); hdr.insert(hdr.end(), (const char*)&oh, (const char*)&oh + sizeof(oh));
+		o += sizeof(PktHead);
+		for (size_t k = span[p].first; k < span[p].second; ++k) {
+			const int64_t n_rec = cnt.rec_off[k + 1] - cnt.rec_off[k], n_mini = cnt.mini_off[k + 1] - cnt.mini_off[k];
+			const int64_t rec_b = pkt_up64(n_rec * (int64_t)sizeof(struct new_seed)), mini_b = pkt_up64(n_mini * 8);
+			PktResult pr;
+			memset(&pr, 0, sizeof(pr));
+			pr.read_id = reads[k].task.read_id;
+			pr.n_a = (uint32_t)n_rec; pr.n_minipos = (uint32_t)n_mini; pr.rep_len = (uint32_t)cnt.rep_len[k];
+			pr.sub_size = (uint32_t)(sizeof(PktResult) + rec_b + mini_b);
+			hdr_dst.push_back(o); hdr.insert(hdr.end(), (const char*)&pr, (const char*)&pr + sizeof(pr));
+			o += sizeof(PktResult);
+			rec_dst[k] = o; o += rec_b;
+			mini_dst[k] = o; o += mini_b;
+		}
+		resp_size[p] = o - start;
+		if (resp_size[p] > 0x7fffffffLL) shim_fatal("response", "a response packet exceeds 2 GiB (fpga_get_retbuf reports its size as int)");
+		const uint32_t sz = (uint32_t)resp_size[p];
+		memcpy(hdr.data() + head_at + offsetof(PktHead, size), &sz, sizeof(sz));
+	}
+	std::vector<void*> resp(P);
+	for (size_t p = 0; p < P; ++p) {
+		resp[p] = g_pool.get((size_t)resp_size[p]);
+		if (!resp[p]) shim_fatal("response", "out of host memory");
+	}
+	if (trace) clock_gettime(CLOCK_MONOTONIC, &t2);
+	rc = seed_packets_end(d.idx, (int)P, resp.data(), resp_size.data(), (int64_t)R, rec_dst.data(), mini_dst.data(), (int64_t)hdr_dst.size(), hdr.data(), hdr_dst.data());
+	if (rc != MM2B200_OK) {
+		for (void *q : resp) g_pool.put(q);
+		if ((rc == MM2B200_ERR_CUDA || rc == MM2B200_ERR_STATE) && shim_abort_on_error()) shim_fatal("device batch failed", mm2b200_last_error());
+		return false;
+	}
+	if (trace) {
+		clock_gettime(CLOCK_MONOTONIC, &t3);
+		auto ms = [](const struct timespec &a, const struct timespec &b) { return 1e3 * (double)(b.tv_sec - a.tv_sec) + 1e-6 * (double)(b.tv_nsec - a.tv_nsec); };
+		int64_t in_b = 0, out_b = 0;
+		for (size_t p = 0; p < P; ++p) { in_b += pkts[p].size; out_b += resp_size[p]; }
+		fprintf(stderr, "[mm2b200 trace] shim batch: %zu packets, %zu reads, %.1f MB in, %.1f MB out: upload + seeding + fill %.2f ms, layout + buffers %.2f ms, scatter + download %.2f ms\n",
+		        P, R, 1e-6 * (double)in_b, 1e-6 * (double)out_b, ms(t0, t1), ms(t1, t2), ms(t2, t3));
+	}
+	S.n_batches.fetch_add(1);
+	for (size_t p = 0; p < P; ++p) out.push_back(Packet{resp[p], (uint32_t)resp_size[p]});
+	return true;
+}
+
 // parse, run, answer.  Appends one response packet per request packet to `out`.
 void process_batch(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &base, const std::vector<Packet> &pkts, std::vector<Packet> &out)
 {
@@ -306,6 +413,11 @@ void process_batch(Shim &S, ShimDevice &d, const mm2b200_seed_params_t &base, co
 		while (g < keys.size() && keys[g] != key) ++g;
 		if (g == keys.size()) { keys.push_back(key); groups.emplace_back(); }
 		groups[g].push_back((int)k);
+	}
+	if (S.direct && groups.size() == 1 && !reads.empty()) {
+		mm2b200_seed_params_t q = base;
+		q.chain.max_dist_x = keys[0].first; q.chain.max_dist_y = keys[0].second; q.chain.n_segs = keys[0].second;   // as below
+		if (process_batch_direct(S, d, q, pkts, heads, span, reads, out)) return;
 	}
 	std::vector<int> last_call;
 	for (size_t g = 0; g < groups.size(); ++g) {
@@ -412,8 +524,10 @@ extern "C" int fpga_init(int flag)
 	std::unique_ptr<Shim> S(new Shim());
 	S->max_bytes = env_i64("MM2B200_SHIM_MAX_BYTES", S->max_bytes);
 	S->batch_mv = env_i64("MM2B200_SHIM_BATCH_MV", S->batch_mv);
+	{ const char *e = getenv("MM2B200_SHIM_ZEROCOPY"); S->direct = !(e && e[0] == '0'); }
+	{ const std::vector<int> devs = shim_devices(); g_pool.pin = S->direct; g_pool.device = devs.empty() ? 0 : devs[0]; }
 	// two workers per GPU by default (each with its own context and copy of the index streams): while one batch is on the
-	// device the other worker copies packets into staging / cuts responses
+	// device the other worker parses packets / lays out responses (and, on the careful path, copies them)
 	const int per_dev = (int)env_i64("MM2B200_SHIM_WORKERS", 2);
 	for (int ord : shim_devices()) for (int rep = 0; rep < per_dev; ++rep) {
 		std::unique_ptr<ShimDevice> d(new ShimDevice());

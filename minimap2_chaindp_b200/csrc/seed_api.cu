@@ -129,6 +129,11 @@ struct mm2b200_index {
 	cudaStream_t copy_stream = nullptr;
 	std::vector<cudaEvent_t> ev_chunk;
 	cudaEvent_t ev_small = nullptr;
+	// packet path of the driver shim (seed_packets_begin / _end): raw request packets, gathered minimizers, response packets
+	DevBuf d_pkt_in, d_pkt_mv, d_pkt_meta, d_pkt_out;
+	PinBuf h_pkt, h_pkt_cnt;
+	const int64_t *pk_rec_off = nullptr, *pk_mini_off = nullptr; const void *pk_rec = nullptr; const uint64_t *pk_mini = nullptr;
+	int64_t pk_reads = -1, pk_rec_total = 0;
 	int64_t launches = 0;
 	cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
 	double ms[3] = { 0, 0, 0 };
@@ -162,6 +167,7 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	ix->d_bloom.release();
 	ix->d_in.release(); ix->d_work.release(); ix->d_anchor.release(); ix->d_reads.release();
 	ix->h_reg_off.release(); ix->h_regs.release(); ix->h_chunk_off.release();
+	ix->d_pkt_in.release(); ix->d_pkt_mv.release(); ix->d_pkt_meta.release(); ix->d_pkt_out.release(); ix->h_pkt.release(); ix->h_pkt_cnt.release();
 	if (ix->copy_stream) { cudaStreamSynchronize(ix->copy_stream); cudaStreamDestroy(ix->copy_stream); }
 	for (auto e : ix->ev_chunk) cudaEventDestroy(e);
 	if (ix->ev_small) cudaEventDestroy(ix->ev_small);
@@ -489,6 +495,183 @@ extern "C" int mm2b200_seed_fill_batch(mm2b200_index_t *ix, const mm2b200_seed_p
 	memset(res, 0, sizeof(*res));
 	return seed_fill_locked(ix, prm, n_reads, mv_off, mv, bid, qlen, res);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// packets in, packets out: the device side of the driver shim (fpgadrv_shim.cu)
+// ---------------------------------------------------------------------------------------------------------
+// The shim's request buffers are page-locked (it hands them out itself, fpga_get_writebuf), so a request packet is DMA'd to
+// HBM as it is and the minimizers are pulled out of the packet layout there; the response packets are laid out in HBM and
+// DMA'd straight into page-locked response buffers.  No byte of a packet is copied by a host thread.
+namespace {
+
+__global__ void __launch_bounds__(256) k_pkt_gather(const ulonglong2 *raw, const int64_t *src16, const int64_t *mv_off, ulonglong2 *mv, int n_reads)
+{
+	for (int r = blockIdx.x; r < n_reads; r += gridDim.x) {
+		const ulonglong2 *s = raw + src16[r];
+		ulonglong2 *d = mv + mv_off[r];
+		const int n = (int)(mv_off[r + 1] - mv_off[r]);
+		for (int i = threadIdx.x; i < n; i += blockDim.x) d[i] = s[i];
+	}
+}
+
+// read r's records (24 B each) and mini_pos words behind its collect_result_t, each area padded with zeros to 64 bytes
+__global__ void __launch_bounds__(256) k_pkt_scatter(uint64_t *out, const int64_t *rec_dst, const int64_t *mini_dst, const int64_t *rec_off, int64_t rec_total,
+                                                      const uint64_t *rec, const int64_t *mini_off, const uint64_t *mini, int n_reads)
+{
+	for (int r = blockIdx.x; r < n_reads; r += gridDim.x) {
+		const int64_t r0 = rec_off[r], n_rec = (r + 1 < n_reads ? rec_off[r + 1] : rec_total) - r0;
+		const int64_t m0 = mini_off[r], n_mini = mini_off[r + 1] - m0;
+		{
+			const int64_t words = 3 * n_rec, padded = (24 * n_rec + 63) / 64 * 8;
+			uint64_t *d = out + rec_dst[r] / 8;
+			const uint64_t *s = rec + 3 * r0;
+			for (int64_t i = threadIdx.x; i < padded; i += blockDim.x) d[i] = i < words ? s[i] : 0;
+		}
+		{
+			const int64_t padded = (8 * n_mini + 63) / 64 * 8;
+			uint64_t *d = out + mini_dst[r] / 8;
+			const uint64_t *s = mini + m0;
+			for (int64_t i = threadIdx.x; i < padded; i += blockDim.x) d[i] = i < n_mini ? s[i] : 0;
+		}
+	}
+}
+
+// the 64-byte headers (chaindp_sndhdr_t, collect_result_t), built by the host
+__global__ void __launch_bounds__(256) k_pkt_headers(ulonglong2 *out, const ulonglong2 *hdr, const int64_t *hdr_dst, int64_t n_hdr)
+{
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < 4 * n_hdr) out[hdr_dst[i >> 2] / 16 + (i & 3)] = hdr[i];
+}
+
+} // namespace
+
+namespace mm2b200 {
+
+int seed_packets_begin(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int n_pkts, const void *const *req, const int64_t *req_size,
+                       int64_t n_reads, const int64_t *src16, const int32_t *n_mv, const uint32_t *bid, const int32_t *qlen, PacketCounts *out)
+{
+	int rc;
+	if (!ix || !prm || !out || n_pkts <= 0 || n_reads <= 0 || n_reads >= ((int64_t)1 << 31) - 1) return failf(MM2B200_ERR_ARG, "bad packet batch");
+	if (!ix->committed) return failf(MM2B200_ERR_STATE, "index not committed (mm2b200_index_commit)");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	ix->pk_reads = -1;
+	CU_TRY(cudaSetDevice(ix->device));
+	cudaStream_t st = ix->stream;
+	const size_t R = (size_t)n_reads;
+	int64_t raw_bytes = 0, M = 0;
+	for (int p = 0; p < n_pkts; ++p) raw_bytes += pkt_up64(req_size[p]);
+	// per-read arrays through page-locked staging: mv_off (prefix sums), src16, bid, qlen
+	if ((rc = ix->h_pkt.reserve(16 * (R + 1) + 8 * (R + 1)))) return rc;
+	int64_t *h_off = ix->h_pkt.as<int64_t>(), *h_src = h_off + (R + 1);
+	uint32_t *h_bid = (uint32_t*)(h_src + (R + 1));
+	int32_t *h_qlen = (int32_t*)(h_bid + (R + 1));
+	for (size_t r = 0; r < R; ++r) {
+		if (n_mv[r] < 0 || src16[r] < 0 || 16 * (src16[r] + (int64_t)n_mv[r]) > raw_bytes) return failf(MM2B200_ERR_ARG, "read %zu lies outside its packet", r);
+		h_off[r] = M; M += n_mv[r]; h_src[r] = src16[r]; h_bid[r] = bid[r]; h_qlen[r] = qlen[r];
+	}
+	h_off[R] = M;
+	int64_t *d_off, *d_src; uint32_t *d_bid; int32_t *d_qlen;
+	{
+		Carver c;
+		c.add(&d_off, 8 * (R + 1)); c.add(&d_src, 8 * (R + 1)); c.add(&d_bid, 4 * (R + 1)); c.add(&d_qlen, 4 * (R + 1));
+		if ((rc = ix->d_pkt_meta.reserve(c.total()))) return rc;
+		c.place(ix->d_pkt_meta.p);
+	}
+	if ((rc = ix->d_pkt_in.reserve((size_t)raw_bytes + 64)) || (rc = ix->d_pkt_mv.reserve(16 * ((size_t)M + 1)))) return rc;
+	CU_TRY(cudaMemcpyAsync(d_off, h_off, 8 * (R + 1), cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_src, h_src, 8 * R, cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_bid, h_bid, 4 * R, cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_qlen, h_qlen, 4 * R, cudaMemcpyHostToDevice, st));
+	const Trace tr;
+	static thread_local cudaEvent_t tev[3] = { nullptr, nullptr, nullptr };
+	if (tr.on) { for (auto &e : tev) if (!e) cudaEventCreate(&e); cudaEventRecord(tev[0], st); }
+	int64_t at = 0;
+	for (int p = 0; p < n_pkts; ++p) {
+		if (req_size[p] > 0) CU_TRY(cudaMemcpyAsync((char*)ix->d_pkt_in.p + at, req[p], (size_t)req_size[p], cudaMemcpyHostToDevice, st));
+		at += pkt_up64(req_size[p]);
+	}
+	if (tr.on) cudaEventRecord(tev[1], st);
+	tr.mark("packets queued");
+	const int sm = ctx_sm_count(ix->ctx);
+	k_pkt_gather<<<(int)(n_reads < (int64_t)sm * 8 ? n_reads : (int64_t)sm * 8), 256, 0, st>>>((const ulonglong2*)ix->d_pkt_in.p, d_src, d_off, (ulonglong2*)ix->d_pkt_mv.p, (int)n_reads);
+	CU_TRY(cudaGetLastError());
+	++ix->launches;
+	// collect_seed_hits, then mm_chain_dp_fpga, on the minimizers where the gather left them
+	SeedOut so;
+	if ((rc = seed_stage(ix, prm, n_reads, d_off, (const mm128_t*)ix->d_pkt_mv.p, d_bid, d_qlen, so, M, false))) return rc;
+	mm2b200_dev_records_t dev;
+	if ((rc = mm2b200_fill_device(ix->ctx, &prm->chain, n_reads, so.n_anchors, so.w.a_off, (const mm128_t*)so.w.a, st, &dev))) return rc;
+	if ((rc = ix->h_pkt_cnt.reserve(8 * (R + 1) + 8 * (R + 1) + 4 * (R + 1) + 64))) return rc;
+	int64_t *h_rec_off = ix->h_pkt_cnt.as<int64_t>(), *h_mini_off = h_rec_off + (R + 1), *h_tot = h_mini_off + (R + 1);
+	int32_t *h_rep = (int32_t*)(h_tot + 8);
+	CU_TRY(cudaMemcpyAsync(h_tot, dev.d_totals, 64, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(h_rec_off, dev.d_rec_off, 8 * R, cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(h_mini_off, so.w.mini_off, 8 * (R + 1), cudaMemcpyDeviceToHost, st));
+	CU_TRY(cudaMemcpyAsync(h_rep, so.w.rep_len, 4 * R, cudaMemcpyDeviceToHost, st));
+	if (tr.on) cudaEventRecord(tev[2], st);
+	CU_TRY(cudaStreamSynchronize(st));
+	tr.mark("counts on the host");
+	if (tr.on) {
+		float a = 0, b = 0; cudaEventElapsedTime(&a, tev[0], tev[1]); cudaEventElapsedTime(&b, tev[1], tev[2]);
+		fprintf(stderr, "[mm2b200 trace] device: %d packets (%.1f MB) uploaded in %.3f ms, gather + seeding + fill %.3f ms\n", n_pkts, 1e-6 * (double)raw_bytes, a, b);
+	}
+	seed_finish(ix, so);
+	h_rec_off[R] = h_tot[3];
+	ix->pk_rec_off = dev.d_rec_off; ix->pk_rec = dev.d_rec; ix->pk_rec_total = h_tot[3];
+	ix->pk_mini_off = so.w.mini_off; ix->pk_mini = so.w.mini_out;
+	ix->pk_reads = n_reads;
+	out->rec_off = h_rec_off; out->mini_off = h_mini_off; out->rep_len = h_rep; out->n_anchors = so.n_anchors;
+	return MM2B200_OK;
+}
+
+int seed_packets_end(mm2b200_index *ix, int n_pkts, void *const *resp, const int64_t *resp_size, int64_t n_reads,
+                     const int64_t *rec_dst, const int64_t *mini_dst, int64_t n_hdr, const void *hdr, const int64_t *hdr_dst)
+{
+	int rc;
+	if (!ix || n_pkts <= 0 || n_reads <= 0 || n_hdr <= 0) return failf(MM2B200_ERR_ARG, "bad packet batch");
+	std::lock_guard<std::mutex> lk(ix->mu);
+	if (ix->pk_reads != n_reads) return failf(MM2B200_ERR_STATE, "seed_packets_end without the matching seed_packets_begin");
+	ix->pk_reads = -1;
+	CU_TRY(cudaSetDevice(ix->device));
+	cudaStream_t st = ix->stream;
+	const size_t R = (size_t)n_reads, H = (size_t)n_hdr;
+	int64_t out_bytes = 0;
+	for (int p = 0; p < n_pkts; ++p) {
+		if (resp_size[p] % 64) return failf(MM2B200_ERR_ARG, "a response packet is not a multiple of 64 bytes");
+		out_bytes += resp_size[p];
+	}
+	if ((rc = ix->h_pkt.reserve(16 * (R + 1) + 72 * (H + 1)))) return rc;
+	int64_t *h_rec_dst = ix->h_pkt.as<int64_t>(), *h_mini_dst = h_rec_dst + (R + 1), *h_hdr_dst = h_mini_dst + (R + 1);
+	char *h_hdr = (char*)(h_hdr_dst + (H + 1));
+	memcpy(h_rec_dst, rec_dst, 8 * R); memcpy(h_mini_dst, mini_dst, 8 * R); memcpy(h_hdr_dst, hdr_dst, 8 * H); memcpy(h_hdr, hdr, 64 * H);
+	int64_t *d_rec_dst, *d_mini_dst, *d_hdr_dst; char *d_hdr;
+	{
+		Carver c;
+		c.add(&d_rec_dst, 8 * (R + 1)); c.add(&d_mini_dst, 8 * (R + 1)); c.add(&d_hdr_dst, 8 * (H + 1)); c.add(&d_hdr, 64 * (H + 1));
+		if ((rc = ix->d_pkt_meta.reserve(c.total()))) return rc;        // the arrays of _begin are no longer needed
+		c.place(ix->d_pkt_meta.p);
+	}
+	if ((rc = ix->d_pkt_out.reserve((size_t)out_bytes + 64))) return rc;
+	CU_TRY(cudaMemcpyAsync(d_rec_dst, h_rec_dst, 8 * R, cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_mini_dst, h_mini_dst, 8 * R, cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_hdr_dst, h_hdr_dst, 8 * H, cudaMemcpyHostToDevice, st));
+	CU_TRY(cudaMemcpyAsync(d_hdr, h_hdr, 64 * H, cudaMemcpyHostToDevice, st));
+	const int sm = ctx_sm_count(ix->ctx);
+	k_pkt_scatter<<<(int)(n_reads < (int64_t)sm * 8 ? n_reads : (int64_t)sm * 8), 256, 0, st>>>((uint64_t*)ix->d_pkt_out.p, d_rec_dst, d_mini_dst, ix->pk_rec_off, ix->pk_rec_total,
+	                                                                                               (const uint64_t*)ix->pk_rec, ix->pk_mini_off, ix->pk_mini, (int)n_reads);
+	k_pkt_headers<<<(unsigned)((4 * H + 255) / 256), 256, 0, st>>>((ulonglong2*)ix->d_pkt_out.p, (const ulonglong2*)d_hdr, d_hdr_dst, n_hdr);
+	CU_TRY(cudaGetLastError());
+	ix->launches += 2;
+	int64_t at = 0;
+	for (int p = 0; p < n_pkts; ++p) {
+		if (resp_size[p] > 0) CU_TRY(cudaMemcpyAsync(resp[p], (const char*)ix->d_pkt_out.p + at, (size_t)resp_size[p], cudaMemcpyDeviceToHost, st));
+		at += resp_size[p];
+	}
+	CU_TRY(cudaStreamSynchronize(st));
+	return MM2B200_OK;
+}
+
+} // namespace mm2b200
 
 // ---------------------------------------------------------------------------------------------------------
 // packet level: the fork's wire format

@@ -82,4 +82,18 @@ int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cuda
 int launch_seed_expand(const DevIndex &ix, const SeedWork &w, cudaStream_t s);
 int launch_seed_sort(const SeedWork &w, cudaStream_t s);
 
+// ---- the driver shim's device path (seed_api.cu): request packets -> HBM -> response packets, no host copy of a packet
+// _begin: the request packets req[p] (req_size[p] bytes; page-locked memory makes each a plain DMA) are laid end to end,
+// each padded to 64 bytes; read r has n_mv[r] minimizers at 16 * src16[r] bytes into that concatenation.  Runs
+// collect_seed_hits + mm_chain_dp_fpga and returns the per-read counts (page-locked, valid until the next call on the index):
+// rec_off[n_reads+1], mini_off[n_reads+1], rep_len[n_reads].  The records and mini_pos stay in HBM for _end.
+// _end: resp[p] (resp_size[p] bytes, multiples of 64) laid end to end the same way; read r's records go to byte rec_dst[r]
+// and its mini_pos to mini_dst[r] of that concatenation (each area zero-padded to 64 bytes), the n_hdr 64-byte headers in
+// hdr to hdr_dst[]; returns when every response packet is in host memory.  Same thread, back to back, one batch at a time.
+struct PacketCounts { const int64_t *rec_off, *mini_off; const int32_t *rep_len; int64_t n_anchors; };
+int seed_packets_begin(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int n_pkts, const void *const *req, const int64_t *req_size,
+                       int64_t n_reads, const int64_t *src16, const int32_t *n_mv, const uint32_t *bid, const int32_t *qlen, PacketCounts *out);
+int seed_packets_end(mm2b200_index *ix, int n_pkts, void *const *resp, const int64_t *resp_size, int64_t n_reads,
+                     const int64_t *rec_dst, const int64_t *mini_dst, int64_t n_hdr, const void *hdr, const int64_t *hdr_dst);
+
 } // namespace mm2b200

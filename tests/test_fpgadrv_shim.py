@@ -114,8 +114,12 @@ def _pump(packets, n_threads=4):
     return got
 
 
-def test_request_packets_of_the_reference_through_the_driver_symbols():
+@pytest.mark.parametrize("zerocopy", ["1", "0"])
+def test_request_packets_of_the_reference_through_the_driver_symbols(monkeypatch, zerocopy):
+    """both data paths of the shim: packets DMA'd as they are and laid out on the device (default), and the careful path that
+    stages and cuts them on the host (MM2B200_SHIM_ZEROCOPY=0; also what a refused batch falls back to)"""
     from minimap2_chaindp_b200 import fpgadrv
+    monkeypatch.setenv("MM2B200_SHIM_ZEROCOPY", zerocopy)
     fpgadrv.init()
     try:
         for path in GOLD:                                   # each fixture loads a new index over the old one
