@@ -117,6 +117,7 @@ struct mm2b200_index {
 	std::vector<uint8_t> host[4];          // B, H, V, P chunks appended until commit
 	bool committed = false;
 	DevBuf d_stream[4], d_bloom;
+	size_t l2_window = 0; float l2_ratio = 0;  // presence filter kept in L2 while the lookup runs (0: not available / switched off)
 	DevIndex dix{};
 	int64_t resident_bytes = 0;
 	// per-batch state
@@ -231,7 +232,7 @@ extern "C" int mm2b200_index_commit(mm2b200_index_t *ix)
 	ix->dix.b = b;
 	ix->dix.n_slots = (int64_t)(nV / 8);
 	ix->dix.n_pos = (int64_t)(nP / 8);
-	ix->dix.bloom = nullptr; ix->dix.bloom_mask = 0;
+	ix->dix.bloom = nullptr; ix->dix.bloom_mask = 0; ix->l2_window = 0;
 	{	// presence filter over the live keys (seed_internal.h): >= 8 bits per hash slot, at least 2^20, at most 2^33 bits
 		const char *eb = getenv("MM2B200_SEED_BLOOM");
 		if (!(eb && atoi(eb) == 0) && ix->dix.n_slots > 0) {
@@ -248,7 +249,25 @@ extern "C" int mm2b200_index_commit(mm2b200_index_t *ix)
 			CU_TRY(cudaStreamSynchronize(ix->stream));
 			CU_TRY(cudaGetLastError());
 			if (bad) { ix->dix.bloom = nullptr; ix->dix.bloom_mask = 0; }      // a bucket points outside H: the lookup will say so
-			else ix->resident_bytes += (int64_t)(bits / 8);
+			else {
+				ix->resident_bytes += (int64_t)(bits / 8);
+				// The filter is probed at random by every minimizer while the lookup streams gigabytes of minimizers and results
+				// through L2: marked persisting for that kernel (a carve-out of L2 no streaming line can evict), its probes stop
+				// going to HBM.  MM2B200_SEED_L2PIN=0 switches this off.
+				const char *ep = getenv("MM2B200_SEED_L2PIN");
+				cudaDeviceProp prop;
+				if (!(ep && atoi(ep) == 0) && cudaGetDeviceProperties(&prop, ix->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0 && prop.accessPolicyMaxWindowSize > 0) {
+					const size_t bytes = (size_t)(bits / 8);
+					const size_t carve = bytes < (size_t)prop.persistingL2CacheMaxSize ? bytes : (size_t)prop.persistingL2CacheMaxSize;
+					size_t cur = 0;
+					cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+					if (cur >= carve || cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess) {
+						ix->l2_window = bytes < (size_t)prop.accessPolicyMaxWindowSize ? bytes : (size_t)prop.accessPolicyMaxWindowSize;
+						ix->l2_ratio = ix->l2_window <= carve ? 1.0f : (float)carve / (float)ix->l2_window;
+					}
+					cudaGetLastError();
+				}
+			}
 		}
 	}
 	ix->committed = true;
@@ -353,7 +372,20 @@ int seed_stage(mm2b200_index *ix, const mm2b200_seed_params_t *prm, int64_t n_re
 	w.flag = prm->flag; w.max_occ = prm->max_occ;
 	const bool prof = ctx_profile(ix->ctx) != 0;
 	if (prof) CU_TRY(cudaEventRecord(ix->ev[0], st));
+	if (ix->l2_window) {
+		cudaStreamAttrValue av;
+		memset(&av, 0, sizeof(av));
+		av.accessPolicyWindow.base_ptr = (void*)ix->dix.bloom; av.accessPolicyWindow.num_bytes = ix->l2_window;
+		av.accessPolicyWindow.hitRatio = ix->l2_ratio; av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting; av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+		if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av) != cudaSuccess) { cudaGetLastError(); ix->l2_window = 0; }
+	}
 	ix->launches += launch_seed_lookup(ix->dix, w, ctx_sm_count(ix->ctx), st);
+	if (ix->l2_window) {                           // the kernels behind the lookup get an ordinary L2 again
+		cudaStreamAttrValue av;
+		memset(&av, 0, sizeof(av));
+		cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
+		cudaGetLastError();
+	}
 	if (prof) CU_TRY(cudaEventRecord(ix->ev[1], st));
 	if ((rc = ix->h_totals.reserve(8 * ST_TOTALS * 2))) return rc;
 	int64_t *tot = ix->h_totals.as<int64_t>();
