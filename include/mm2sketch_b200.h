@@ -53,6 +53,24 @@ typedef struct {
 int mm2b200_sketch_device(mm2b200_ctx_t *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
                           const char *d_seq, const uint32_t *d_rid, void *stream, mm2b200_dev_sketch_t *out, int64_t *n_mv);
 
+/* Allocation-free form of mm2b200_sketch_device.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The call allocates nothing, on the host or on the device, and needs no context: the kernels' scratch (16 B per
+ * base of minimizer slots, per-read counts) lies in a static device array inside the library, sized for
+ * MM2B200_NOALLOC_MAX_READS reads and MM2B200_NOALLOC_MAX_BASES bases per call (16 MiB, held by every GPU that loads the
+ * library until the process exits); larger batches are rejected with MM2B200_ERR_ARG.  The device that holds the buffers
+ * must be current.  Inputs as for mm2b200_sketch_device (seq_off[0] = 0, seq_off[n_reads] = n_bases).  Outputs are the
+ * caller's device buffers: d_mv[mv_cap] (the packed minimizers, same content and order as mm2b200_sketch_device),
+ * d_mv_off[n_reads+1], d_totals[8] ([0] = number of minimizers, [1] = 1 when they exceed mv_cap: nothing is written to d_mv
+ * then; n_bases is always enough).  Everything is enqueued on `stream`.  With n_mv == NULL the call returns without waiting;
+ * otherwise it waits for the stream, stores the count and reports an overflow as MM2B200_ERR_ARG.
+ * All calls share the one scratch array: calls that overlap on a GPU (two streams, two threads) race -- serialise them. */
+#define MM2B200_NOALLOC_MAX_READS 4096
+#define MM2B200_NOALLOC_MAX_BASES (1 << 20)
+int mm2b200_sketch_device_noalloc(const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
+                                  const char *d_seq, const uint32_t *d_rid, void *stream, mm128_t *d_mv, int64_t mv_cap,
+                                  int64_t *d_mv_off, int64_t *d_totals, int64_t *n_mv);
+
 /* device time of the sketching stage with cfg.profile = 1 (accumulated) and its kernel launches */
 int mm2b200_sketch_stage_ms(mm2b200_ctx_t *ctx, double *ms, int64_t *launches);
 

@@ -733,3 +733,106 @@ extern "C" int mm2b200_sketch_batch(mm2b200_ctx_t *ctx, const mm2b200_sketch_par
 	res->n_reads = n_reads; res->mv_off = h_mv_off; res->mv = (const mm128_t*)s->h_mv.p;
 	return MM2B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// mm2b200_sketch_device_noalloc (include/mm2sketch_b200.h): the sketching kernels with their scratch in a static device
+// array, for callers that must not allocate.  No counterpart in the reference.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+// scratch of one call: the minimizer slots (16 B per base), the per-read counts, the work counter of k_sketch_odd.
+// Held by every GPU that loads the library until the process exits.
+#define NA_RAW_BYTES   ((size_t)16 * (MM2B200_NOALLOC_MAX_BASES + 1))
+#define NA_CNT_BYTES   ((size_t)4 * (MM2B200_NOALLOC_MAX_READS + 64))
+#define NA_BYTES       (NA_RAW_BYTES + NA_CNT_BYTES + 256)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// In host code g_noalloc_scratch is only a handle: the device address is asked for once per device (that device current).
+std::mutex g_na_mu;
+unsigned char *g_na_ptr[64];
+int g_na_sm[64];
+
+int noalloc_scratch(unsigned char **ptr, int *sm)
+{
+	int dev = -1;
+	CU_TRY(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= 64) return failf(MM2B200_ERR_ARG, "device ordinal %d is outside the table of the allocation-free entry point", dev);
+	std::lock_guard<std::mutex> lk(g_na_mu);
+	if (!g_na_ptr[dev]) {
+		unsigned char *p = nullptr;
+		CU_TRY(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+		int n = 0;
+		CU_TRY(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+		g_na_sm[dev] = n > 0 ? n : 1;
+		g_na_ptr[dev] = p;
+	}
+	*ptr = g_na_ptr[dev]; *sm = g_na_sm[dev];
+	return MM2B200_OK;
+}
+
+// k_sketch_pack with a bound: the caller's output holds mv_cap minimizers; totals[1] = 1 when the batch has more
+__global__ void __launch_bounds__(256) k_sketch_pack_cap(SketchWork W, int64_t mv_cap)
+{
+	if (W.mv_off[W.n_reads] > mv_cap) {
+		if (blockIdx.x == 0 && threadIdx.x == 0) W.totals[1] = 1;
+		return;
+	}
+	for (int r = blockIdx.x; r < W.n_reads; r += gridDim.x) {
+		const int n = W.n_mv[r];
+		const ulonglong2 *src = W.raw + W.seq_off[r];
+		ulonglong2 *dst = W.mv + W.mv_off[r];
+		for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+	}
+}
+
+} // namespace
+
+extern "C" int mm2b200_sketch_device_noalloc(const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
+                                             const char *d_seq, const uint32_t *d_rid, void *stream, mm128_t *d_mv, int64_t mv_cap,
+                                             int64_t *d_mv_off, int64_t *d_totals, int64_t *n_mv)
+{
+	int rc;
+	if ((rc = check_sketch(prm))) return rc;
+	if (n_reads < 0 || n_bases < 0 || mv_cap < 0 || !d_seq_off || !d_mv_off || !d_totals || (n_bases && !d_seq) || (mv_cap && !d_mv))
+		return failf(MM2B200_ERR_ARG, "bad sketching arguments");
+	if (n_reads > MM2B200_NOALLOC_MAX_READS || n_bases > MM2B200_NOALLOC_MAX_BASES)
+		return failf(MM2B200_ERR_ARG, "batch of %lld reads / %lld bases exceeds the static scratch of the allocation-free entry point (%d reads, %d bases): "
+		             "send less per call or use mm2b200_sketch_device", (long long)n_reads, (long long)n_bases, MM2B200_NOALLOC_MAX_READS, MM2B200_NOALLOC_MAX_BASES);
+	unsigned char *scratch = nullptr;
+	int sm = 1;
+	if ((rc = noalloc_scratch(&scratch, &sm))) return rc;
+	cudaStream_t st = (cudaStream_t)stream;
+	SketchWork W;
+	memset(&W, 0, sizeof(W));
+	W.seq = (const uint8_t*)d_seq; W.seq_off = d_seq_off; W.rid = d_rid;
+	W.n_reads = (int32_t)n_reads; W.w = prm->w; W.k = prm->k; W.is_hpc = prm->is_hpc ? 1 : 0;
+	W.r_begin = 0; W.r_end = (int32_t)n_reads;
+	W.raw = (ulonglong2*)scratch;
+	W.n_mv = (int32_t*)(scratch + NA_RAW_BYTES);
+	W.next_read = (int*)(scratch + NA_RAW_BYTES + NA_CNT_BYTES);
+	W.mv_off = d_mv_off; W.mv = (ulonglong2*)d_mv; W.totals = d_totals;
+	// the array keeps what the last call left: the work counter and the totals must start at zero (the slots and counts are
+	// written before they are read)
+	CU_TRY(cudaMemsetAsync(W.next_read, 0, 256, st));
+	CU_TRY(cudaMemsetAsync(d_totals, 0, 64, st));
+	if (n_reads > 0) {
+		const int64_t resident = (int64_t)sm * 3;
+		const int grid = (int)(n_reads < resident ? n_reads : resident);
+		const bool odd = !W.is_hpc && (W.k & 1) && W.k <= 15;
+		if (!odd) k_sketch<<<grid, SK_T, 0, st>>>(W);
+		else if (W.w == 10) k_sketch_odd<10><<<grid, SK_T, 0, st>>>(W);
+		else if (W.w == 5) k_sketch_odd<5><<<grid, SK_T, 0, st>>>(W);
+		else k_sketch_odd<0><<<grid, SK_T, 0, st>>>(W);
+		k_sketch_scan<<<1, 1024, 0, st>>>(W);
+		k_sketch_pack_cap<<<(int)(n_reads < (int64_t)sm * 8 ? n_reads : (int64_t)sm * 8), 256, 0, st>>>(W, mv_cap);
+		CU_TRY(cudaGetLastError());
+	} else CU_TRY(cudaMemsetAsync(d_mv_off, 0, 8, st));
+	if (n_mv) {                                   // the caller wants the count now: one wait, and the overflow check with it
+		int64_t tot[2] = { 0, 0 };
+		CU_TRY(cudaMemcpyAsync(tot, d_totals, 16, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaStreamSynchronize(st));
+		*n_mv = tot[0];
+		if (tot[1]) return failf(MM2B200_ERR_ARG, "the batch has %lld minimizers, the output holds %lld (nothing was written to it)", (long long)tot[0], (long long)mv_cap);
+	}
+	return MM2B200_OK;
+}

@@ -43,6 +43,8 @@ def _lib():
         L.mm2b200_sketch_batch.argtypes = [vp, C.POINTER(SketchParams), i64, vp, vp, vp, C.POINTER(_SketchResult)]
         L.mm2b200_sketch_device.argtypes = [vp, C.POINTER(SketchParams), i64, i64, vp, vp, vp, vp, C.POINTER(_DevSketch), C.POINTER(i64)]
         L.mm2b200_sketch_stage_ms.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64)]
+        L.mm2b200_sketch_device_noalloc.argtypes = [C.POINTER(SketchParams), i64, i64, vp, vp, vp, vp, vp, i64, vp, vp, C.POINTER(i64)]
+        L.mm2b200_sketch_device_noalloc.restype = C.c_int
         _bound = True
     return L
 
