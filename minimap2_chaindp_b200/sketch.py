@@ -13,7 +13,7 @@ from . import api
 from .api import ChainContext, _check, _view
 
 # every symbol include/mm2sketch_b200.h declares
-EXPORTED_SYMBOLS = ("mm2b200_sketch_batch", "mm2b200_sketch_device", "mm2b200_sketch_stage_ms")
+EXPORTED_SYMBOLS = ("mm2b200_sketch_batch", "mm2b200_sketch_device", "mm2b200_sketch_device_noalloc", "mm2b200_sketch_stage_ms")
 
 # (w, k, is_hpc) per preset (options.c:79-142: mm_set_opt)
 SKETCH_PRESETS = {"map-ont": (10, 15, 0), "ava-ont": (5, 15, 0), "map-pb": (10, 19, 1), "ava-pb": (5, 19, 1), "asm5": (19, 19, 0), "sr": (11, 21, 0)}
