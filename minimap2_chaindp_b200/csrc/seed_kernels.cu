@@ -355,7 +355,9 @@ __global__ void __launch_bounds__(SORT_T) k_seed_sort(SeedWork w)
 		__syncthreads();
 		if (s_tie) {
 			// equal keys in a read of more than 64 anchors: the reference's sort is not stable there -- replay it step for step
-			uint64_t *kx = w.key + base, *ky = w.ky + base;
+			// (in shared memory when both arrays fit where the sort keys were: one thread walks them with dependent accesses)
+			const bool in_sh = n <= SORT_CAP / 2;
+			uint64_t *kx = in_sh ? s_key : w.key + base, *ky = in_sh ? s_key + SORT_CAP / 2 : w.ky + base;
 			for (int i = tid; i < n; i += SORT_T) { const ulonglong2 a = w.a_un[base + i]; kx[i] = a.x; ky[i] = a.y; }
 			__syncthreads();
 			if (tid == 0) {

@@ -28,7 +28,20 @@ static __device__ void radix_sort_kv_exact(uint64_t *kx, uint64_t *ky, int n, in
 	stk[0] = 0; stk[1] = n; stk[2] = 56; sp = 3;
 	while (sp) {
 		sp -= 3;
-		const int beg = stk[sp], end = stk[sp + 1], shift = stk[sp + 2];
+		const int beg = stk[sp], end = stk[sp + 1];
+		int shift = stk[sp + 2];
+		// A level at which every key of the range has the same digit leaves the range as it is and hands all of it to the next
+		// level (one bucket, larger than RS_MIN like the range itself): such levels are skipped -- straight to the highest digit
+		// in which two keys differ (none: the keys are all equal and every remaining level is the identity).  One pass of
+		// independent loads instead of a counting pass and a permutation pass per skipped level.
+		{
+			const uint64_t x0 = kx[beg];
+			uint64_t d = 0;
+			for (int i = beg + 1; i < end; ++i) d |= kx[i] ^ x0;
+			if (shift < 56) d &= ((uint64_t)1 << (shift + 8)) - 1;       // digits above this level are equal by construction
+			if (d == 0) continue;
+			shift = (63 - __clzll((long long)d)) & ~7;
+		}
 		for (int k = 0; k < 256; ++k) head[k] = 0;
 		for (int i = beg; i < end; ++i) ++head[(kx[i] >> shift) & 0xff];
 		for (int k = 0, acc = beg; k < 256; ++k) { const int c = head[k]; head[k] = acc; acc += c; tail[k] = acc; }
