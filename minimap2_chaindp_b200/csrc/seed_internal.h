@@ -30,7 +30,7 @@ __host__ __device__ __forceinline__ uint64_t bloom_bit(uint64_t minier, int whic
 	return (z ^ (z >> 31)) & mask;
 }
 
-enum SeedTotal { ST_ANCHORS = 0, ST_MINI = 1, ST_ERROR = 2, ST_EXACT = 3, ST_MAX_READ = 4, ST_TOTALS = 8 };
+enum SeedTotal { ST_ANCHORS = 0, ST_MINI = 1, ST_ERROR = 2, ST_EXACT = 3, ST_MAX_READ = 4, ST_NEXT_READ = 5 /* work counter of k_seed_lookup */, ST_TOTALS = 8 };
 enum SeedError { SE_INDEX_RANGE = 1, SE_READ_TOO_LONG = 2 };
 
 #define SEED_IDX_BITS 21                       // anchors of one read are numbered in 21 bits inside the sort key

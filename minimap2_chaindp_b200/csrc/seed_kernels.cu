@@ -133,10 +133,15 @@ static __device__ __forceinline__ bool filters_on(int flag) { return (1 & flag &
 __global__ void __launch_bounds__(LOOKUP_T) k_seed_lookup(DevIndex ix, SeedWork w)
 {
 	const int lane = threadIdx.x & 31;
-	const int gw = (blockIdx.x * LOOKUP_T + threadIdx.x) >> 5, nw = (gridDim.x * LOOKUP_T) >> 5;
 	const unsigned lt = (1u << lane) - 1;
 	const bool filt = filters_on(w.flag);
-	for (int r = gw; r < w.n_reads; r += nw) {
+	// reads are handed out one by one through a counter (the grid is what is resident; reads differ in length and in how many
+	// of their minimizers are in the index)
+	for (;;) {
+		int r = 0;
+		if (lane == 0) r = (int)atomicAdd((unsigned long long*)(w.totals + ST_NEXT_READ), 1ULL);
+		r = __shfl_sync(0xffffffffu, r, 0);
+		if (r >= w.n_reads) break;
 		const int64_t m0 = w.mv_off[r], m1 = w.mv_off[r + 1];
 		const uint32_t bid = w.bid[r];
 		int run_a = 0, run_m = 0, rep_sum = 0, carry_en = 0;     // carry_en: rep_en of map.c:114 (rep_st = rep_en = 0 at the start)
@@ -245,7 +250,9 @@ int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cuda
 	if (w.n_reads > 0 && w.n_mv > 0) {
 		const int warps_per_cta = LOOKUP_T / 32;
 		int grid = (w.n_reads + warps_per_cta - 1) / warps_per_cta;
-		const int cap = sm_count * 8;                 // 8 CTAs of 256 threads per SM: all 64 warp slots
+		static int occ = 0;                           // resident CTAs per SM (the same on every device this process uses)
+		if (!occ) { int o = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, k_seed_lookup, LOOKUP_T, 0) != cudaSuccess || o < 1) { cudaGetLastError(); o = 4; } occ = o; }
+		const int cap = sm_count * occ;               // one wave: a grid beyond it would run its rest on a part of the machine
 		if (grid > cap) grid = cap;
 		k_seed_lookup<<<grid, LOOKUP_T, 0, s>>>(ix, w); ++n;
 	} else if (w.n_reads > 0) {
