@@ -130,7 +130,7 @@ static __device__ __forceinline__ bool filters_on(int flag) { return (1 & flag &
 // ---------------------------------------------------------------------------------------------------------
 #define LOOKUP_T 256
 
-__global__ void __launch_bounds__(LOOKUP_T) k_seed_lookup(DevIndex ix, SeedWork w)
+__global__ void __launch_bounds__(LOOKUP_T, 6) k_seed_lookup(DevIndex ix, SeedWork w)
 {
 	const int lane = threadIdx.x & 31;
 	const unsigned lt = (1u << lane) - 1;
