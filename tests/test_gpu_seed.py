@@ -208,6 +208,17 @@ def test_reads_longer_than_the_shared_memory_sort(ctx):
     assert int(np.diff(out.a_off).max()) > 4096
 
 
+def test_anchor_counts_around_the_sort_network_boundaries(ctx):
+    """the anchor sort pads a read to a multiple of 32 keys and changes method at distances of 32: reads of every length from 0
+    to 700 minimizers (and a few longer ones) give anchor counts on, just below and just above the multiples of 32"""
+    rng = np.random.default_rng(11)
+    table, oix = _synthetic(rng, n_keys=6000, b=8, max_list=8, deleted=0.1)
+    lens = np.concatenate([np.arange(0, 700), rng.integers(700, 1800, 40)])
+    out = _check_against_oracle(ctx, rng, oix, table, lens.size, lens, 0, max_occ=50)
+    n_a = np.diff(out.a_off)
+    assert {0, 1, 31}.issubset(set(int(x) % 32 for x in n_a)) and int(n_a.max()) > 2048 and ((n_a > 1024) & (n_a <= 2048)).any()
+
+
 def test_repetitive_minimizers_and_rep_len(ctx):
     rng = np.random.default_rng(9)
     table, oix = _synthetic(rng, n_keys=1500, b=6, max_list=40)
