@@ -20,10 +20,14 @@
 #include "mm2map_b200.h"
 
 namespace mm2b200 {
-// sketch.cu: mm2b200_sketch_device on bases that arrive in parts (reads [part_cut[k], part_cut[k+1]) are in HBM once part_ev[k] fired)
-int sketch_device_parts(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
-                        const char *d_seq, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv, int n_parts, const int64_t *part_cut,
-                        const cudaEvent_t *part_ev);
+// sketch.cu: mm_sketch for a group of chunks that share the slot arrays; reads [part_cut[k], part_cut[k+1]) of a chunk are in HBM
+// once part_ev[k] has fired -- kernels of a chunk on the sketching stream, its scan
+// and packing later on the compute stream
+int sketch_pipe_launch(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, bool first, bool last, int64_t group_reads, int64_t group_bases, int group_parts,
+                       int64_t r_off, int64_t b_off, int part_off, int64_t nr, const int64_t *d_seq_off, const char *d_seq, cudaStream_t st,
+                       int n_parts, const int64_t *part_cut, const cudaEvent_t *part_ev, cudaEvent_t done_ev);
+int sketch_pipe_finish(mm2b200_ctx *ctx, int64_t r_off, int64_t b_off, int64_t nr, const int64_t *d_seq_off, cudaStream_t st, cudaEvent_t done_ev,
+                       mm2b200_dev_sketch_t *out, int64_t *n_mv);
 }
 using namespace mm2b200;
 
@@ -130,6 +134,8 @@ struct mm2b200_index {
 	cudaStream_t copy_stream = nullptr;
 	std::vector<cudaEvent_t> ev_chunk;
 	cudaEvent_t ev_small = nullptr;
+	cudaStream_t sk_stream = nullptr;       // mm2b200_map_regs_batch: the sketching kernels follow the upload on their own stream
+	std::vector<cudaEvent_t> ev_sk;         // one per chunk: its parts are sketched
 	// packet path of the driver shim (seed_packets_begin / _end): raw request packets, gathered minimizers, response packets
 	DevBuf d_pkt_in, d_pkt_mv, d_pkt_meta, d_pkt_out;
 	PinBuf h_pkt, h_pkt_cnt;
@@ -172,6 +178,8 @@ extern "C" void mm2b200_index_destroy(mm2b200_index_t *ix)
 	if (ix->copy_stream) { cudaStreamSynchronize(ix->copy_stream); cudaStreamDestroy(ix->copy_stream); }
 	for (auto e : ix->ev_chunk) cudaEventDestroy(e);
 	if (ix->ev_small) cudaEventDestroy(ix->ev_small);
+	if (ix->sk_stream) { cudaStreamSynchronize(ix->sk_stream); cudaStreamDestroy(ix->sk_stream); }
+	for (auto e : ix->ev_sk) cudaEventDestroy(e);
 	for (PinBuf *b : { &ix->h_stage, &ix->h_totals, &ix->h_rep, &ix->h_mini_off, &ix->h_mini, &ix->h_a_off, &ix->h_a,
 	                   &ix->h_n_u, &ix->h_u_off, &ix->h_b_off, &ix->h_u, &ix->h_b, &ix->h_rec_off, &ix->h_rec }) b->release();
 	for (auto &e : ix->ev) if (e) cudaEventDestroy(e);
@@ -837,16 +845,40 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	cudaStream_t st = ix->stream;
 	if (!ix->copy_stream) CU_TRY(cudaStreamCreateWithFlags(&ix->copy_stream, cudaStreamNonBlocking));
 	const size_t R = (size_t)n_reads;
-	// Chunks of whole reads of about MM2B200_MAP_CHUNK bases (default 2 G: the sketching slots take 16 B per base, so a chunk
-	// stays below 32 GB of scratch).  A chunk is a memory bound, not a pipeline stage: inside a chunk the upload already hides
-	// behind the sketching (parts, below), the kernels of a 1-Gbase call add up to more than its upload, and every stage's tail
-	// is paid once per chunk -- so the default keeps a batch whole unless memory says otherwise.
+	// Two levels.  GROUPS of whole reads of about MM2B200_MAP_CHUNK bases (default 2 G) bound the memory: the sketching slots
+	// take 16 B per base, so a group stays below 32 GB of scratch.  Each group is cut into MM2B200_MAP_STAGES chunks (default 2;
+	// 1 for groups below 200 Mbases) that form a pipeline: the sketching kernels of all chunks follow the upload on their own
+	// stream, and a chunk is seeded, chained and post-processed on the compute stream while the next chunk's bases are still
+	// crossing PCIe and being sketched.  More chunks do not pay: every stage's tail is paid once per chunk.
 	int64_t chunk_bases = 2000000000;
 	{ const char *e = getenv("MM2B200_MAP_CHUNK"); const long long v = e ? atoll(e) : 0; if (v > 0) chunk_bases = (int64_t)v; }
-	std::vector<int64_t> cut(1, 0);
+	int n_stages = 2;
+	{ const char *e = getenv("MM2B200_MAP_STAGES"); const int v = e ? atoi(e) : 0; if (v > 0 && v <= 64) n_stages = v; }
+	int64_t stage_min = 200000000;                  // smaller groups are not worth a second chunk's tails (MM2B200_MAP_STAGE_MIN, bases)
+	{ const char *e = getenv("MM2B200_MAP_STAGE_MIN"); const long long v = e ? atoll(e) : 0; if (v > 0) stage_min = (int64_t)v; }
+	std::vector<int64_t> gcut(1, 0);
 	for (int64_t r = 0; r < n_reads; ++r)
-		if (seq_off[r + 1] - seq_off[cut.back()] >= chunk_bases && r + 1 < n_reads) cut.push_back(r + 1);
-	cut.push_back(n_reads);
+		if (seq_off[r + 1] - seq_off[gcut.back()] >= chunk_bases && r + 1 < n_reads) gcut.push_back(r + 1);
+	gcut.push_back(n_reads);
+	std::vector<int64_t> cut(1, 0);
+	std::vector<size_t> grp_first;                  // first chunk of every group, and one behind the last
+	for (size_t g = 0; g + 1 < gcut.size(); ++g) {
+		grp_first.push_back(cut.size() - 1);
+		const int64_t gb = n_reads ? seq_off[gcut[g + 1]] - seq_off[gcut[g]] : 0;
+		const int ns = gb < stage_min ? 1 : n_stages;
+		// the first chunk is the smaller one (MM2B200_MAP_FIRST percent of the group, default a third with two chunks; measured 30 / 35 / 40 / 45 %: 34.6 / 35.0 / 35.1 / 35.6 ms): what follows its
+		// sketching should end when the last chunk's sketching does, which is when the upload ends
+		double first = 1.0 / ns;
+		if (ns == 2) first = 1.0 / 3;
+		{ const char *e = getenv("MM2B200_MAP_FIRST"); const int v = e ? atoi(e) : 0; if (v > 0 && v < 100 && ns > 1) first = 0.01 * v; }
+		int made = 1;
+		for (int64_t r = gcut[g]; r < gcut[g + 1] && made < ns; ++r) {
+			const double frac = first + (1.0 - first) * (made - 1) / (ns > 1 ? ns - 1 : 1);
+			if ((double)(seq_off[r + 1] - seq_off[gcut[g]]) >= frac * (double)gb && r + 1 < gcut[g + 1]) { cut.push_back(r + 1); ++made; }
+		}
+		cut.push_back(gcut[g + 1]);
+	}
+	grp_first.push_back(cut.size() - 1);
 	const size_t n_chunks = cut.size() - 1;
 	char *d_seq; int64_t *d_off; uint32_t *d_bid, *d_hash; int32_t *d_qlen;
 	{
@@ -875,6 +907,13 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	if (!ix->ev_small) CU_TRY(cudaEventCreateWithFlags(&ix->ev_small, cudaEventDisableTiming));
 	CU_TRY(cudaEventRecord(ix->ev_small, ix->copy_stream));
 	CU_TRY(cudaStreamWaitEvent(st, ix->ev_small, 0));
+	if (!ix->sk_stream) CU_TRY(cudaStreamCreateWithFlags(&ix->sk_stream, cudaStreamNonBlocking));
+	CU_TRY(cudaStreamWaitEvent(ix->sk_stream, ix->ev_small, 0));
+	while (ix->ev_sk.size() < n_chunks) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+		ix->ev_sk.push_back(e);
+	}
 	// every chunk's bases are queued on the copy stream now, in parts of about MM2B200_MAP_PART bases (default 48 M) with an
 	// event behind each, so that the sketching of a part can start while the following parts are still on the bus
 	int64_t part_bases = 48000000;
@@ -910,14 +949,31 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 	int64_t tot_regs = 0, tot_mv = 0, tot_anchors = 0, tot_chains = 0;
 	tr.mark("uploads queued");
 
+	size_t g = 0;                                 // the group chunk c belongs to
 	for (size_t c = 0; c < n_chunks; ++c) {
-		const int64_t r0 = cut[c], nr = cut[c + 1] - cut[c], lo = seq_off[r0] - b0, nb = seq_off[cut[c + 1]] - seq_off[r0];
+		const int64_t r0 = cut[c], nr = cut[c + 1] - cut[c];
 		const int64_t *d_off_c = d_off + r0 + (int64_t)c;
-		// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0, part by part as the bases arrive
+		while (grp_first[g + 1] <= c) ++g;
+		const size_t c0 = grp_first[g], c1 = grp_first[g + 1];
+		const int64_t g_r0 = cut[c0], g_b0 = n_reads ? seq_off[g_r0] : 0;
+		if (c == c0) {
+			// collect_minimizers (map.c:99-111) for single-segment reads: mm_sketch with rid = 0.  The kernels of every chunk of the
+			// group go on the sketching stream now, part by part behind the upload; nothing of the previous group is in flight.
+			const int64_t g_reads = cut[c1] - g_r0, g_bases = n_reads ? seq_off[cut[c1]] - g_b0 : 0;
+			const int g_parts = (int)(part_first[c1] - part_first[c0]);
+			for (size_t q = c0; q < c1; ++q) {
+				const size_t p0 = part_first[q], np = part_first[q + 1] - p0 - 1;
+				const int64_t q_b0 = n_reads ? seq_off[cut[q]] : 0;
+				if ((rc = sketch_pipe_launch(ix->ctx, sk, q == c0, q + 1 == c1, g_reads, g_bases, g_parts, cut[q] - g_r0, q_b0 - g_b0, (int)(p0 - part_first[c0]),
+				                             cut[q + 1] - cut[q], d_off + cut[q] + (int64_t)q, d_seq + (q_b0 - b0), ix->sk_stream, (int)np, part_cut.data() + p0,
+				                             ix->ev_chunk.data() + p0, ix->ev_sk[q]))) return rc;
+			}
+			tr.mark("sketching queued");
+		}
+		// the chunk's minimizers: counted and packed once its parts are sketched
 		mm2b200_dev_sketch_t dsk;
 		int64_t n_mv = 0;
-		const size_t p0 = part_first[c], np = part_first[c + 1] - p0 - 1;
-		if ((rc = sketch_device_parts(ix->ctx, sk, nr, nb, d_off_c, d_seq + lo, st, &dsk, &n_mv, (int)np, part_cut.data() + p0, ix->ev_chunk.data() + p0))) return rc;
+		if ((rc = sketch_pipe_finish(ix->ctx, r0 - g_r0, (n_reads ? seq_off[r0] : 0) - g_b0, nr, d_off_c, st, ix->ev_sk[c], &dsk, &n_mv))) return rc;
 		tr.mark("sketch counted");
 		// collect_seed_hits (map.c:187-236) on the minimizers where the sketch left them
 		SeedOut so;
@@ -945,7 +1001,7 @@ extern "C" int mm2b200_map_regs_batch(mm2b200_index_t *ix, const mm2b200_sketch_
 		tot_regs += n_regs; tot_mv += n_mv; tot_anchors += so.n_anchors; tot_chains += tot[1];
 		{                                          // the regions must be off the device before the next chunk reuses the buffers
 			CU_TRY(cudaStreamSynchronize(st));
-			sketch_stage_account(ix->ctx);
+			if (c + 1 == c1) { CU_TRY(cudaStreamSynchronize(ix->sk_stream)); sketch_stage_account(ix->ctx); }
 			post_stage_account(ix->ctx);
 		}
 	}

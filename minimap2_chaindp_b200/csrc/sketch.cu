@@ -512,7 +512,9 @@ struct SketchState {
 	Buf d_raw, d_mv, d_small, d_in;
 	Buf h_off, h_mv, h_tot;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-	std::vector<cudaEvent_t> ev_part;      // MM2B200_TRACE: one timing event behind every part of a part-wise sketch
+	// pipelined form (sketch_pipe_launch / _finish): where the group's arrays lie in d_raw / d_small
+	ulonglong2 *p_raw = nullptr; int32_t *p_n_mv = nullptr; int64_t *p_mv_off = nullptr, *p_totals = nullptr; int *p_counters = nullptr;
+	bool pipe_timed = false;
 	double ms = 0; int64_t launches = 0;
 	SketchState() { h_off.pinned = h_mv.pinned = h_tot.pinned = true; }
 };
@@ -525,7 +527,6 @@ void sketch_state_free(void *p)
 	for (Buf *b : { &s->d_raw, &s->d_mv, &s->d_small, &s->d_in, &s->h_off, &s->h_mv, &s->h_tot }) b->release();
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
-	for (auto e : s->ev_part) cudaEventDestroy(e);
 	delete s;
 }
 
@@ -551,15 +552,12 @@ int check_sketch(const mm2b200_sketch_params_t *prm)
 }
 
 // kernels on `st`; waits once for the count; leaves the packing on the stream
-// n_parts > 0: the bases arrive in parts -- reads [part_cut[k], part_cut[k+1]) are in HBM once part_ev[k] has fired (the
-// composed path uploads them on a copy stream); each part is sketched as soon as it is there, the packing waits for all.
 int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases,
-                       const int64_t *d_seq_off, const char *d_seq, const uint32_t *d_rid, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv,
-                       int n_parts = 0, const int64_t *part_cut = nullptr, const cudaEvent_t *part_ev = nullptr)
+                       const int64_t *d_seq_off, const char *d_seq, const uint32_t *d_rid, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv)
 {
 	int rc;
 	const size_t R = (size_t)n_reads;
-	if ((rc = s->d_raw.reserve(16 * ((size_t)n_bases + 1))) || (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256 + up256(4 * ((size_t)(n_parts > 0 ? n_parts : 1) + 1)))) ||
+	if ((rc = s->d_raw.reserve(16 * ((size_t)n_bases + 1))) || (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256 + 256)) ||
 	    (rc = s->h_tot.reserve(64))) return rc;
 	SketchWork W;
 	memset(&W, 0, sizeof(W));
@@ -570,8 +568,8 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 	W.n_mv = (int32_t*)cur; cur += up256(4 * (R + 1));
 	W.mv_off = (int64_t*)cur; cur += up256(8 * (R + 2));
 	W.totals = (int64_t*)cur; cur += 256;
-	int *counters = (int*)cur;                                         // one work counter per launch of k_sketch_odd
-	const bool prof = ctx_profile(ctx) != 0, trace = prof && n_parts > 0 && getenv("MM2B200_TRACE") != nullptr;
+	int *counters = (int*)cur;                                         // the work counter of k_sketch_odd
+	const bool prof = ctx_profile(ctx) != 0;
 	if (prof) {
 		if (!s->ev0) { CU_TRY(cudaEventCreate(&s->ev0)); CU_TRY(cudaEventCreate(&s->ev1)); }
 		CU_TRY(cudaEventRecord(s->ev0, st));
@@ -590,36 +588,14 @@ int sketch_device_impl(mm2b200_ctx_t *ctx, SketchState *s, const mm2b200_sketch_
 			else if (W.w == 5) k_sketch_odd<5><<<g, SK_T, 0, st>>>(W);
 			else k_sketch_odd<0><<<g, SK_T, 0, st>>>(W);
 		};
-		if (odd) CU_TRY(cudaMemsetAsync(counters, 0, 4 * ((size_t)(n_parts > 0 ? n_parts : 1)), st));
+		if (odd) CU_TRY(cudaMemsetAsync(counters, 0, 4, st));
 		W.next_read = counters;
-		if (n_parts <= 0) {
-			W.r_begin = 0; W.r_end = (int32_t)n_reads;
-			launch(grid);
-		} else {
-			for (int k = 0; k < n_parts; ++k) {
-				const int64_t nr = part_cut[k + 1] - part_cut[k];
-				CU_TRY(cudaStreamWaitEvent(st, part_ev[k], 0));
-				if (nr <= 0) continue;
-				W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1]; W.next_read = counters + k;
-				launch((int)(nr < resident ? nr : resident));
-				++launches;
-				if (trace) {
-					while ((int)s->ev_part.size() <= k) { cudaEvent_t e; CU_TRY(cudaEventCreate(&e)); s->ev_part.push_back(e); }
-					CU_TRY(cudaEventRecord(s->ev_part[k], st));
-				}
-			}
-			--launches;
-		}
+		W.r_begin = 0; W.r_end = (int32_t)n_reads;
+		launch(grid);
 		k_sketch_scan<<<1, 1024, 0, st>>>(W);
 		CU_TRY(cudaGetLastError());
 		CU_TRY(cudaMemcpyAsync(s->h_tot.p, W.totals, 8, cudaMemcpyDeviceToHost, st));
 		CU_TRY(cudaStreamSynchronize(st));
-		if (trace) {
-			for (int k = 0; k < n_parts && k < (int)s->ev_part.size(); ++k) {
-				float t = 0, u = 0; cudaEventElapsedTime(&t, s->ev0, s->ev_part[k]); cudaEventElapsedTime(&u, s->ev0, part_ev[k]);
-				fprintf(stderr, "[mm2b200 trace] part %d: bases in HBM %.3f ms, sketched %.3f ms after the stage began\n", k, u, t);
-			}
-		}
 		total = *(int64_t*)s->h_tot.p;
 		if ((rc = s->d_mv.reserve(16 * ((size_t)total + 1)))) return rc;
 		W.mv = (ulonglong2*)s->d_mv.p;
@@ -650,18 +626,103 @@ void sketch_account(mm2b200_ctx_t *ctx, SketchState *s)
 
 } // namespace
 
-// the composed path (seed_api.cu): mm2b200_sketch_device on bases that arrive in parts
+// The composed path, pipelined (seed_api.cu): a GROUP of chunks shares one slot array and one count array.  _launch puts the
+// sketching kernels of one chunk's parts on the sketching stream (they follow the upload) and records done_ev behind them;
+// _finish, on the compute stream, waits for done_ev, scans the chunk's counts and packs its minimizers -- so the seeding and
+// chaining of a chunk run while the next chunk's bases are still being uploaded and sketched.  r_off / b_off: the chunk's
+// first read / base inside the group; d_seq_off are the chunk's own offsets (first = 0).  `first` sizes the group's arrays
+// (the caller has synchronised everything that used them).
 namespace mm2b200 {
-int sketch_device_parts(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, int64_t n_reads, int64_t n_bases, const int64_t *d_seq_off,
-                        const char *d_seq, cudaStream_t st, mm2b200_dev_sketch_t *out, int64_t *n_mv, int n_parts, const int64_t *part_cut,
-                        const cudaEvent_t *part_ev)
+int sketch_pipe_launch(mm2b200_ctx *ctx, const mm2b200_sketch_params_t *prm, bool first, bool last, int64_t group_reads, int64_t group_bases, int group_parts,
+                       int64_t r_off, int64_t b_off, int part_off, int64_t nr, const int64_t *d_seq_off, const char *d_seq, cudaStream_t st,
+                       int n_parts, const int64_t *part_cut, const cudaEvent_t *part_ev, cudaEvent_t done_ev)
 {
 	int rc;
 	if ((rc = check_sketch(prm))) return rc;
 	SketchState *s = sketch_state(ctx);
 	std::lock_guard<std::mutex> lk(s->mu);
 	CU_TRY(cudaSetDevice(s->device));
-	return sketch_device_impl(ctx, s, prm, n_reads, n_bases, d_seq_off, d_seq, nullptr, st, out, n_mv, n_parts, part_cut, part_ev);
+	const bool prof = ctx_profile(ctx) != 0;
+	if (first) {
+		const size_t R = (size_t)group_reads;
+		if ((rc = s->d_raw.reserve(16 * ((size_t)group_bases + 1))) ||
+		    (rc = s->d_small.reserve(up256(4 * (R + 1)) + up256(8 * (R + 2)) + 256 + up256(4 * ((size_t)group_parts + 1)))) || (rc = s->h_tot.reserve(64))) return rc;
+		char *cur = (char*)s->d_small.p;
+		s->p_raw = (ulonglong2*)s->d_raw.p;
+		s->p_n_mv = (int32_t*)cur; cur += up256(4 * (R + 1));
+		s->p_mv_off = (int64_t*)cur; cur += up256(8 * (R + 2));
+		s->p_totals = (int64_t*)cur; cur += 256;
+		s->p_counters = (int*)cur;
+		CU_TRY(cudaMemsetAsync(s->p_counters, 0, 4 * ((size_t)group_parts + 1), st));
+		s->pipe_timed = false;
+		if (prof) {
+			if (!s->ev0) { CU_TRY(cudaEventCreate(&s->ev0)); CU_TRY(cudaEventCreate(&s->ev1)); }
+			CU_TRY(cudaEventRecord(s->ev0, st));
+		}
+	}
+	SketchWork W;
+	memset(&W, 0, sizeof(W));
+	W.seq = (const uint8_t*)d_seq; W.seq_off = d_seq_off; W.rid = nullptr;
+	W.n_reads = (int32_t)nr; W.w = prm->w; W.k = prm->k; W.is_hpc = prm->is_hpc ? 1 : 0;
+	W.raw = s->p_raw + b_off; W.n_mv = s->p_n_mv + r_off;
+	const int sm = ctx_sm_count(ctx);
+	const int64_t resident = (int64_t)sm * 3;
+	const bool odd = !W.is_hpc && (W.k & 1) && W.k <= 15 && !getenv_off("MM2B200_SKETCH_ODD");
+	int launches = 0;
+	for (int k = 0; k < n_parts; ++k) {
+		const int64_t n = part_cut[k + 1] - part_cut[k];
+		CU_TRY(cudaStreamWaitEvent(st, part_ev[k], 0));
+		if (n <= 0) continue;
+		W.r_begin = (int32_t)part_cut[k]; W.r_end = (int32_t)part_cut[k + 1]; W.next_read = s->p_counters + part_off + k;
+		const int g = (int)(n < resident ? n : resident);
+		if (!odd) k_sketch<<<g, SK_T, 0, st>>>(W);
+		else if (W.w == 10) k_sketch_odd<10><<<g, SK_T, 0, st>>>(W);
+		else if (W.w == 5) k_sketch_odd<5><<<g, SK_T, 0, st>>>(W);
+		else k_sketch_odd<0><<<g, SK_T, 0, st>>>(W);
+		++launches;
+	}
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaEventRecord(done_ev, st));
+	if (last && prof) { CU_TRY(cudaEventRecord(s->ev1, st)); s->pipe_timed = true; }
+	s->launches += launches;
+	ctx_add_launches(ctx, launches);
+	return MM2B200_OK;
+}
+
+int sketch_pipe_finish(mm2b200_ctx *ctx, int64_t r_off, int64_t b_off, int64_t nr, const int64_t *d_seq_off, cudaStream_t st, cudaEvent_t done_ev,
+                       mm2b200_dev_sketch_t *out, int64_t *n_mv)
+{
+	int rc;
+	SketchState *s = sketch_state(ctx);
+	std::lock_guard<std::mutex> lk(s->mu);
+	CU_TRY(cudaSetDevice(s->device));
+	SketchWork W;
+	memset(&W, 0, sizeof(W));
+	W.seq_off = d_seq_off; W.n_reads = (int32_t)nr;
+	W.raw = s->p_raw + b_off; W.n_mv = s->p_n_mv + r_off; W.mv_off = s->p_mv_off; W.totals = s->p_totals;
+	CU_TRY(cudaStreamWaitEvent(st, done_ev, 0));
+	int64_t total = 0;
+	if (nr > 0) {
+		const int sm = ctx_sm_count(ctx);
+		k_sketch_scan<<<1, 1024, 0, st>>>(W);
+		CU_TRY(cudaGetLastError());
+		CU_TRY(cudaMemcpyAsync(s->h_tot.p, W.totals, 8, cudaMemcpyDeviceToHost, st));
+		CU_TRY(cudaStreamSynchronize(st));
+		total = *(int64_t*)s->h_tot.p;
+		if ((rc = s->d_mv.reserve(16 * ((size_t)total + 1)))) return rc;
+		W.mv = (ulonglong2*)s->d_mv.p;
+		k_sketch_pack<<<(int)(nr < (int64_t)sm * 8 ? nr : (int64_t)sm * 8), 256, 0, st>>>(W);
+		CU_TRY(cudaGetLastError());
+		s->launches += 2;
+		ctx_add_launches(ctx, 2);
+	} else {
+		if ((rc = s->d_mv.reserve(16))) return rc;
+		CU_TRY(cudaMemsetAsync(W.mv_off, 0, 8, st));
+		CU_TRY(cudaMemsetAsync(W.totals, 0, 64, st));
+	}
+	out->d_mv_off = W.mv_off; out->d_mv = (const mm128_t*)s->d_mv.p; out->d_totals = W.totals;
+	if (n_mv) *n_mv = total;
+	return MM2B200_OK;
 }
 }
 

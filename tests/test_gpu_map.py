@@ -10,15 +10,20 @@ from post_util import read_hash
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("preset,flag,max_occ,chunk", [("map-ont", 0, 50, 0), ("map-ont", 0, 50, 20000), ("map-pb", 0, 50, 0), ("map-pb", 0, 50, 1),
-                                                        ("ava-ont", 0x1 | 0x2 | 0x400 | 0x800000, 30, 50000), ("asm5", 0, 10, 0)])
-def test_bases_in_regions_out(preset, flag, max_occ, chunk, monkeypatch):
-    """chunk > 0: MM2B200_MAP_CHUNK bases per pipeline chunk (1 = every read its own chunk), so that the call runs as many
-    chunks whose uploads overlap the computation of the chunks before them"""
-    if chunk:
-        monkeypatch.setenv("MM2B200_MAP_CHUNK", str(chunk))
-    else:
-        monkeypatch.delenv("MM2B200_MAP_CHUNK", raising=False)
+@pytest.mark.parametrize("preset,flag,max_occ,chunk,stages", [("map-ont", 0, 50, 0, 0), ("map-ont", 0, 50, 20000, 0), ("map-pb", 0, 50, 0, 0), ("map-pb", 0, 50, 1, 0),
+                                                               ("ava-ont", 0x1 | 0x2 | 0x400 | 0x800000, 30, 50000, 0), ("asm5", 0, 10, 0, 0),
+                                                               ("map-ont", 0, 50, 0, 2), ("map-pb", 0, 50, 0, 5), ("map-ont", 0, 50, 100000, 3), ("ava-ont", 0x1 | 0x2, 30, 0, 64)])
+def test_bases_in_regions_out(preset, flag, max_occ, chunk, stages, monkeypatch):
+    """chunk > 0: MM2B200_MAP_CHUNK bases per group (1 = every read its own group: the memory bound of the call); stages > 0: every
+    group runs as a pipeline of that many chunks (MM2B200_MAP_STAGES, with MM2B200_MAP_STAGE_MIN lowered so that these small
+    batches qualify): a chunk is seeded and chained while the next one is uploaded and sketched"""
+    for name, v in (("MM2B200_MAP_CHUNK", chunk), ("MM2B200_MAP_STAGES", stages), ("MM2B200_MAP_STAGE_MIN", 1 if stages else 0)):
+        if v:
+            monkeypatch.setenv(name, str(v))
+        else:
+            monkeypatch.delenv(name, raising=False)
+    if stages:
+        monkeypatch.setenv("MM2B200_MAP_PART", "30000")                 # several upload parts per chunk
     import oracle
     from oracle import post as opost, seed as oseed
     from minimap2_chaindp_b200 import api, post, seed, sketch
