@@ -1,15 +1,19 @@
 // fpgadrv_shim.cu -- the fork's driver boundary (fpga.h:37-62) on B200s: the 11 symbols the
 // fork's objects expect from the closed libfpgadrv.a, implemented over the seeding + chaining device path of this library.
-// See include/mm2fpgadrv_b200.h for the contract.  Host code only: the device work is mm2b200_seed_fill_batch.
+// See include/mm2fpgadrv_b200.h for the contract.  Host code only: the device work is in seed_api.cu (seed_packets_begin /
+// seed_packets_end; mm2b200_seed_fill_batch on the careful path).
 //
 // Structure (B200-first, not the FPGA's ring of fixed buffers):
+//   fpga_get_writebuf     -> a page-locked, recycled buffer the fork fills with one request packet
 //   fpga_writebuf_submit  -> a queue of request packets
-//   one worker per GPU    -> takes everything that waits (bounded), copies the minimizers of all packets once into a pinned
-//                            staging array (so the H2D copy is one DMA), runs ONE device batch for all reads, cuts the
-//                            records / mini_pos back into one response packet per request packet
+//   workers (2 per GPU)   -> take everything that waits (bounded) as ONE device batch.  Direct path: every packet is DMA'd
+//                            as it is, unpacked on the device, and the response packets are laid out in HBM and DMA'd into
+//                            page-locked response buffers; the host only parses headers and computes the response layout.
+//                            Careful path (a batch the device refused as a whole, or MM2B200_SHIM_ZEROCOPY=0): minimizers
+//                            copied into pinned staging, records / mini_pos cut back into response packets by the worker.
 //   fpga_get_retbuf       -> a queue of finished response packets
-// A batch the device refuses (allocation failure, anchor count beyond the index space) is halved and retried; a single read
-// that still fails is answered with err_flag = 1, the fork's own "host, redo this read" protocol (map.c:933-944).
+// On the careful path a refused batch (allocation failure, anchor count beyond the index space) is halved and retried; a
+// single read that still fails is answered with err_flag = 1, the fork's own "host, redo this read" protocol (map.c:933-944).
 #include <cuda_runtime.h>
 #include <stddef.h>
 #include <stdint.h>

@@ -250,8 +250,8 @@ int launch_seed_lookup(const DevIndex &ix, const SeedWork &w, int sm_count, cuda
 	if (w.n_reads > 0 && w.n_mv > 0) {
 		const int warps_per_cta = LOOKUP_T / 32;
 		int grid = (w.n_reads + warps_per_cta - 1) / warps_per_cta;
-		static int occ = 0;                           // resident CTAs per SM (the same on every device this process uses)
-		if (!occ) { int o = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, k_seed_lookup, LOOKUP_T, 0) != cudaSuccess || o < 1) { cudaGetLastError(); o = 4; } occ = o; }
+		// resident CTAs per SM (the same on every device this process uses; initialised once, also when several shim workers get here together)
+		static const int occ = [] { int o = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, k_seed_lookup, LOOKUP_T, 0) != cudaSuccess || o < 1) { cudaGetLastError(); o = 4; } return o; }();
 		const int cap = sm_count * occ;               // one wave: a grid beyond it would run its rest on a part of the machine
 		if (grid > cap) grid = cap;
 		k_seed_lookup<<<grid, LOOKUP_T, 0, s>>>(ix, w); ++n;
