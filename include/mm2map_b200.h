@@ -33,7 +33,12 @@ typedef struct {
 
 /* Read r owns seq[seq_off[r] .. seq_off[r+1]); bid[r] is collect_task_t.bid (rank of the read's name among the target names,
  * bit 31 = the name IS a target name; map.c:262-284,352), hash[r] the read-name hash (map.c:347-349).  seed->chain carries the
- * DP parameters (max_dist_x / max_dist_y = the chaining gaps of map.c:358-366).  Inputs are host pointers, not consumed. */
+ * DP parameters (max_dist_x / max_dist_y = the chaining gaps of map.c:358-366).  Inputs are host pointers, not consumed.
+ * The call runs as a pipeline: the bases cross PCIe in parts (page-locked seq[] makes each a plain DMA), the sketching of a
+ * part follows its upload on a stream of its own, and the batch is cut into two chunks of whole reads so that the first is
+ * seeded, chained and post-processed while the second is still being uploaded and sketched; minimizers, anchors and chains
+ * never leave HBM.  Scratch: 16 B of HBM per base of a group of MM2B200_MAP_CHUNK (2 G) bases; larger batches run group by
+ * group. */
 int mm2b200_map_regs_batch(mm2b200_index_t *idx, const mm2b200_sketch_params_t *sketch, const mm2b200_seed_params_t *seed,
                            const mm2b200_post_params_t *post, int64_t n_reads, const int64_t *seq_off, const char *seq,
                            const uint32_t *bid, const uint32_t *hash, mm2b200_map_result_t *res);
